@@ -1,0 +1,391 @@
+"""Pin the oracle restatement against the reference itself and write golden fixtures.
+
+Run in the BUILD CONTAINER only (needs /root/reference):
+
+    python -m oracle.make_golden            # asserts + rewrites tests/golden/*.pt
+
+For every case it (1) imports the reference's ``acqfs.py`` / ``actor.py`` /
+``amortized_network.py`` verbatim over ``oracle/botorch_shim.py``, (2) runs them on
+seeded inputs, (3) runs ``oracle/hes_oracle.py`` on the same inputs and the same
+RNG stream, (4) asserts agreement to 1e-12 (values) / 1e-10 (gradients), and (5)
+stores inputs, every random draw, and the reference outputs + gradients in
+``tests/golden/<case>.pt`` so that the GPU box (where /root/reference does not
+exist) can check both the oracle and the CUDA path against them.
+
+TEST INFRASTRUCTURE ONLY.
+"""
+from __future__ import annotations
+
+import os
+import sys
+import tempfile
+import types
+
+import torch
+
+from nonmyopia_b200.synthetic import make_problem
+from oracle import botorch_shim as bs
+from oracle import gp_math, hes_oracle as ho
+
+GOLDEN_DIR = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden")
+F64 = torch.float64
+
+
+def _shim_model(prob, n=None):
+    X = prob.train_X[-n:] if n else prob.train_X
+    Y = prob.train_Y[-n:] if n else prob.train_Y
+    if prob.outputscale is None:
+        cm = bs.MaternKernel(nu={"matern12": 0.5, "matern32": 1.5, "matern52": 2.5}[prob.kernel]) \
+            if prob.kernel != "rbf" else bs.RBFKernel()
+        cm.lengthscale = prob.lengthscale
+    else:
+        base = bs.RBFKernel(ard_num_dims=prob.d) if prob.kernel == "rbf" else bs.MaternKernel(
+            nu={"matern12": 0.5, "matern32": 1.5, "matern52": 2.5}[prob.kernel], ard_num_dims=prob.d)
+        base.lengthscale = prob.lengthscale
+        cm = bs.ScaleKernel(base)
+        cm.outputscale = prob.outputscale
+    lik = bs.GaussianLikelihood()
+    lik.noise = prob.noise
+    m = bs.SingleTaskGP(X, Y, likelihood=lik, covar_module=cm)
+    m.mean_module.constant = torch.tensor(prob.mean_const)
+    m.eval()
+    return m, X, Y
+
+
+def _gp_inputs(prob, X, Y):
+    return dict(train_X=X.clone(), train_Y=Y.clone(), kernel=prob.kernel,
+                lengthscale=float(prob.lengthscale),
+                outputscale=prob.outputscale, noise=prob.noise, mean_const=prob.mean_const,
+                ard=prob.outputscale is not None)
+
+
+def _cost_hypers(spec: ho.CostSpec):
+    return dict(radius=spec.radius, k=spec.k, p_norm=spec.p_norm, max_noise=spec.max_noise,
+                discount=spec.discount, discount_threshold=spec.discount_threshold)
+
+
+def _close(a, b, tol, what):
+    err = (a - b).abs().max().item() if a.numel() else 0.0
+    scale = max(1.0, b.abs().max().item() if b.numel() else 1.0)
+    assert err <= tol * scale, f"{what}: |ref - oracle| = {err:.3e}"
+    return err
+
+
+def _ref_acqf(ref, model, spec: ho.HESSpec, n_samples=64):
+    return ref.acqfs.qMultiStepHEntropySearch(
+        model=model, loss_function_class=ref.acqfs.qLossFunctionTopK,
+        loss_func_hypers=dict(dist_weight=spec.dist_weight, dist_threshold=spec.dist_threshold),
+        cost_function_class=ref.acqfs.qCostFunction, cost_func_hypers=_cost_hypers(spec.cost),
+        lookahead_steps=spec.lookahead, n_actions=spec.n_actions,
+        n_fantasy_at_design_pts=list(spec.nf), n_fantasy_at_action_pts=n_samples,
+        enable_ts=spec.enable_ts)
+
+
+def _ref_net(ref, P, d, H):
+    net = ref.amortized_network.AmortizedNetwork(
+        d + 1, d, H, 1, torch.tensor([[0.0, 1.0]] * d, dtype=F64)).double()
+    net.load_state_dict({k: v.clone() for k, v in P.items()})
+    return net
+
+
+# --------------------------------------------------------------------------
+def case_ts_am(ref, name, env, n, L, n_r, H, seed, cost: ho.CostSpec, kernel="matern52", ard=True):
+    prob = make_problem(env, seed=2, kernel=kernel, outputscale=1.0 if ard else None)
+    model, X, Y = _shim_model(prob, n)
+    d = prob.d
+    torch.manual_seed(seed)
+    acq = _ref_acqf(ref, model, ho.HESSpec(L, [1] * L, 1, cost, enable_ts=True))
+    acq.dump_model()
+    path = acq.f
+    P = ho.init_policy_params(d, H)
+    prev_X = X[-1:].expand(n_r, -1).clone()
+    prev_y = Y[-1:].expand(n_r, -1).clone()
+    prev_h = torch.randn(n_r, H, dtype=F64)
+    spec = ho.HESSpec(L, [1] * L, 1, cost, enable_ts=True)
+    outs = {}
+    for mode, noisy in (("main", False), ("orig", True)):
+        net = _ref_net(ref, P, d, H)
+        torch.manual_seed(seed + 17)
+        r = acq.forward(prev_X, prev_y, prev_h, net, enable_noise=noisy)
+        tot = (r["acqf_loss"] + (2.0 - r["acqf_cost"]).abs()).mean()
+        g_ref = torch.autograd.grad(tot, list(net.parameters()))
+        g_ref = {k: g for (k, _), g in zip(net.named_parameters(), g_ref)}
+        Pq = {k: v.clone().requires_grad_(True) for k, v in P.items()}
+        torch.manual_seed(seed + 17)
+        o = ho.hes_forward(spec, prev_X, prev_y, prev_h, Pq, path=path, enable_noise=noisy)
+        tot_o = (o["acqf_loss"] + (2.0 - o["acqf_cost"]).abs()).mean()
+        g_or = dict(zip(Pq.keys(), torch.autograd.grad(tot_o, list(Pq.values()))))
+        _close(o["acqf_loss"], r["acqf_loss"], 1e-12, f"{name}/{mode} loss")
+        _close(o["acqf_cost"], r["acqf_cost"], 1e-12, f"{name}/{mode} cost")
+        for s in range(L):
+            _close(o["X"][s], r["X"][s], 1e-13, f"{name}/{mode} X[{s}]")
+            _close(o["hidden_state"][s], r["hidden_state"][s], 1e-13, f"{name}/{mode} h[{s}]")
+        _close(o["actions"], r["actions"], 1e-13, f"{name}/{mode} actions")
+        for k in g_ref:
+            _close(g_or[k], g_ref[k], 1e-10, f"{name}/{mode} grad {k}")
+        outs[mode] = dict(
+            acqf_loss=r["acqf_loss"].detach(), acqf_cost=r["acqf_cost"].detach(),
+            X=[x.detach() for x in r["X"]], actions=r["actions"].detach(),
+            hidden_state=[h.detach() for h in r["hidden_state"]],
+            grads={k: v.detach() for k, v in g_ref.items()},
+            rot=[None if q is None else (q[0], q[1]) for q in o["draws"].rot],
+            cost_noise=[z for z in o["draws"].cost_noise])
+    fx = dict(kind="ts_am", gp=_gp_inputs(prob, X, Y), d=d, H=H, L=L, n_r=n_r,
+              cost=_cost_hypers(cost), budget=2.0,
+              path=dict(W=path.W.clone(), w=path.w.clone(), v=path.v.clone()),
+              policy={k: v.clone() for k, v in P.items()},
+              prev_X=prev_X, prev_y=prev_y, prev_h=prev_h, out=outs)
+    torch.save(fx, os.path.join(GOLDEN_DIR, name + ".pt"))
+    print(f"[golden] {name}: ok")
+
+
+def case_ts_free(ref, name, env, n, L, n_r, seed, cost):
+    """HES-TS without the network: maps are free tensors (actor.py:559-560)."""
+    prob = make_problem(env, seed=2)
+    model, X, Y = _shim_model(prob, n)
+    d = prob.d
+    torch.manual_seed(seed)
+    spec = ho.HESSpec(L, [1] * L, 1, cost, enable_ts=True)
+    acq = _ref_acqf(ref, model, spec)
+    acq.dump_model()
+    path = acq.f
+    prev_X = X[-1:].expand(n_r, -1).clone()
+    prev_y = Y[-1:].expand(n_r, -1).clone()
+    logits = [torch.randn(n_r, d, dtype=F64) * 0.5 for _ in range(L + 1)]
+    la = [l.clone().requires_grad_(True) for l in logits]
+    lb = [l.clone().requires_grad_(True) for l in logits]
+    h0 = torch.zeros(n_r, 4, dtype=F64)
+    torch.manual_seed(seed + 17)
+    r = acq.forward(prev_X, prev_y, h0, [torch.sigmoid(x) for x in la], enable_noise=False)
+    g_ref = torch.autograd.grad((r["acqf_loss"] + (2.0 - r["acqf_cost"]).abs()).mean(), la)
+    torch.manual_seed(seed + 17)
+    o = ho.hes_forward(spec, prev_X, prev_y, h0, [torch.sigmoid(x) for x in lb], path=path,
+                       enable_noise=False)
+    g_or = torch.autograd.grad((o["acqf_loss"] + (2.0 - o["acqf_cost"]).abs()).mean(), lb)
+    _close(o["acqf_loss"], r["acqf_loss"], 1e-12, name + " loss")
+    _close(o["acqf_cost"], r["acqf_cost"], 1e-12, name + " cost")
+    for a, b in zip(g_or, g_ref):
+        _close(a, b, 1e-10, name + " grad")
+    fx = dict(kind="ts_free", gp=_gp_inputs(prob, X, Y), d=d, L=L, n_r=n_r, cost=_cost_hypers(cost),
+              budget=2.0, path=dict(W=path.W.clone(), w=path.w.clone(), v=path.v.clone()),
+              prev_X=prev_X, prev_y=prev_y, logits=logits,
+              out=dict(acqf_loss=r["acqf_loss"].detach(), acqf_cost=r["acqf_cost"].detach(),
+                       grads=[g.detach() for g in g_ref], cost_noise=list(o["draws"].cost_noise)))
+    torch.save(fx, os.path.join(GOLDEN_DIR, name + ".pt"))
+    print(f"[golden] {name}: ok")
+
+
+def case_mc(ref, name, env, n, nf, n_r, S_a, seed, cost, kernel="matern52", ard=True):
+    prob = make_problem(env, seed=2, kernel=kernel, outputscale=1.0 if ard else None)
+    model, X, Y = _shim_model(prob, n)
+    d, L = prob.d, len(nf)
+    torch.manual_seed(seed)
+    spec = ho.HESSpec(L, list(nf), 1, cost, enable_ts=False)
+    acq = _ref_acqf(ref, model, spec, n_samples=S_a)      # draws L+1 sampler seeds from the RNG
+    acq.dump_model()
+    prev_X = X[-1:].expand(n_r, -1).clone()
+    prev_y = Y[-1:].expand(n_r, -1).clone()
+    h0 = torch.zeros(n_r, 4, dtype=F64)
+    widths = [1]
+    for w in nf:
+        widths.append(widths[-1] * w)
+    logits = [torch.randn(widths[s] * n_r, d, dtype=F64) * 0.7 for s in range(L + 1)]
+    la = [l.clone().requires_grad_(True) for l in logits]
+    lb = [l.clone().requires_grad_(True) for l in logits]
+    torch.manual_seed(seed + 17)
+    r = acq.forward(prev_X, prev_y, h0, [torch.sigmoid(x) for x in la], enable_noise=False)
+    g_ref = torch.autograd.grad((r["acqf_loss"] + (2.0 - r["acqf_cost"]).abs()).mean(), la)
+    design_base = [(s.base_samples.reshape(-1).clone() if s.base_samples is not None else None)
+                   for s in acq.design_samplers]
+    action_base = acq.action_sampler.base_samples.reshape(-1).clone()
+    gp = model.dense()
+    torch.manual_seed(seed + 17)
+    o = ho.hes_forward(spec, prev_X, prev_y, h0, [torch.sigmoid(x) for x in lb], gp=gp,
+                       design_base=design_base, action_base=action_base, enable_noise=False)
+    g_or = torch.autograd.grad((o["acqf_loss"] + (2.0 - o["acqf_cost"]).abs()).mean(), lb)
+    _close(o["acqf_loss"], r["acqf_loss"], 1e-12, name + " loss")
+    _close(o["acqf_cost"], r["acqf_cost"], 1e-12, name + " cost")
+    for a, b in zip(g_or, g_ref):
+        _close(a, b, 1e-10, name + " grad")
+    fx = dict(kind="mc", gp=_gp_inputs(prob, X, Y), d=d, L=L, nf=list(nf), n_r=n_r, S_a=S_a,
+              cost=_cost_hypers(cost), budget=2.0, prev_X=prev_X, prev_y=prev_y, logits=logits,
+              design_base=design_base, action_base=action_base,
+              out=dict(acqf_loss=r["acqf_loss"].detach(), acqf_cost=r["acqf_cost"].detach(),
+                       grads=[g.detach() for g in g_ref], cost_noise=list(o["draws"].cost_noise)))
+    torch.save(fx, os.path.join(GOLDEN_DIR, name + ".pt"))
+    print(f"[golden] {name}: ok")
+
+
+def case_baselines(ref, name, env, n, n_r, seed, cost):
+    prob = make_problem(env, seed=2)
+    model, X, Y = _shim_model(prob, n)
+    d = prob.d
+    best_f = float(Y.max())
+    res = {}
+    n_r_default = n_r
+    for algo in ("qEI", "qPI", "qSR", "qUCB", "qUCB-2.0", "qKG"):
+        # qKG's cost comes out as a [num_fantasies] vector (cdist of 64 x 64 blocks,
+        # acqfs.py:152-164) that the actor adds to the [n_restarts] loss, so the
+        # reference only runs with n_restarts == 64 (its default): keep that quirk.
+        n_r = 64 if algo == "qKG" else n_r_default
+        prev_X = X[-1:].expand(n_r, -1).clone()
+        prev_y = Y[-1:].expand(n_r, -1).clone()
+        torch.manual_seed(seed)
+        sampler = bs.SobolQMCNormalSampler(sample_shape=64, seed=0, resample=False)
+        acq = ref.acqfs.qBOAcqf(
+            name=algo, model=model, lookahead_steps=1 if algo == "qKG" else 0, n_actions=1,
+            n_fantasy_at_design_pts=[64], loss_function_class=ref.acqfs.qLossFunctionTopK,
+            loss_func_hypers=dict(dist_weight=1, dist_threshold=0.5),
+            cost_function_class=ref.acqfs.qCostFunction, cost_func_hypers=_cost_hypers(cost),
+            sampler=sampler, best_f=best_f)
+        if algo == "qKG":
+            maps = [torch.rand(n_r, d, dtype=F64), torch.rand(64 * n_r, d, dtype=F64)]
+        else:
+            maps = [torch.rand(n_r, d, dtype=F64)]
+        ma = [m.clone().requires_grad_(True) for m in maps]
+        mb = [m.clone().requires_grad_(True) for m in maps]
+        torch.manual_seed(seed + 17)
+        r = acq.forward(prev_X, prev_y, ma)
+        g_ref = torch.autograd.grad((r["acqf_loss"] + r["acqf_cost"]).mean(), ma)
+        base = sampler.base_samples.reshape(-1).clone()
+        torch.manual_seed(seed + 17)
+        o = ho.baseline_forward(algo, model.dense(), prev_X, mb, base=base, cost_spec=cost,
+                                best_f=best_f)
+        g_or = torch.autograd.grad((o["acqf_loss"] + o["acqf_cost"]).mean(), mb)
+        _close(o["acqf_loss"], r["acqf_loss"], 1e-12, f"{name}/{algo} loss")
+        _close(o["acqf_cost"], r["acqf_cost"], 1e-12, f"{name}/{algo} cost")
+        for a, b in zip(g_or, g_ref):
+            _close(a, b, 1e-10, f"{name}/{algo} grad")
+        # cost noise actually consumed (same order as the reference's randn_like calls)
+        torch.manual_seed(seed + 17)
+        if algo == "qKG":
+            nz = [torch.randn(n_r, 1, 1, dtype=F64), torch.randn(n_r, 64, 64, dtype=F64)]
+        else:
+            nz = [torch.randn(n_r, 1, 1, dtype=F64)]
+        res[algo] = dict(maps=maps, base=base, n_r=n_r, prev_X=prev_X, acqf_loss=r["acqf_loss"].detach(),
+                         acqf_cost=r["acqf_cost"].detach(), grads=[g.detach() for g in g_ref],
+                         cost_noise=nz)
+    fx = dict(kind="baselines", gp=_gp_inputs(prob, X, Y), d=d, n_r=n_r, cost=_cost_hypers(cost),
+              best_f=best_f, algos=res)
+    torch.save(fx, os.path.join(GOLDEN_DIR, name + ".pt"))
+    print(f"[golden] {name}: ok")
+
+
+def case_query(ref, name, env, n, L, n_r, H, seed, cost, n_iter):
+    """Whole ``Actor.query`` (HES-TS-AM) verbatim vs ``hes_oracle.query_loop``."""
+    prob = make_problem(env, seed=2)
+    model, X, Y = _shim_model(prob, n)
+    d = prob.d
+    tmp = tempfile.mkdtemp()
+    parms = types.SimpleNamespace(
+        algo="HES", algo_ts=True, amortized=True, algo_lookahead_steps=L, x_dim=d, y_dim=1,
+        hidden_dim=H, n_actions=1, n_restarts=n_r, n_samples=64, env_discretized=False,
+        num_categories=None, bounds=torch.tensor([[0.0, 1.0]] * d, dtype=F64), torch_dtype=F64,
+        device="cpu", acq_opt_lr=1e-3, acq_opt_iter=n_iter, n_initial_points=n, save_dir=tmp,
+        budget=2 * d**0.5, plot=False, loss_function_class=ref.acqfs.qLossFunctionTopK,
+        loss_func_hypers=dict(dist_weight=1, dist_threshold=0.5),
+        cost_function_class=ref.acqfs.qCostFunction, cost_func_hypers=_cost_hypers(cost))
+    torch.manual_seed(seed)
+    actor = ref.actor.Actor(parms)
+    P0 = {k: v.detach().clone() for k, v in actor.maps.state_dict().items()}
+    hbuf = torch.randn(n, H, dtype=F64)
+    buffer = bs.TensorDict(dict(x=X, y=Y, h=hbuf, cost=torch.zeros(n, dtype=F64)))
+    actor.construct_acqf(model, buffer)
+    actor.hidden_noise = torch.randn(n_r, H).to(F64)
+    torch.manual_seed(seed + 5)
+    # dump_model draws the path from the global RNG first, then the loop consumes it
+    out = actor.query(buffer, iteration=n, save_trajectory=False)
+    # oracle: same stream
+    torch.manual_seed(seed + 5)
+    path = gp_math.draw_matheron_path(model.dense(), model.train_targets, 1)
+    # actor.py:526-555 builds two throw-away networks (random init) before the loop
+    _burn = [_ref_net(ref, P0, d, H) for _ in range(2)]
+    spec = ho.HESSpec(L, [1] * L, 1, cost, enable_ts=True)
+    P = {k: v.clone() for k, v in P0.items()}
+    prev_X = X[-1:].expand(n_r, -1)
+    prev_y = Y[-1:].expand(n_r, -1)
+    prev_h = hbuf[-1:].expand(n_r, -1) + actor.hidden_noise
+    draws = []
+
+    def rec(ep, o, total):
+        pass
+
+    o = ho.query_loop(spec, prev_X, prev_y, prev_h, P, budget=parms.budget, lr=1e-3,
+                      n_iter=n_iter, past_initial=False, path=path, record=rec)
+    _close(o["best_loss"], out["all_losses"], 1e-9, name + " best_loss")
+    _close(o["best_cost"], out["all_costs"], 1e-9, name + " best_cost")
+    assert int(o["idx"]) == int(out["chosen_idx"]), (o["idx"], out["chosen_idx"])
+    _close(o["next_X"], out["next_X"], 1e-9, name + " next_X")
+    # replay once more to record the per-iteration draws for the CUDA path
+    torch.manual_seed(seed + 5)
+    path2 = gp_math.draw_matheron_path(model.dense(), model.train_targets, 1)
+    _burn = [_ref_net(ref, P0, d, H) for _ in range(2)]
+    P2 = {k: v.clone() for k, v in P0.items()}
+    all_draws = []
+    frozen = {k: v.clone() for k, v in P0.items()}
+    # (the loop inside query_loop draws main-rollout rotations, cost noise, then the
+    #  original rollout's; re-run it iteration by iteration capturing the draws)
+    leaves = list(P2.values())
+    for p in leaves:
+        p.requires_grad_(True)
+    opt = torch.optim.AdamW(leaves, lr=1e-3)
+    for ep in range(o["n_iter"]):
+        om = ho.hes_forward(spec, prev_X, prev_y, prev_h, P2, path=path2, enable_noise=False)
+        with torch.no_grad():
+            oo = ho.hes_forward(spec, prev_X, prev_y, prev_h, frozen, path=path2, enable_noise=True)
+        KL = 0
+        for s in range(L):
+            KL = KL + ho.cosine_distance(oo["X"][s], om["X"][s])
+        KL = KL + ho.cosine_distance(oo["actions"], om["actions"])
+        total = om["acqf_loss"] + (parms.budget - om["acqf_cost"]).abs() + KL
+        g = torch.autograd.grad(total.mean(), leaves, allow_unused=True)
+        for p, gg in zip(leaves, g):
+            p.grad = gg
+        opt.step()
+        opt.zero_grad()
+        all_draws.append(dict(main_rot=om["draws"].rot, main_noise=om["draws"].cost_noise,
+                              orig_rot=oo["draws"].rot, orig_noise=oo["draws"].cost_noise))
+    for k in P:
+        _close(P2[k].detach(), P[k].detach(), 1e-12, name + " replay params " + k)
+    fx = dict(kind="query_ts_am", gp=_gp_inputs(prob, X, Y), d=d, H=H, L=L, n_r=n_r,
+              cost=_cost_hypers(cost), budget=parms.budget, lr=1e-3, n_iter=o["n_iter"],
+              path=dict(W=path.W.clone(), w=path.w.clone(), v=path.v.clone()),
+              policy=P0, prev_X=prev_X.clone(), prev_y=prev_y.clone(), prev_h=prev_h.clone(),
+              draws=all_draws,
+              out=dict(all_losses=out["all_losses"], all_costs=out["all_costs"],
+                       chosen_idx=int(out["chosen_idx"]), next_X=out["next_X"],
+                       actions=out["actions"], hidden_state=out["hidden_state"],
+                       final_policy={k: v.detach().clone() for k, v in P.items()}))
+    torch.save(fx, os.path.join(GOLDEN_DIR, name + ".pt"))
+    print(f"[golden] {name}: ok ({o['n_iter']} iterations, idx {int(o['idx'])})")
+
+
+def main():
+    os.makedirs(GOLDEN_DIR, exist_ok=True)
+    ref = bs.load_reference()
+    euclid = lambda r: ho.CostSpec(radius=r, k=1, max_noise=1e-5, p_norm=2.0)
+    # TS-AM: cfg-2a shape (Ackley 2D, n=50, L=3) at 8 restarts; H=64
+    case_ts_am(ref, "ts_am_ackley_L3", "Ackley", 50, 3, 8, 64, 11, euclid(0.075))
+    # cfg-1 shape: L=1
+    case_ts_am(ref, "ts_am_ackley_L1", "Ackley", 50, 1, 8, 64, 12, euclid(0.075))
+    # cfg-4 shape: Cosine8 8D (n cut to 60 to keep the fixture small), manhattan cost
+    case_ts_am(ref, "ts_am_cosine8_L3", "Cosine8", 60, 3, 6, 32, 13,
+               ho.CostSpec(radius=0.15, k=1, max_noise=1e-5, p_norm=1.0))
+    # bare isotropic Matern-1.5 (--kernel Matern-1.5) and r-spotlight cost, non-markovian discount
+    case_ts_am(ref, "ts_am_alpine_m32", "Alpine", 40, 2, 6, 16, 14,
+               ho.CostSpec(radius=0.075, k=1e3, max_noise=0.0, p_norm=2.0), kernel="matern32", ard=False)
+    case_ts_am(ref, "ts_am_ackley_rbf_disc", "Ackley", 30, 2, 6, 16, 15,
+               ho.CostSpec(radius=0.075, k=1, max_noise=1e-5, p_norm=2.0, discount=0.1,
+                           discount_threshold=0.375), kernel="rbf")
+    case_ts_free(ref, "ts_free_ackley_L2", "Ackley", 50, 2, 8, 21, euclid(0.075))
+    # MC trees: cfg-3 widths scaled down
+    case_mc(ref, "mc_hartmann_L3", "Hartmann", 40, [4, 3, 2], 3, 8, 31, euclid(0.125))
+    case_mc(ref, "mc_ackley_L1", "Ackley", 30, [8], 4, 16, 32, euclid(0.075))
+    case_mc(ref, "mc_ackley_L4_m12", "Ackley", 25, [4, 2, 2, 1], 2, 8, 33, euclid(0.075),
+            kernel="matern12", ard=False)
+    case_baselines(ref, "baselines_ackley", "Ackley", 30, 5, 41, euclid(0.075))
+    case_query(ref, "query_ts_am_ackley_L1", "Ackley", 50, 1, 8, 32, 51, euclid(0.075), n_iter=12)
+
+
+if __name__ == "__main__":
+    sys.exit(main())
