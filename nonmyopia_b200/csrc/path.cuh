@@ -1,0 +1,100 @@
+// Thompson-sample path evaluation, device side (reference acqfs.py:362,409-411).
+//   f(x) = c + feat_scale * sum_m [ sin(z_m) w_m + cos(z_m) w_{M/2+m} ] + amp * sum_j kappa(x, X_j) v_j
+//   z_m  = pi * sum_k w_phase[m,k] x_k          (w_phase = W / (lengthscale * pi))
+// A group of `nl` threads shares one point; every thread returns PARTIAL sums of the
+// value and of the d gradient components over its slice of the frequencies and of the
+// training points; the caller reduces over the group.  The constants are read
+// through the read-only path (L1/L2 resident: <= 32 KB + 8 KB + n*(d+1)*8 B).
+#pragma once
+#include "common.cuh"
+
+namespace nmb {
+
+template <typename T> struct PathDev {
+    int d, n_freq, n_train, n_paths, kernel_id;
+    T feat_scale, amplitude, mean_const;
+    const T* __restrict__ w_phase;
+    const T* __restrict__ w_feat;
+    const T* __restrict__ inv_ls;
+    const T* __restrict__ train_x;
+    const T* __restrict__ v_update;
+};
+
+template <typename T> inline PathDev<T> to_dev(const nmb_path_t& p) {
+    PathDev<T> o;
+    o.d = p.d; o.n_freq = p.n_freq; o.n_train = p.n_train; o.n_paths = p.n_paths;
+    o.kernel_id = p.kernel_id;
+    o.feat_scale = (T)p.feat_scale; o.amplitude = (T)p.amplitude; o.mean_const = (T)p.mean_const;
+    o.w_phase = (const T*)p.w_phase; o.w_feat = (const T*)p.w_feat; o.inv_ls = (const T*)p.inv_ls;
+    o.train_x = (const T*)p.train_x; o.v_update = (const T*)p.v_update;
+    return o;
+}
+
+// x: the point (registers, DMAX padded), s: path index, (lane, nl): this thread's slot
+// in its group.  Outputs are partial: y_part excludes mean_const.
+template <typename T, int DMAX>
+__device__ __forceinline__ void path_partial(const PathDev<T>& P, const T (&x)[DMAX], int s, int lane,
+                                             int nl, T& y_part, T (&g_part)[DMAX]) {
+    const int d = P.d;
+    T acc = T(0);
+    T gacc[DMAX];
+#pragma unroll
+    for (int k = 0; k < DMAX; ++k) gacc[k] = T(0);
+
+    // ---- random-Fourier-feature prior
+    const T* wsin = P.w_feat + (size_t)s * 2 * P.n_freq;
+    const T* wcos = wsin + P.n_freq;
+    for (int m = lane; m < P.n_freq; m += nl) {
+        const T* wr = P.w_phase + (size_t)m * d;
+        T wk[DMAX];
+        T u = T(0);
+#pragma unroll
+        for (int k = 0; k < DMAX; ++k) {
+            wk[k] = (k < d) ? __ldg(wr + k) : T(0);
+            u = fma(wk[k], x[k], u);
+        }
+        T sn, cs;
+        Num<T>::sincospi(u, &sn, &cs);
+        const T ws = __ldg(wsin + m), wc = __ldg(wcos + m);
+        acc = fma(sn, ws, fma(cs, wc, acc));
+        const T dphi = cs * ws - sn * wc;   // d/dz of (sin z ws + cos z wc)
+#pragma unroll
+        for (int k = 0; k < DMAX; ++k) gacc[k] = fma(dphi, wk[k], gacc[k]);
+    }
+    acc *= P.feat_scale;
+    const T gs = P.feat_scale * Num<T>::kPi;
+#pragma unroll
+    for (int k = 0; k < DMAX; ++k) gacc[k] *= gs;
+
+    // ---- pathwise update  amp * k(x, X_tr) . v
+    T ils[DMAX];
+#pragma unroll
+    for (int k = 0; k < DMAX; ++k) ils[k] = (k < d) ? __ldg(P.inv_ls + k) : T(0);
+    const T* vv = P.v_update + (size_t)s * P.n_train;
+    T kacc = T(0);
+    T kg[DMAX];
+#pragma unroll
+    for (int k = 0; k < DMAX; ++k) kg[k] = T(0);
+    for (int j = lane; j < P.n_train; j += nl) {
+        const T* xr = P.train_x + (size_t)j * d;
+        T sd[DMAX];
+        T r2 = T(0);
+#pragma unroll
+        for (int k = 0; k < DMAX; ++k) {
+            sd[k] = (k < d) ? (x[k] - __ldg(xr + k)) * ils[k] : T(0);
+            r2 = fma(sd[k], sd[k], r2);
+        }
+        T kap, gc;
+        kernel_profile<T>(P.kernel_id, r2, kap, gc);
+        const T vj = __ldg(vv + j);
+        kacc = fma(kap, vj, kacc);
+        const T gv = gc * vj;
+#pragma unroll
+        for (int k = 0; k < DMAX; ++k) kg[k] = fma(gv, sd[k], kg[k]);
+    }
+    y_part = fma(P.amplitude, kacc, acc);
+#pragma unroll
+    for (int k = 0; k < DMAX; ++k) g_part[k] = fma(P.amplitude * ils[k], kg[k], gacc[k]);
+}
+
+}  // namespace nmb

@@ -73,7 +73,7 @@ class _Kernel(nn.Module):
     def __init__(self, ard_num_dims=None, **kw):
         super().__init__()
         nd = 1 if ard_num_dims is None else ard_num_dims
-        self.register_buffer("_lengthscale", torch.full((1, nd), math.log(2.0)))
+        self.register_buffer("_lengthscale", torch.full((1, nd), math.log(2.0), dtype=torch.float64))
 
     @property
     def lengthscale(self):
@@ -106,7 +106,7 @@ class ScaleKernel(nn.Module):
     def __init__(self, base_kernel, **kw):
         super().__init__()
         self.base_kernel = base_kernel
-        self.register_buffer("_outputscale", torch.tensor(math.log(2.0)))
+        self.register_buffer("_outputscale", torch.tensor(math.log(2.0), dtype=torch.float64))
 
     @property
     def outputscale(self):
@@ -126,7 +126,7 @@ class GaussianLikelihood(nn.Module):
     def __init__(self, noise_prior=None, **kw):
         super().__init__()
         self.noise_prior = noise_prior
-        self.register_buffer("_noise", torch.tensor([math.log(2.0) + 1e-4]))
+        self.register_buffer("_noise", torch.tensor([math.log(2.0) + 1e-4], dtype=torch.float64))
 
     @property
     def noise(self):
@@ -140,7 +140,7 @@ class GaussianLikelihood(nn.Module):
 class ConstantMean(nn.Module):
     def __init__(self):
         super().__init__()
-        self.register_buffer("constant", torch.tensor(0.0))
+        self.register_buffer("constant", torch.tensor(0.0, dtype=torch.float64))
 
 
 class ExactMarginalLogLikelihood(nn.Module):
