@@ -80,6 +80,135 @@ int nmb_path_eval(const nmb_path_t* path, int dtype, const void* x, int64_t n_po
                   int64_t points_per_path, void* y, void* dydx, void* stream);
 
 /* ------------------------------------------------------------------------
+ * Amortized policy network (reference amortized_network.py:15-139, continuous branch):
+ *   Linear(d+1,H) ELU Linear(H,H) ELU -> GRUCell(H,H) -> cat -> Linear(2H,H) ELU
+ *   Linear(H,H) ELU Linear(H,d*n_a) -> sigmoid [-> random planar rotation about x]
+ * Parameters travel as ONE flat buffer in the reference's state_dict order
+ * (embedding.{weight,bias}, prepro.2.{weight,bias}, rnn.{weight_ih,weight_hh,bias_ih,
+ * bias_hh}, postpro_A.{0,3,6}.{weight,bias}, postpro_X.{0,3,6}.{weight,bias}), torch
+ * [out][in] layout ("theta"), plus a copy with every weight matrix transposed to
+ * [in][out] ("theta_t") that the forward GEMMs stream.  H <= 64, H % 4 == 0, n_a == 1.
+ * ---------------------------------------------------------------------- */
+int64_t nmb_policy_param_count(int d, int H, int n_actions);
+/* theta_t <- per-matrix transpose of theta (biases copied) */
+int nmb_policy_transpose(int dtype, int d, int H, int n_actions, const void* theta, void* theta_t, void* stream);
+
+/* spotlight cost (reference acqfs.py:583-633; presets main.py:219-237) */
+typedef struct nmb_cost {
+    double radius;             /* the host passes the float32-rounded radius, as the reference's buffer holds it */
+    double k, max_noise, p_norm, discount, discount_threshold;
+    double prev_cost;          /* cost already spent before this BO step (actor.py:482-486) */
+} nmb_cost_t;
+
+/* ------------------------------------------------------------------------
+ * Fused HES-TS-AM rollout: for every chain (restart x path) run L design steps and
+ * the action step  policy -> [rotation] -> Thompson path -> spotlight cost, i.e. the
+ * whole of qMultiStepHEntropySearch.forward with enable_ts and an amortized map
+ * (reference acqfs.py:277-456 with :361-362, :408-411; SURVEY App. C dataflow).
+ * ---------------------------------------------------------------------- */
+typedef struct nmb_ts_problem {
+    int32_t dtype, d, H, L;
+    int64_t n_chains;          /* N = restarts x paths */
+    int64_t chains_per_path;   /* chain i evaluates path i / chains_per_path */
+    const nmb_path_t* path;    /* host pointer */
+    nmb_cost_t cost;
+    const void* prev_x;        /* [N, d]  last observed design, expanded (actor.py:458-460) */
+    const void* prev_y;        /* [N]     */
+    const void* prev_h;        /* [N, H]  hidden state + hidden_noise (actor.py:472-481) */
+    uint64_t seed;             /* in-kernel RNG (used only where rot_q / cost_noise are NULL) */
+    const int64_t* step_ptr;   /* device counter mixed into the in-kernel RNG, may be NULL */
+    const int32_t* done_flag;  /* device flag: non-zero => kernels return immediately, may be NULL */
+} nmb_ts_problem_t;
+
+typedef struct nmb_ts_rollout {
+    const void* theta;         /* [n_params] torch layout (used by backward) */
+    const void* theta_t;       /* [n_params] transposed layout (used by forward) */
+    int32_t noisy_design;      /* enable_noise: rotate the design outputs (acqfs.py:320-326) */
+    int32_t noisy_action;      /* the action call always rotates in the reference (acqfs.py:390-395) */
+    const void* rot_q;         /* [L+1][N][4] host-built float32-rounded 2x2 blocks (amortized_network.py:144-153) or NULL */
+    const int32_t* rot_dims;   /* [L+1][N][2] coordinate pairs (amortized_network.py:156) */
+    const void* cost_noise;    /* [L+1][N] N(0,1) draws of the L+1 cost calls (acqfs.py:624) or NULL */
+    uint32_t rng_stream;
+    uint32_t _pad;
+    void* X;                   /* out [L][N][d]   design points x_1..x_L */
+    void* A;                   /* out [N][d]      action */
+    void* Y;                   /* out [L+1][N]    f(x_1..x_L), f(a) */
+    void* loss;                /* out [N]         -f(a)  (top-k loss, n_actions = 1) */
+    void* cost;                /* out [N]         accumulated spotlight cost */
+    void* save;                /* workspace for backward (nmb_ts_save_bytes) or NULL for a no-grad rollout */
+} nmb_ts_rollout_t;
+
+int64_t nmb_ts_save_bytes(int dtype, int d, int H, int L, int64_t n_chains);
+/* element offset of the hidden-state block HS[L+2][N][H] inside a save workspace */
+int64_t nmb_ts_save_hidden_offset(int d, int H, int L, int64_t n_chains);
+
+/* forward for n_rollouts (1 or 2) rollouts in ONE launch (grid.y = rollout) */
+int nmb_ts_rollout_fwd(const nmb_ts_problem_t* prob, const nmb_ts_rollout_t* rollouts, int n_rollouts, void* stream);
+
+/* backward of one saved rollout.  Seeds: g_loss[N], g_cost[N] (required), g_X [L][N][d],
+ * g_A [N][d] (optional extra adjoints of the returned points, e.g. the cosine term of
+ * actor.py:594-609).  Fills the pre-activation adjoints in `save` for nmb_policy_wgrad.
+ * g_prev (optional) receives [N][d+1+H] adjoints of (prev_x, prev_y, prev_h). */
+int nmb_ts_rollout_bwd(const nmb_ts_problem_t* prob, const nmb_ts_rollout_t* rollout, const void* g_loss,
+                       const void* g_cost, const void* g_X, const void* g_A, void* g_prev, void* stream);
+
+/* Weight gradients of a saved+back-propagated rollout: split-K GEMMs over all nodes.
+ * partials: [n_splits_max][n_params]; seg_splits[20] (host, out) = how many leading
+ * rows of `partials` hold data for each parameter segment.  Deterministic (no atomics). */
+int64_t nmb_policy_wgrad_max_splits(int L, int64_t n_chains);
+int nmb_policy_wgrad(const nmb_ts_problem_t* prob, const void* save, void* partials, int32_t* seg_splits_host,
+                     void* stream);
+/* grad[i] = sum_s partials[s][i] over the segment's split count */
+int nmb_policy_reduce_partials(int dtype, int d, int H, int n_actions, const void* partials,
+                               const int32_t* seg_splits_host, void* grad, void* stream);
+
+/* ------------------------------------------------------------------------
+ * Device-resident optimisation loop state (reference actor.py:489-662: AdamW loop, best-restart
+ * bookkeeping, early stop).  Lives in device memory so that one Adam iteration is a fixed
+ * sequence of launches (CUDA-graph capturable) with no host synchronisation.
+ * ---------------------------------------------------------------------- */
+typedef struct nmb_loop_state {
+    int64_t step;          /* iterations completed (ep) */
+    int32_t done;          /* loop has stopped (early stop): kernels become no-ops */
+    int32_t done_next;     /* set by the bookkeeping of this iteration, latched into done by the optimiser step */
+    int32_t stall;         /* early-stop counter (actor.py:636-639) */
+    int32_t improved;      /* this iteration took a snapshot (actor.py:623-636) */
+    int32_t chosen_idx;    /* argmin of this iteration's total loss */
+    int32_t n_snapshots;
+    double  best_min;      /* min over restarts of best_loss + best_cost + best_KL */
+    double  loss_mean, cost_mean;   /* acqf_loss.mean(), acqf_cost.mean() of the last iteration (actor.py:618-619) */
+} nmb_loop_state_t;
+
+/* Per-restart objective of one iteration + bookkeeping (one CTA):
+ *   KL[c]    = sum_l (1 - cos(X_orig[l][c], X[l][c])) + (1 - cos(A_orig[c], A[c]))   (actor.py:594-609; 0 if X_orig NULL)
+ *   total[c] = loss[c] + |budget - cost[c]| + KL[c]                                   (actor.py:620)
+ *   seeds of d mean_c(total) / d{loss, cost, X, A}  (the mean is over n_global restarts)
+ *   chosen = argmin total; snapshot decision and early-stop counter (actor.py:622-639).
+ * past_initial = (iteration > n_initial_points).  hist_loss/hist_cost [max_iter][N] optional. */
+int nmb_ts_objective(int dtype, int d, int L, int64_t n_chains, int64_t n_global, double budget, int past_initial,
+                     const void* loss, const void* cost, const void* X, const void* A, const void* X_orig,
+                     const void* A_orig, void* KL, void* total, void* g_loss, void* g_cost, void* g_X, void* g_A,
+                     const void* best_sum /* [N] best_loss+best_cost+best_KL, unused */, void* hist_loss,
+                     void* hist_cost, int64_t hist_capacity, nmb_loop_state_t* state, void* stream);
+
+/* if (state->improved) dst[i] <- src[i] for up to 8 (src, dst, n_elems) triples (snapshot, actor.py:624-635) */
+int nmb_snapshot_if_improved(int dtype, int n_copies, const void* const* src_host, void* const* dst_host,
+                             const int64_t* n_elems_host, const nmb_loop_state_t* state, void* stream);
+
+/* AdamW step (torch.optim.AdamW semantics, actor.py:489,646-648) on the flat parameter buffer with the
+ * split reduction of nmb_policy_wgrad fused in; also refreshes theta_t, latches done, advances step.
+ * seg_splits_host[s] == 0 => the segment received no gradient and is skipped, like a None grad.
+ * For free tensors use nmb_adamw_flat.  bias_corr: device [capacity][2] = (1-beta1^t, sqrt(1-beta2^t)), t = step+1. */
+typedef struct nmb_adamw {
+    double lr, beta1, beta2, eps, weight_decay;
+} nmb_adamw_t;
+int nmb_policy_adamw_step(int dtype, int d, int H, int n_actions, const nmb_adamw_t* hp, void* theta, void* theta_t,
+                          void* exp_avg, void* exp_avg_sq, const void* partials, const int32_t* seg_splits_host,
+                          nmb_loop_state_t* state, int advance_state, void* stream);
+int nmb_adamw_flat(int dtype, int64_t n, const nmb_adamw_t* hp, void* param, void* exp_avg, void* exp_avg_sq,
+                   const void* grad, nmb_loop_state_t* state, int advance_state, void* stream);
+
+/* ------------------------------------------------------------------------
  * FP64 / FP32 pipe micro-benchmarks used for the roofline denominators
  * (MEASURED_PEAKS.json has no FP64 entry).
  * which: 0 = dependent-chain-free FMA throughput, 1 = sincospi, 2 = exp.

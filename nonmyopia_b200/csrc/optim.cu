@@ -1,0 +1,320 @@
+// Optimiser-loop kernels: parameter transpose, per-restart objective + best-restart
+// bookkeeping, conditional snapshot, fused AdamW (reference actor.py:489-662).
+#include "policy_dev.cuh"
+
+namespace nmb {
+
+struct SegTab { int off[S_COUNT + 1]; int O[S_COUNT]; int K[S_COUNT]; int splits[S_COUNT]; };
+
+static SegTab make_segtab(int d, int H, int na, const int32_t* splits) {
+    PolicyLayout lay;
+    lay.init(d, H, na);
+    SegTab t;
+    for (int s = 0; s <= S_COUNT; ++s) t.off[s] = lay.off[s];
+    for (int s = 0; s < S_COUNT; ++s) { t.O[s] = lay.O[s]; t.K[s] = lay.K[s]; t.splits[s] = splits ? splits[s] : 1; }
+    return t;
+}
+
+// index of parameter i inside the transposed buffer
+__device__ __forceinline__ int transposed_index(const SegTab& tb, int i, int& seg) {
+    int s = 0;
+    while (s + 1 < S_COUNT && i >= tb.off[s + 1]) ++s;
+    seg = s;
+    if (tb.K[s] == 0) return i;
+    const int loc = i - tb.off[s];
+    const int o = loc / tb.K[s], k = loc - o * tb.K[s];
+    return tb.off[s] + k * tb.O[s] + o;
+}
+
+template <typename T>
+__global__ void transpose_kernel(SegTab tb, const T* __restrict__ theta, T* __restrict__ theta_t, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    int seg;
+    theta_t[transposed_index(tb, i, seg)] = theta[i];
+}
+
+// torch.optim.AdamW (single-tensor path): p *= 1 - lr*wd; m.lerp_(g, 1-b1); v = b2 v + (1-b2) g^2;
+// denom = sqrt(v)/sqrt(1-b2^t) + eps; p -= (lr/(1-b1^t)) * m/denom
+template <typename T>
+__global__ void adamw_kernel(SegTab tb, int use_tab, nmb_adamw_t hp, T* __restrict__ theta, T* __restrict__ theta_t,
+                             T* __restrict__ m, T* __restrict__ v, const T* __restrict__ partials, long long n,
+                             nmb_loop_state_t* state, int advance) {
+    const bool stopped = state && state->done;
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (!stopped && i < n) {
+        int seg = 0, ti = (int)i, nsp = 1;
+        if (use_tab) { ti = transposed_index(tb, (int)i, seg); nsp = tb.splits[seg]; }
+        if (nsp > 0) {
+            T g = T(0);
+            for (int q = 0; q < nsp; ++q) g += partials[(size_t)q * n + i];
+            const long long t = (state ? state->step : 0) + 1;
+            const double bc1 = 1.0 - ::pow(hp.beta1, (double)t);
+            const double bc2s = ::sqrt(1.0 - ::pow(hp.beta2, (double)t));
+            T p = theta[i] * (T)(1.0 - hp.lr * hp.weight_decay);
+            T mi = m[i], vi = v[i];
+            mi = mi + (g - mi) * (T)(1.0 - hp.beta1);
+            vi = vi * (T)hp.beta2 + (T)(1.0 - hp.beta2) * g * g;
+            const T denom = Num<T>::sqrt(vi) / (T)bc2s + (T)hp.eps;
+            p = p - (T)(hp.lr / bc1) * (mi / denom);
+            theta[i] = p; m[i] = mi; v[i] = vi;
+            if (theta_t) theta_t[ti] = p;
+        }
+    }
+    (void)advance;
+}
+
+// latch done / advance the step counter once all optimiser blocks have finished (separate tiny
+// kernel: no inter-block ordering assumptions inside adamw_kernel)
+__global__ void advance_state_kernel(nmb_loop_state_t* state) {
+    if (state->done) return;
+    state->step += 1;
+    state->done = state->done_next;
+}
+
+// ---- objective + bookkeeping: one CTA of 1024 threads
+template <typename T>
+__global__ void __launch_bounds__(1024) objective_kernel(int d, int L, long long N, long long n_global, T budget,
+                                                         int past_initial, const T* __restrict__ loss,
+                                                         const T* __restrict__ cost, const T* __restrict__ X,
+                                                         const T* __restrict__ A, const T* __restrict__ Xo,
+                                                         const T* __restrict__ Ao, T* __restrict__ KL,
+                                                         T* __restrict__ total, T* __restrict__ g_loss,
+                                                         T* __restrict__ g_cost, T* __restrict__ g_X,
+                                                         T* __restrict__ g_A, T* __restrict__ hist_loss,
+                                                         T* __restrict__ hist_cost, long long hist_cap,
+                                                         nmb_loop_state_t* state) {
+    if (state->done) return;
+    __shared__ double s_val[32];
+    __shared__ long long s_idx[32];
+    __shared__ double s_sum[2][32];
+    const int tid = threadIdx.x;
+    const T inv_n = T(1) / (T)n_global;
+    const T eps = T(1e-6);
+    double best = 1.0 / 0.0;
+    long long best_i = 0x7fffffffffffffffLL;
+    double sl = 0.0, sc = 0.0;
+    for (long long c = tid; c < N; c += blockDim.x) {
+        T kl = T(0);
+        for (int l = 0; l <= L; ++l) {
+            const T* xm = l < L ? X + ((size_t)l * N + c) * d : A + (size_t)c * d;
+            const T* xo = nullptr;
+            if (Xo) xo = l < L ? Xo + ((size_t)l * N + c) * d : Ao + (size_t)c * d;
+            T* gdst = l < L ? (g_X ? g_X + ((size_t)l * N + c) * d : nullptr) : (g_A ? g_A + (size_t)c * d : nullptr);
+            if (!xo) {
+                if (gdst) for (int k = 0; k < d; ++k) gdst[k] = T(0);
+                continue;
+            }
+            // F.cosine_similarity(dim=-1, eps=1e-6): x.y / (max(|x|, eps) * max(|y|, eps))
+            T dot = T(0), nm = T(0), no = T(0);
+            for (int k = 0; k < d; ++k) { dot = fma(xm[k], xo[k], dot); nm = fma(xm[k], xm[k], nm); no = fma(xo[k], xo[k], no); }
+            const T rm = Num<T>::sqrt(nm), rqo = Num<T>::sqrt(no);
+            const T cm = rm > eps ? rm : eps, co = rqo > eps ? rqo : eps;
+            const T cs = dot / (cm * co);
+            kl += T(1) - cs;
+            if (gdst) {
+                // d(1 - cos)/d xm = -( xo/(cm co) - cos * xm / cm^2 )   (norm clamp inactive: |xm| > eps)
+                for (int k = 0; k < d; ++k) {
+                    const T dcs = xo[k] / (cm * co) - (rm > eps ? cs * xm[k] / (cm * cm) : T(0));
+                    gdst[k] = -inv_n * dcs;
+                }
+            }
+        }
+        const T lc = loss[c], cc = cost[c];
+        const T gap = budget - cc;
+        const T tot = lc + Num<T>::fabs(gap) + kl;
+        if (KL) KL[c] = kl;
+        total[c] = tot;
+        g_loss[c] = inv_n;
+        g_cost[c] = gap > T(0) ? -inv_n : (gap < T(0) ? inv_n : T(0));
+        if (hist_loss && state->step < hist_cap) {
+            hist_loss[(size_t)state->step * N + c] = lc;
+            hist_cost[(size_t)state->step * N + c] = cc;
+        }
+        sl += (double)lc; sc += (double)cc;
+        if ((double)tot < best) { best = (double)tot; best_i = c; }   // strided ascending: first minimum kept
+    }
+    // block argmin (lowest index among equal minima, like torch.argmin)
+    for (int m = 16; m > 0; m >>= 1) {
+        const double ov = __shfl_xor_sync(0xffffffffu, best, m);
+        const long long oi = __shfl_xor_sync(0xffffffffu, best_i, m);
+        if (ov < best || (ov == best && oi < best_i)) { best = ov; best_i = oi; }
+        sl += __shfl_xor_sync(0xffffffffu, sl, m);
+        sc += __shfl_xor_sync(0xffffffffu, sc, m);
+    }
+    if ((tid & 31) == 0) { s_val[tid >> 5] = best; s_idx[tid >> 5] = best_i; s_sum[0][tid >> 5] = sl; s_sum[1][tid >> 5] = sc; }
+    __syncthreads();
+    if (tid == 0) {
+        const int nw = blockDim.x >> 5;
+        for (int w = 1; w < nw; ++w) {
+            if (s_val[w] < best || (s_val[w] == best && s_idx[w] < best_i)) { best = s_val[w]; best_i = s_idx[w]; }
+            sl += s_sum[0][w]; sc += s_sum[1][w];
+        }
+        state->chosen_idx = (int)best_i;
+        state->loss_mean = sl / (double)N;
+        state->cost_mean = sc / (double)N;
+        // actor.py:623: compare this iteration's best total (with |budget - cost|) with the min of
+        // best_loss + best_cost + best_KL (without) - reproduced literally.
+        // best_min is refreshed by nmb_snapshot bookkeeping below after the copy decision.
+        const bool improve = state->step == 0 || best < state->best_min;
+        state->improved = improve ? 1 : 0;
+        if (improve) {
+            state->stall = 0;
+            state->n_snapshots += 1;
+        } else if (past_initial || state->step >= 200) {
+            state->stall += 1;
+        }
+        state->done_next = state->stall > 50 ? 1 : 0;
+    }
+}
+
+// after the decision: best_min <- min_c(loss + cost + KL) of the snapshot just taken
+template <typename T>
+__global__ void __launch_bounds__(1024) best_min_kernel(long long N, const T* __restrict__ loss, const T* __restrict__ cost,
+                                                        const T* __restrict__ KL, nmb_loop_state_t* state) {
+    if (state->done || !state->improved) return;
+    __shared__ double s_val[32];
+    double best = 1.0 / 0.0;
+    for (long long c = threadIdx.x; c < N; c += blockDim.x) {
+        const double v = (double)(loss[c] + cost[c] + (KL ? KL[c] : T(0)));
+        best = v < best ? v : best;
+    }
+    for (int m = 16; m > 0; m >>= 1) { const double o = __shfl_xor_sync(0xffffffffu, best, m); best = o < best ? o : best; }
+    if ((threadIdx.x & 31) == 0) s_val[threadIdx.x >> 5] = best;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < (int)(blockDim.x >> 5); ++w) best = s_val[w] < best ? s_val[w] : best;
+        state->best_min = best;
+    }
+}
+
+struct CopyList { const void* src[8]; void* dst[8]; long long n[8]; int count; };
+
+template <typename T>
+__global__ void snapshot_kernel(CopyList cl, const nmb_loop_state_t* state) {
+    if (state->done || !state->improved) return;
+    for (int q = 0; q < cl.count; ++q) {
+        const T* s = (const T*)cl.src[q];
+        T* dptr = (T*)cl.dst[q];
+        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < cl.n[q];
+             i += (long long)gridDim.x * blockDim.x)
+            dptr[i] = s[i];
+    }
+}
+
+}  // namespace nmb
+
+using namespace nmb;
+
+extern "C" int nmb_policy_transpose(int dtype, int d, int H, int n_actions, const void* theta, void* theta_t,
+                                    void* stream) {
+    NMB_REQUIRE(theta && theta_t, NMB_EINVAL, "nmb_policy_transpose: null pointer");
+    SegTab tb = make_segtab(d, H, n_actions, nullptr);
+    const int n = tb.off[S_COUNT];
+    cudaStream_t st = (cudaStream_t)stream;
+    if (dtype == NMB_F64) transpose_kernel<double><<<(n + 255) / 256, 256, 0, st>>>(tb, (const double*)theta, (double*)theta_t, n);
+    else if (dtype == NMB_F32) transpose_kernel<float><<<(n + 255) / 256, 256, 0, st>>>(tb, (const float*)theta, (float*)theta_t, n);
+    else { set_error("nmb_policy_transpose: dtype %d", dtype); return NMB_EINVAL; }
+    NMB_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int nmb_ts_objective(int dtype, int d, int L, int64_t n_chains, int64_t n_global, double budget,
+                                int past_initial, const void* loss, const void* cost, const void* X, const void* A,
+                                const void* X_orig, const void* A_orig, void* KL, void* total, void* g_loss,
+                                void* g_cost, void* g_X, void* g_A, const void* best_sum, void* hist_loss,
+                                void* hist_cost, int64_t hist_capacity, nmb_loop_state_t* state, void* stream) {
+    (void)best_sum;
+    NMB_REQUIRE(loss && cost && A && total && g_loss && g_cost && state, NMB_EINVAL, "nmb_ts_objective: null argument");
+    NMB_REQUIRE((X_orig == nullptr) == (A_orig == nullptr), NMB_EINVAL, "nmb_ts_objective: X_orig/A_orig mismatch");
+    NMB_REQUIRE(L == 0 || X, NMB_EINVAL, "nmb_ts_objective: X is null");
+    cudaStream_t st = (cudaStream_t)stream;
+    if (dtype == NMB_F64) {
+        objective_kernel<double><<<1, 1024, 0, st>>>(d, L, n_chains, n_global, budget, past_initial, (const double*)loss,
+            (const double*)cost, (const double*)X, (const double*)A, (const double*)X_orig, (const double*)A_orig,
+            (double*)KL, (double*)total, (double*)g_loss, (double*)g_cost, (double*)g_X, (double*)g_A,
+            (double*)hist_loss, (double*)hist_cost, hist_capacity, state);
+    } else if (dtype == NMB_F32) {
+        objective_kernel<float><<<1, 1024, 0, st>>>(d, L, n_chains, n_global, (float)budget, past_initial, (const float*)loss,
+            (const float*)cost, (const float*)X, (const float*)A, (const float*)X_orig, (const float*)A_orig,
+            (float*)KL, (float*)total, (float*)g_loss, (float*)g_cost, (float*)g_X, (float*)g_A,
+            (float*)hist_loss, (float*)hist_cost, hist_capacity, state);
+    } else { set_error("nmb_ts_objective: dtype %d", dtype); return NMB_EINVAL; }
+    NMB_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int nmb_snapshot_if_improved(int dtype, int n_copies, const void* const* src_host, void* const* dst_host,
+                                        const int64_t* n_elems_host, const nmb_loop_state_t* state, void* stream) {
+    NMB_REQUIRE(n_copies >= 1 && n_copies <= 8 && src_host && dst_host && n_elems_host && state, NMB_EINVAL,
+                "nmb_snapshot_if_improved: bad arguments");
+    CopyList cl;
+    cl.count = n_copies;
+    long long mx = 0;
+    for (int i = 0; i < n_copies; ++i) {
+        cl.src[i] = src_host[i]; cl.dst[i] = dst_host[i]; cl.n[i] = n_elems_host[i];
+        mx = cl.n[i] > mx ? cl.n[i] : mx;
+    }
+    long long blocks = (mx + 255) / 256;
+    const long long cap = (long long)sm_count() * 8;
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (dtype == NMB_F64) snapshot_kernel<double><<<(unsigned)blocks, 256, 0, st>>>(cl, state);
+    else if (dtype == NMB_F32) snapshot_kernel<float><<<(unsigned)blocks, 256, 0, st>>>(cl, state);
+    else { set_error("nmb_snapshot_if_improved: dtype %d", dtype); return NMB_EINVAL; }
+    NMB_LAUNCH_CHECK();
+    // keep best_min in step with the snapshot: copies 0,1,2 are by convention loss, cost, KL
+    if (n_copies >= 2) {
+        const void* kl = n_copies >= 3 ? src_host[2] : nullptr;
+        if (dtype == NMB_F64)
+            best_min_kernel<double><<<1, 1024, 0, st>>>(n_elems_host[0], (const double*)src_host[0], (const double*)src_host[1],
+                                                        (const double*)kl, const_cast<nmb_loop_state_t*>(state));
+        else
+            best_min_kernel<float><<<1, 1024, 0, st>>>(n_elems_host[0], (const float*)src_host[0], (const float*)src_host[1],
+                                                       (const float*)kl, const_cast<nmb_loop_state_t*>(state));
+        NMB_LAUNCH_CHECK();
+    }
+    return 0;
+}
+
+template <typename T>
+static int launch_adamw(SegTab tb, int use_tab, const nmb_adamw_t* hp, void* theta, void* theta_t, void* m, void* v,
+                        const void* partials, long long n, nmb_loop_state_t* state, int advance, cudaStream_t st) {
+    adamw_kernel<T><<<(unsigned)((n + 255) / 256), 256, 0, st>>>(tb, use_tab, *hp, (T*)theta, (T*)theta_t, (T*)m, (T*)v,
+                                                                 (const T*)partials, n, state, 0);
+    NMB_LAUNCH_CHECK();
+    if (advance && state) {
+        advance_state_kernel<<<1, 1, 0, st>>>(state);
+        NMB_LAUNCH_CHECK();
+    }
+    return 0;
+}
+
+extern "C" int nmb_policy_adamw_step(int dtype, int d, int H, int n_actions, const nmb_adamw_t* hp, void* theta,
+                                     void* theta_t, void* exp_avg, void* exp_avg_sq, const void* partials,
+                                     const int32_t* seg_splits_host, nmb_loop_state_t* state, int advance_state,
+                                     void* stream) {
+    NMB_REQUIRE(hp && theta && exp_avg && exp_avg_sq && partials && seg_splits_host, NMB_EINVAL,
+                "nmb_policy_adamw_step: null argument");
+    SegTab tb = make_segtab(d, H, n_actions, seg_splits_host);
+    const long long n = tb.off[S_COUNT];
+    cudaStream_t st = (cudaStream_t)stream;
+    if (dtype == NMB_F64) return launch_adamw<double>(tb, 1, hp, theta, theta_t, exp_avg, exp_avg_sq, partials, n, state, advance_state, st);
+    if (dtype == NMB_F32) return launch_adamw<float>(tb, 1, hp, theta, theta_t, exp_avg, exp_avg_sq, partials, n, state, advance_state, st);
+    set_error("nmb_policy_adamw_step: dtype %d", dtype);
+    return NMB_EINVAL;
+}
+
+extern "C" int nmb_adamw_flat(int dtype, int64_t n, const nmb_adamw_t* hp, void* param, void* exp_avg, void* exp_avg_sq,
+                              const void* grad, nmb_loop_state_t* state, int advance_state, void* stream) {
+    NMB_REQUIRE(hp && param && exp_avg && exp_avg_sq && grad && n >= 0, NMB_EINVAL, "nmb_adamw_flat: bad argument");
+    if (n == 0) return 0;
+    SegTab tb;
+    memset(&tb, 0, sizeof(tb));
+    cudaStream_t st = (cudaStream_t)stream;
+    if (dtype == NMB_F64) return launch_adamw<double>(tb, 0, hp, param, nullptr, exp_avg, exp_avg_sq, grad, n, state, advance_state, st);
+    if (dtype == NMB_F32) return launch_adamw<float>(tb, 0, hp, param, nullptr, exp_avg, exp_avg_sq, grad, n, state, advance_state, st);
+    set_error("nmb_adamw_flat: dtype %d", dtype);
+    return NMB_EINVAL;
+}

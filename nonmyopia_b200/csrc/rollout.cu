@@ -1,0 +1,487 @@
+// Fused HES-TS-AM rollout, forward and backward (reference acqfs.py:277-456 with an
+// amortized map and enable_ts; SURVEY App. C "Fused TS-AM rollout dataflow").
+//
+// One CTA (256 threads) owns a tile of 32 chains and walks all L+1 policy steps:
+//   policy step (policy_dev.cuh)  ->  [planar rotation about the input point]
+//   -> Thompson-path value + gradient (path.cuh, 8 threads per chain)
+//   -> spotlight cost of the move  -> next step's input.
+// The backward kernel walks the same chain in reverse (BPTT through the GRU and through
+// f's input gradient) and leaves every layer's pre-activation adjoint in the save
+// workspace for the split-K weight-gradient kernel (wgrad.cu).
+#include "path.cuh"
+#include "policy_dev.cuh"
+
+namespace nmb {
+
+// ------------------------------------------------------------------ counter RNG (Philox4x32-10)
+__device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint2 k) {
+    const unsigned M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
+#pragma unroll
+    for (int i = 0; i < 10; ++i) {
+        const unsigned hi0 = __umulhi(M0, c.x), lo0 = M0 * c.x;
+        const unsigned hi1 = __umulhi(M1, c.z), lo1 = M1 * c.z;
+        c = make_uint4(hi1 ^ c.y ^ k.x, lo1, hi0 ^ c.w ^ k.y, lo0);
+        k.x += W0; k.y += W1;
+    }
+    return c;
+}
+
+template <typename T> struct CostDev {
+    T radius, k, max_noise, p_norm, discount, discount_threshold, prev_cost, disc_mult;
+};
+
+template <typename T> static CostDev<T> to_dev(const nmb_cost_t& c) {
+    CostDev<T> o;
+    o.radius = (T)c.radius; o.k = (T)c.k; o.max_noise = (T)c.max_noise; o.p_norm = (T)c.p_norm;
+    o.discount = (T)c.discount; o.discount_threshold = (T)c.discount_threshold; o.prev_cost = (T)c.prev_cost;
+    // the reference forms 1 - discount * mask in float32 (acqfs.py:626-631)
+    o.disc_mult = (T)(1.0f - (float)c.discount);
+    return o;
+}
+
+template <typename T> struct RolloutDev {
+    const T* theta;
+    const T* theta_t;
+    int noisy_design, noisy_action;
+    const T* rot_q;
+    const int* rot_dims;
+    const T* cost_noise;
+    unsigned rng_stream;
+    T *X, *A, *Y, *loss, *cost;
+    SaveAreas<T> sv;
+    int has_save;
+};
+
+template <typename T> struct ProblemDev {
+    int d, H, L;
+    long long N, cpp;
+    PathDev<T> path;
+    CostDev<T> cost;
+    PolicyLayout lay;
+    const T *prev_x, *prev_y, *prev_h;
+    unsigned long long seed;
+    const long long* step_ptr;
+    const int* done_flag;
+};
+
+// rotation block + coordinate pair of (call, chain): given tensors or in-kernel draws that
+// mimic the reference's float32 angle / float32 cos, sin (amortized_network.py:136,144-153)
+template <typename T>
+__device__ __forceinline__ void get_rotation(const RolloutDev<T>& ro, const ProblemDev<T>& pb, long long step, int call,
+                                             long long chain, T (&q)[4], int& di, int& dj) {
+    if (ro.rot_q) {
+        const T* p = ro.rot_q + ((size_t)call * pb.N + chain) * 4;
+        q[0] = p[0]; q[1] = p[1]; q[2] = p[2]; q[3] = p[3];
+        const int* dd = ro.rot_dims + ((size_t)call * pb.N + chain) * 2;
+        di = dd[0]; dj = dd[1];
+    } else {
+        const uint4 r = philox4x32_10(make_uint4((unsigned)chain, (unsigned)(chain >> 32), (unsigned)step,
+                                                 (ro.rng_stream << 8) | (unsigned)call),
+                                      make_uint2((unsigned)pb.seed, (unsigned)(pb.seed >> 32)));
+        const float u = (float)(r.x >> 8) * (1.0f / 16777216.0f);
+        const float th = u * 2.0f * 3.14159265358979323846f - 3.14159265358979323846f;
+        const float c = cosf(th), s = sinf(th);
+        q[0] = (T)c; q[1] = (T)(-s); q[2] = (T)s; q[3] = (T)c;
+        di = (int)(r.y % (unsigned)pb.d);
+        dj = pb.d > 1 ? (di + 1 + (int)(r.z % (unsigned)(pb.d - 1))) % pb.d : di;
+    }
+}
+
+template <typename T>
+__device__ __forceinline__ T get_cost_noise(const RolloutDev<T>& ro, const ProblemDev<T>& pb, long long step, int call,
+                                            long long chain) {
+    if (ro.cost_noise) return ro.cost_noise[(size_t)call * pb.N + chain];
+    const uint4 r = philox4x32_10(make_uint4((unsigned)chain, (unsigned)(chain >> 32), (unsigned)step,
+                                             0x80000000u | (ro.rng_stream << 8) | (unsigned)call),
+                                  make_uint2((unsigned)pb.seed, (unsigned)(pb.seed >> 32)));
+    const double u1 = ((double)r.x * 4294967296.0 + (double)r.y + 1.0) * (1.0 / 18446744073709551616.0);
+    const double u2 = ((double)r.z * 4294967296.0 + (double)r.w) * (1.0 / 18446744073709551616.0);
+    double sn, cs;
+    ::sincospi(2.0 * u2, &sn, &cs);
+    return (T)(::sqrt(-2.0 * ::log(u1)) * cs);
+}
+
+// distance of the move and its derivative direction (torch.cdist p-norm on 1x1 blocks)
+template <typename T, int DMAX>
+__device__ __forceinline__ T move_dist(const CostDev<T>& c, int d, const T (&cur)[DMAX], const T (&prev)[DMAX],
+                                       T (&dir)[DMAX]) {
+    T dist = T(0);
+    if (c.p_norm == T(2)) {
+#pragma unroll
+        for (int k = 0; k < DMAX; ++k) if (k < d) { const T df = cur[k] - prev[k]; dist = fma(df, df, dist); }
+        dist = Num<T>::sqrt(dist);
+#pragma unroll
+        for (int k = 0; k < DMAX; ++k) dir[k] = (k < d && dist > T(0)) ? (cur[k] - prev[k]) / dist : T(0);
+    } else if (c.p_norm == T(1)) {
+#pragma unroll
+        for (int k = 0; k < DMAX; ++k) {
+            const T df = k < d ? cur[k] - prev[k] : T(0);
+            dist += Num<T>::fabs(df);
+            dir[k] = df > T(0) ? T(1) : (df < T(0) ? T(-1) : T(0));
+        }
+    } else {
+        const double p = (double)c.p_norm;
+        double acc = 0.0;
+#pragma unroll
+        for (int k = 0; k < DMAX; ++k) if (k < d) acc += ::pow(::fabs((double)(cur[k] - prev[k])), p);
+        const double dd = ::pow(acc, 1.0 / p);
+        dist = (T)dd;
+#pragma unroll
+        for (int k = 0; k < DMAX; ++k) {
+            const double df = k < d ? (double)(cur[k] - prev[k]) : 0.0;
+            dir[k] = (k < d && dd > 0.0) ? (T)((df > 0 ? 1.0 : -1.0) * ::pow(::fabs(df) / dd, p - 1.0)) : T(0);
+        }
+    }
+    return dist;
+}
+
+extern __shared__ __align__(16) unsigned char nmb_smem_raw[];
+
+// ================================================================== forward
+template <typename T, int DMAX>
+__global__ void __launch_bounds__(kNT, 1) ts_rollout_fwd_kernel(ProblemDev<T> pb, RolloutDev<T> ro0, RolloutDev<T> ro1) {
+    if (pb.done_flag && *pb.done_flag) return;
+    const RolloutDev<T>& ro = blockIdx.y == 0 ? ro0 : ro1;
+    const int d = pb.d, H = pb.H, L = pb.L;
+    const long long N = pb.N;
+    const long long chain0 = (long long)blockIdx.x * kR;
+    const int nvalid = (int)min((long long)kR, N - chain0);
+    const int tid = threadIdx.x;
+    const long long step = pb.step_ptr ? *pb.step_ptr : 0;
+
+    T* smem = reinterpret_cast<T*>(nmb_smem_raw);
+    FwdSmem<T> sm;
+    sm.carve(smem, d, H);
+    T* cost_acc = sm.stage + 2 * kKC * kOB;     // [kR] running cost per chain
+
+    // ---- load the tile's inputs
+    for (int e = tid; e < (d + 1) * kR; e += kNT) {
+        const int k = e >> 5, r = e & 31;
+        T v = T(0);
+        if (r < nvalid) v = k < d ? pb.prev_x[(chain0 + r) * d + k] : pb.prev_y[chain0 + r];
+        sm.IN[k * kRS + r] = v;
+    }
+    for (int e = tid; e < H * kR; e += kNT) {
+        const int k = e >> 5, r = e & 31;
+        const T v = r < nvalid ? pb.prev_h[(chain0 + r) * H + k] : T(0);
+        sm.HB[k * kRS + r] = v;
+        if (ro.has_save && r < nvalid) ro.sv.HS[(chain0 + r) * H + k] = v;
+    }
+    if (tid < kR) cost_acc[tid] = T(0);
+    __syncthreads();
+
+    const SaveAreas<T>* sv = ro.has_save ? &ro.sv : nullptr;
+    for (int l = 0; l <= L; ++l) {
+        const bool head_a = (l == L);
+        const long long node0 = (long long)l * N + chain0;
+        T* hs_out = ro.has_save ? ro.sv.HS + ((size_t)(l + 1) * N + chain0) * H : nullptr;
+        policy_forward_tile<T>(pb.lay, ro.theta_t, head_a, sm, sv, node0, nvalid, hs_out);
+
+        // ---- output point, Thompson path, cost: 8 threads per chain
+        const int r = tid >> 3, lane = tid & 7;
+        const long long chain = chain0 + r;
+        const bool live = r < nvalid;
+        T xin[DMAX], pt[DMAX];
+#pragma unroll
+        for (int k = 0; k < DMAX; ++k) {
+            xin[k] = k < d ? sm.IN[k * kRS + r] : T(0);
+            pt[k] = k < d ? sm.OUT[k * kRS + r] : T(0);
+        }
+        const bool noisy = head_a ? ro.noisy_action : ro.noisy_design;
+        if (noisy && live) {
+            T q[4]; int di, dj;
+            get_rotation<T>(ro, pb, step, l, chain, q, di, dj);
+            T vi = T(0), vj = T(0);
+#pragma unroll
+            for (int k = 0; k < DMAX; ++k) { if (k == di) vi = pt[k] - xin[k]; if (k == dj) vj = pt[k] - xin[k]; }
+            const T ri = q[0] * vi + q[1] * vj, rj = q[2] * vi + q[3] * vj;
+#pragma unroll
+            for (int k = 0; k < DMAX; ++k) {
+                T v = pt[k] - xin[k];
+                if (k == di) v = ri;
+                if (k == dj) v = rj;     // randperm gives di != dj for d >= 2
+                if (k < d) pt[k] = v + xin[k];
+            }
+        }
+        T yp = T(0), gp[DMAX];
+#pragma unroll
+        for (int k = 0; k < DMAX; ++k) gp[k] = T(0);
+        if (live) path_partial<T, DMAX>(pb.path, pt, (int)(chain / pb.cpp), lane, 8, yp, gp);
+        yp = group_sum(yp, 8);
+#pragma unroll
+        for (int k = 0; k < DMAX; ++k) gp[k] = group_sum(gp[k], 8);
+        const T yv = yp + pb.path.mean_const;
+        __syncthreads();     // every thread has read sm.IN / sm.OUT of this step
+        if (live && lane == 0) {
+            // spotlight cost of the move x_l -> point (acqfs.py:426-441)
+            T dir[DMAX];
+            const T dist = move_dist<T, DMAX>(pb.cost, d, pt, xin, dir);
+            const T nz = get_cost_noise<T>(ro, pb, step, l, chain);
+            T h = pb.cost.k * (dist - pb.cost.radius);
+            h = (h > T(0) ? h : T(0)) + nz * pb.cost.max_noise;
+            T mult = T(1);
+            if (pb.cost.discount > T(0)) {
+                const T acc = cost_acc[r] + pb.cost.prev_cost;
+                if (acc + h > pb.cost.discount_threshold) mult = pb.cost.disc_mult;
+                h *= mult;
+            }
+            cost_acc[r] += h;
+            if (ro.has_save) {
+                ro.sv.CM[node0 + r] = mult;
+#pragma unroll
+                for (int k = 0; k < DMAX; ++k) if (k < d) ro.sv.DYDX[(node0 + r) * d + k] = gp[k];
+            }
+            T* dst = head_a ? ro.A + chain * d : ro.X + ((size_t)l * N + chain) * d;
+#pragma unroll
+            for (int k = 0; k < DMAX; ++k) if (k < d) dst[k] = pt[k];
+            if (ro.Y) ro.Y[(size_t)l * N + chain] = yv;
+            if (head_a) {
+                ro.loss[chain] = -yv;
+                ro.cost[chain] = cost_acc[r];
+            }
+            // next step's input
+#pragma unroll
+            for (int k = 0; k < DMAX; ++k) if (k < d) sm.IN[k * kRS + r] = pt[k];
+            sm.IN[d * kRS + r] = yv;
+        }
+        __syncthreads();
+    }
+}
+
+// ================================================================== backward
+template <typename T, int DMAX>
+__global__ void __launch_bounds__(kNT, 1) ts_rollout_bwd_kernel(ProblemDev<T> pb, RolloutDev<T> ro, const T* __restrict__ g_loss,
+                                                                const T* __restrict__ g_cost, const T* __restrict__ g_X,
+                                                                const T* __restrict__ g_A, T* __restrict__ g_prev) {
+    if (pb.done_flag && *pb.done_flag) return;
+    const int d = pb.d, H = pb.H, L = pb.L;
+    const long long N = pb.N;
+    const long long chain0 = (long long)blockIdx.x * kR;
+    const int nvalid = (int)min((long long)kR, N - chain0);
+    const int tid = threadIdx.x;
+    const long long step = pb.step_ptr ? *pb.step_ptr : 0;
+
+    T* smem = reinterpret_cast<T*>(nmb_smem_raw);
+    BwdSmem<T> sm;
+    sm.carve(smem, d, H);
+    T* carry = sm.stage + 2 * kKC * kOB;        // [(DMAX+1)][kR]: adjoint of (x_{l+1}, y_{l+1}) from the level above
+
+    for (int e = tid; e < H * kR; e += kNT) sm.GH[e] = T(0);
+    for (int e = tid; e < (DMAX + 1) * kR; e += kNT) carry[e] = T(0);
+    __syncthreads();
+
+    const SaveAreas<T>& sv = ro.sv;
+    for (int l = L; l >= 0; --l) {
+        const bool head_a = (l == L);
+        const long long node0 = (long long)l * N + chain0;
+        // ---- per-chain adjoint of the step's output point -> GO
+        if (tid < kR) {
+            const int r = tid;
+            if (r < nvalid) {
+                const long long chain = chain0 + r;
+                const size_t node = (size_t)(node0 + r);
+                T pt[DMAX], xin[DMAX], gout[DMAX];
+                const T* psrc = head_a ? ro.A + chain * d : ro.X + ((size_t)l * N + chain) * d;
+#pragma unroll
+                for (int k = 0; k < DMAX; ++k) {
+                    pt[k] = k < d ? psrc[k] : T(0);
+                    xin[k] = k < d ? sv.XY[node * (d + 1) + k] : T(0);
+                }
+                // adjoint of y at this point: -g_loss for the action, the next step's input adjoint otherwise
+                const T gy = head_a ? -g_loss[chain] : carry[DMAX * kR + r];
+#pragma unroll
+                for (int k = 0; k < DMAX; ++k) {
+                    T g = T(0);
+                    if (k < d) {
+                        g = carry[k * kR + r] + gy * sv.DYDX[node * d + k];
+                        if (head_a) { if (g_A) g += g_A[chain * d + k]; }
+                        else if (g_X) g += g_X[((size_t)l * N + chain) * d + k];
+                    }
+                    gout[k] = g;
+                }
+                // cost of the move x_l -> pt
+                T dir[DMAX];
+                const T dist = move_dist<T, DMAX>(pb.cost, d, pt, xin, dir);
+                const T hinge = pb.cost.k * (dist - pb.cost.radius);
+                const T gc = hinge > T(0) ? g_cost[chain] * pb.cost.k * sv.CM[node] : T(0);
+                T gprev[DMAX];
+#pragma unroll
+                for (int k = 0; k < DMAX; ++k) { gout[k] += gc * dir[k]; gprev[k] = -gc * dir[k]; }
+                // rotation: pt = x + M (o - x)  =>  go = M^T gout,  gx += gout - go
+                const bool noisy = head_a ? ro.noisy_action : ro.noisy_design;
+                T go[DMAX];
+#pragma unroll
+                for (int k = 0; k < DMAX; ++k) go[k] = gout[k];
+                if (noisy) {
+                    T q[4]; int di, dj;
+                    get_rotation<T>(ro, pb, step, l, chain, q, di, dj);
+                    T gi = T(0), gj = T(0);
+#pragma unroll
+                    for (int k = 0; k < DMAX; ++k) { if (k == di) gi = gout[k]; if (k == dj) gj = gout[k]; }
+                    const T ti = q[0] * gi + q[2] * gj, tj = q[1] * gi + q[3] * gj;
+#pragma unroll
+                    for (int k = 0; k < DMAX; ++k) {
+                        if (k == di) go[k] = ti;
+                        if (k == dj) go[k] = tj;
+                        gprev[k] += gout[k] - go[k];
+                    }
+                }
+#pragma unroll
+                for (int k = 0; k < DMAX; ++k) {
+                    if (k < d) sm.GO[k * kRS + r] = go[k];
+                    carry[k * kR + r] = gprev[k];     // completed below with the network's input adjoint
+                }
+            } else {
+                for (int k = 0; k < d; ++k) sm.GO[k * kRS + r] = T(0);
+            }
+        }
+        __syncthreads();
+        policy_backward_tile<T>(pb.lay, ro.theta, head_a, sm, sv, node0, node0, nvalid);
+        if (tid < kR) {
+            const int r = tid;
+#pragma unroll
+            for (int k = 0; k < DMAX; ++k) if (k < d) carry[k * kR + r] += sm.GXY[k * kRS + r];
+            carry[DMAX * kR + r] = sm.GXY[d * kRS + r];
+        }
+        __syncthreads();
+    }
+    if (g_prev) {
+        // adjoints of (prev_x, prev_y, prev_h)
+        const int w = d + 1 + H;
+        for (int e = tid; e < w * kR; e += kNT) {
+            const int k = e / kR, r = e % kR;
+            if (r < nvalid) {
+                T v;
+                if (k < d) v = carry[k * kR + r];
+                else if (k == d) v = carry[DMAX * kR + r];
+                else v = sm.GH[(k - d - 1) * kRS + r];
+                g_prev[(chain0 + r) * w + k] = v;
+            }
+        }
+    }
+}
+
+// ================================================================== host side
+template <typename T> static ProblemDev<T> make_problem(const nmb_ts_problem_t& p) {
+    ProblemDev<T> o;
+    o.d = p.d; o.H = p.H; o.L = p.L; o.N = p.n_chains; o.cpp = p.chains_per_path;
+    o.path = to_dev<T>(*p.path);
+    o.cost = to_dev<T>(p.cost);
+    o.lay.init(p.d, p.H, 1);
+    o.prev_x = (const T*)p.prev_x; o.prev_y = (const T*)p.prev_y; o.prev_h = (const T*)p.prev_h;
+    o.seed = p.seed; o.step_ptr = (const long long*)p.step_ptr; o.done_flag = p.done_flag;
+    return o;
+}
+
+template <typename T> static RolloutDev<T> make_rollout(const nmb_ts_problem_t& p, const nmb_ts_rollout_t& r) {
+    RolloutDev<T> o;
+    o.theta = (const T*)r.theta; o.theta_t = (const T*)r.theta_t;
+    o.noisy_design = r.noisy_design; o.noisy_action = r.noisy_action;
+    o.rot_q = (const T*)r.rot_q; o.rot_dims = r.rot_dims; o.cost_noise = (const T*)r.cost_noise;
+    o.rng_stream = r.rng_stream;
+    o.X = (T*)r.X; o.A = (T*)r.A; o.Y = (T*)r.Y; o.loss = (T*)r.loss; o.cost = (T*)r.cost;
+    o.has_save = r.save != nullptr;
+    if (r.save) o.sv = carve_save<T>(r.save, p.d, p.H, p.L, p.n_chains);
+    else memset(&o.sv, 0, sizeof(o.sv));
+    return o;
+}
+
+static int validate_problem(const nmb_ts_problem_t* p, const char* who) {
+    NMB_REQUIRE(p && p->path, NMB_EINVAL, "%s: null problem/path", who);
+    NMB_REQUIRE(p->dtype == NMB_F64 || p->dtype == NMB_F32, NMB_EINVAL, "%s: dtype %d", who, p->dtype);
+    NMB_REQUIRE(p->d >= 1 && p->d <= NMB_MAX_DIM, NMB_ELIMIT, "%s: d=%d outside [1,%d]", who, p->d, NMB_MAX_DIM);
+    NMB_REQUIRE(p->d == p->path->d, NMB_EINVAL, "%s: path dim %d != d %d", who, p->path->d, p->d);
+    NMB_REQUIRE(p->H >= 4 && p->H <= kMaxH && p->H % 4 == 0, NMB_ELIMIT, "%s: hidden_dim=%d must be a multiple of 4 in [4,%d]",
+                who, p->H, kMaxH);
+    NMB_REQUIRE(p->L >= 0 && p->L <= 62, NMB_ELIMIT, "%s: lookahead=%d outside [0,62]", who, p->L);
+    NMB_REQUIRE(p->n_chains >= 1 && p->chains_per_path >= 1, NMB_EINVAL, "%s: bad chain counts", who);
+    NMB_REQUIRE((p->n_chains + p->chains_per_path - 1) / p->chains_per_path <= p->path->n_paths, NMB_EINVAL,
+                "%s: %lld chains / %lld per path exceed %d paths", who, (long long)p->n_chains,
+                (long long)p->chains_per_path, p->path->n_paths);
+    NMB_REQUIRE(p->prev_x && p->prev_y && p->prev_h, NMB_EINVAL, "%s: null inputs", who);
+    return 0;
+}
+
+template <typename T, int DMAX>
+static int launch_fwd(const nmb_ts_problem_t* p, const nmb_ts_rollout_t* r, int n, cudaStream_t st) {
+    ProblemDev<T> pb = make_problem<T>(*p);
+    RolloutDev<T> r0 = make_rollout<T>(*p, r[0]);
+    RolloutDev<T> r1 = n > 1 ? make_rollout<T>(*p, r[1]) : r0;
+    const size_t smem = (FwdSmem<T>::elems(p->d, p->H) + kR) * sizeof(T);
+    auto kern = ts_rollout_fwd_kernel<T, DMAX>;
+    NMB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    dim3 grid((unsigned)((p->n_chains + kR - 1) / kR), (unsigned)n);
+    kern<<<grid, kNT, smem, st>>>(pb, r0, r1);
+    NMB_LAUNCH_CHECK();
+    return 0;
+}
+
+template <typename T, int DMAX>
+static int launch_bwd(const nmb_ts_problem_t* p, const nmb_ts_rollout_t* r, const void* gl, const void* gc,
+                      const void* gX, const void* gA, void* gprev, cudaStream_t st) {
+    ProblemDev<T> pb = make_problem<T>(*p);
+    RolloutDev<T> r0 = make_rollout<T>(*p, *r);
+    const size_t smem = (BwdSmem<T>::elems(p->d, p->H) + (DMAX + 1) * kR) * sizeof(T);
+    auto kern = ts_rollout_bwd_kernel<T, DMAX>;
+    NMB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    dim3 grid((unsigned)((p->n_chains + kR - 1) / kR));
+    kern<<<grid, kNT, smem, st>>>(pb, r0, (const T*)gl, (const T*)gc, (const T*)gX, (const T*)gA, (T*)gprev);
+    NMB_LAUNCH_CHECK();
+    return 0;
+}
+
+}  // namespace nmb
+
+using namespace nmb;
+
+extern "C" int64_t nmb_policy_param_count(int d, int H, int n_actions) {
+    PolicyLayout lay;
+    lay.init(d, H, n_actions);
+    return lay.total();
+}
+
+extern "C" int64_t nmb_ts_save_bytes(int dtype, int d, int H, int L, int64_t n_chains) {
+    return (int64_t)save_elems(d, H, L, n_chains) * (dtype == NMB_F64 ? 8 : 4);
+}
+
+extern "C" int64_t nmb_ts_save_hidden_offset(int d, int H, int L, int64_t n_chains) {
+    const size_t nodes = (size_t)(L + 1) * n_chains;
+    return (int64_t)(nodes * (d + 1) + nodes * H * 2);
+}
+
+#define NMB_DISPATCH_D(FN, T, d, ...)                   \
+    ((d) <= 2 ? FN<T, 2>(__VA_ARGS__)                   \
+     : (d) <= 4 ? FN<T, 4>(__VA_ARGS__)                 \
+     : (d) <= 8 ? FN<T, 8>(__VA_ARGS__)                 \
+                : FN<T, 16>(__VA_ARGS__))
+
+extern "C" int nmb_ts_rollout_fwd(const nmb_ts_problem_t* prob, const nmb_ts_rollout_t* rollouts, int n_rollouts,
+                                  void* stream) {
+    int rc = validate_problem(prob, "nmb_ts_rollout_fwd");
+    if (rc) return rc;
+    NMB_REQUIRE(rollouts && (n_rollouts == 1 || n_rollouts == 2), NMB_EINVAL, "nmb_ts_rollout_fwd: n_rollouts=%d",
+                n_rollouts);
+    for (int i = 0; i < n_rollouts; ++i) {
+        const nmb_ts_rollout_t& r = rollouts[i];
+        NMB_REQUIRE(r.theta_t && r.A && r.loss && r.cost && (prob->L == 0 || r.X), NMB_EINVAL,
+                    "nmb_ts_rollout_fwd: rollout %d has null theta_t/outputs", i);
+        NMB_REQUIRE((r.rot_q == nullptr) == (r.rot_dims == nullptr), NMB_EINVAL,
+                    "nmb_ts_rollout_fwd: rot_q and rot_dims must be given together");
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    if (prob->dtype == NMB_F64) return NMB_DISPATCH_D(launch_fwd, double, prob->d, prob, rollouts, n_rollouts, st);
+    return NMB_DISPATCH_D(launch_fwd, float, prob->d, prob, rollouts, n_rollouts, st);
+}
+
+extern "C" int nmb_ts_rollout_bwd(const nmb_ts_problem_t* prob, const nmb_ts_rollout_t* rollout, const void* g_loss,
+                                  const void* g_cost, const void* g_X, const void* g_A, void* g_prev, void* stream) {
+    int rc = validate_problem(prob, "nmb_ts_rollout_bwd");
+    if (rc) return rc;
+    NMB_REQUIRE(rollout && rollout->save && rollout->theta, NMB_EINVAL,
+                "nmb_ts_rollout_bwd: needs the saved rollout and theta");
+    NMB_REQUIRE(g_loss && g_cost, NMB_EINVAL, "nmb_ts_rollout_bwd: null seeds");
+    cudaStream_t st = (cudaStream_t)stream;
+    if (prob->dtype == NMB_F64)
+        return NMB_DISPATCH_D(launch_bwd, double, prob->d, prob, rollout, g_loss, g_cost, g_X, g_A, g_prev, st);
+    return NMB_DISPATCH_D(launch_bwd, float, prob->d, prob, rollout, g_loss, g_cost, g_X, g_A, g_prev, st);
+}
