@@ -1,0 +1,153 @@
+"""Device-resident AdamW loop for HES-TS-AM (reference actor.py:489-662).
+
+One Adam iteration is a fixed sequence of launches on one stream
+
+    rollout_fwd(main + frozen "original" rollout, one launch)
+    -> objective (KL, total, backward seeds, argmin, snapshot decision, early-stop counter)
+    -> snapshot_if_improved (+ best_min refresh)
+    -> rollout_bwd -> policy_wgrad -> adamw_step (+ state advance)
+
+with every piece of loop state (iteration counter, early-stop counter, best-restart
+snapshot, Adam moments) resident in HBM, so the sequence is captured once in a CUDA
+graph and replayed with no host synchronisation; the host only polls the ``done`` flag
+every few replays.  The reference synchronises four times per iteration
+(actor.py:580-581, 618-619).
+
+Random numbers.  The reference consumes the CPU generator inside every noisy policy call
+(per-sample ``randperm``) and the device generator inside every cost call.  ``draws=None``
+(default, fast) draws statistically identical numbers in-kernel (Philox keyed by seed,
+iteration, call, chain); passing per-iteration draw tensors reproduces a recorded stream
+bit for bit (parity tests) at the price of one eager launch sequence per iteration.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import List, Optional
+
+import torch
+from torch import Tensor
+
+from . import _lib
+from . import ts_engine as te
+
+
+class TSAMLoop:
+    def __init__(self, eng: te.TSRollout, theta0: Tensor, prev_x: Tensor, prev_y: Tensor, prev_h: Tensor, *,
+                 budget: float, lr: float, past_initial: bool, prev_cost: float = 0.0, n_global: Optional[int] = None,
+                 max_iter: int = 500, record_history: bool = False, betas=(0.9, 0.999), eps: float = 1e-8,
+                 weight_decay: float = 1e-2):
+        self.eng = eng
+        d, H, L, N = eng.d, eng.H, eng.L, eng.N
+        dt, dev = eng.dtype, eng.device
+        self.budget, self.past_initial, self.max_iter = float(budget), bool(past_initial), int(max_iter)
+        self.n_global = int(n_global) if n_global else N
+        self.hp = te.AdamWStruct(lr=lr, beta1=betas[0], beta2=betas[1], eps=eps, weight_decay=weight_decay)
+        # parameters: live copy, frozen "original maps" (actor.py:525-535), Adam moments
+        self.theta = theta0.detach().to(dev, dt).clone().contiguous()
+        self.theta_t = eng.transpose(self.theta)
+        self.theta0 = self.theta.clone()
+        self.theta0_t = self.theta_t.clone()
+        self.m = torch.zeros_like(self.theta)
+        self.v = torch.zeros_like(self.theta)
+        # device loop state
+        self.state = torch.zeros(C.sizeof(te.LoopState), dtype=torch.uint8, device=dev)
+        eng.step_ptr = self.state.data_ptr()            # offsetof(step) == 0
+        eng.done_ptr = self.state.data_ptr() + 8        # offsetof(done) == 8
+        self.prev = (prev_x.to(dev, dt).contiguous(), prev_y.reshape(-1).to(dev, dt).contiguous(),
+                     prev_h.to(dev, dt).contiguous())
+        self.prob = eng.problem(*self.prev, prev_cost=prev_cost)
+        self.main = te.RolloutBuffers(d, H, L, N, dt, dev, with_save=True)
+        self.orig = te.RolloutBuffers(d, H, L, N, dt, dev, with_save=False)
+        z = lambda *s: torch.zeros(*s, dtype=dt, device=dev)
+        self.KL, self.total = z(N), z(N)
+        self.g_loss, self.g_cost, self.g_X, self.g_A = z(N), z(N), z(max(L, 1), N, d), z(N, d)
+        self.best_loss, self.best_cost, self.best_KL = z(N), z(N), z(N)
+        self.best_X, self.best_A, self.best_HS = z(max(L, 1), N, d), z(N, d), z(L + 2, N, H)
+        self.hist_loss = z(self.max_iter, N) if record_history else None
+        self.hist_cost = z(self.max_iter, N) if record_history else None
+        srcs = [self.main.loss, self.main.cost, self.KL, self.main.X, self.main.A, self.main.HS]
+        dsts = [self.best_loss, self.best_cost, self.best_KL, self.best_X, self.best_A, self.best_HS]
+        self._src = (C.c_void_p * 6)(*[t.data_ptr() for t in srcs])
+        self._dst = (C.c_void_p * 6)(*[t.data_ptr() for t in dsts])
+        self._cnt = (C.c_int64 * 6)(*[t.numel() for t in srcs])
+        self.graph = None
+        self.n_launches_per_iter = 8
+
+    # ------------------------------------------------------------------ one iteration
+    def _iteration(self, draws=None) -> None:
+        eng, lib = self.eng, self.eng.lib
+        st = _lib.stream_ptr()
+        if draws is None:
+            rm = eng.rollout_struct(self.main, self.theta, self.theta_t, noisy_design=False, rng_stream=0)
+            ro = eng.rollout_struct(self.orig, self.theta0, self.theta0_t, noisy_design=True, rng_stream=1)
+        else:
+            mq, md, mn, oq, od, on = draws
+            rm = eng.rollout_struct(self.main, self.theta, self.theta_t, False, mq, md, mn, 0)
+            ro = eng.rollout_struct(self.orig, self.theta0, self.theta0_t, True, oq, od, on, 1)
+        eng.forward(self.prob, [rm, ro])
+        state_p = C.c_void_p(self.state.data_ptr())
+        _lib.check(lib.nmb_ts_objective(
+            eng.dt, eng.d, eng.L, C.c_int64(eng.N), C.c_int64(self.n_global), C.c_double(self.budget),
+            int(self.past_initial), _lib.ptr(self.main.loss), _lib.ptr(self.main.cost), _lib.ptr(self.main.X),
+            _lib.ptr(self.main.A), _lib.ptr(self.orig.X), _lib.ptr(self.orig.A), _lib.ptr(self.KL),
+            _lib.ptr(self.total), _lib.ptr(self.g_loss), _lib.ptr(self.g_cost), _lib.ptr(self.g_X),
+            _lib.ptr(self.g_A), None, _lib.ptr(self.hist_loss), _lib.ptr(self.hist_cost),
+            C.c_int64(self.max_iter), state_p, st), "nmb_ts_objective")
+        _lib.check(lib.nmb_snapshot_if_improved(eng.dt, 6, self._src, self._dst, self._cnt, state_p, st),
+                   "nmb_snapshot_if_improved")
+        eng.backward(self.prob, rm, self.g_loss, self.g_cost, self.g_X, self.g_A)
+        partials = eng.weight_grad_partials(self.prob, self.main)
+        _lib.check(lib.nmb_policy_adamw_step(eng.dt, eng.d, eng.H, 1, C.byref(self.hp), _lib.ptr(self.theta),
+                                             _lib.ptr(self.theta_t), _lib.ptr(self.m), _lib.ptr(self.v),
+                                             _lib.ptr(partials), eng.seg_splits, state_p, 1, st),
+                   "nmb_policy_adamw_step")
+
+    def read_state(self) -> te.LoopState:
+        raw = self.state.cpu().numpy().tobytes()
+        return te.LoopState.from_buffer_copy(raw)
+
+    def capture(self) -> None:
+        """Capture one iteration in a CUDA graph (after a dry pass that sets kernel attributes)."""
+        if self.graph is not None:
+            return
+        # dry pass: done = 1 makes every kernel return at once; restores done = 0 afterwards
+        self.state[8:12] = torch.tensor([1, 0, 0, 0], dtype=torch.uint8, device=self.state.device)
+        self._iteration()
+        torch.cuda.synchronize()
+        self.state.zero_()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            self._iteration()
+        self.graph = g
+
+    def run(self, n_iter: Optional[int] = None, draws_per_iter: Optional[List] = None, poll_every: int = 16,
+            use_graph: bool = True) -> te.LoopState:
+        n_iter = self.max_iter if n_iter is None else n_iter
+        if draws_per_iter is not None:
+            for ep in range(min(n_iter, len(draws_per_iter))):
+                self._iteration(draws_per_iter[ep])
+                if self.read_state().done:
+                    break
+            return self.read_state()
+        if use_graph:
+            self.capture()
+        ep = 0
+        while ep < n_iter:
+            k = min(poll_every, n_iter - ep)
+            for _ in range(k):
+                if use_graph:
+                    self.graph.replay()
+                else:
+                    self._iteration()
+            ep += k
+            if self.read_state().done:
+                break
+        return self.read_state()
+
+    # ------------------------------------------------------------------ results (actor.py:661-733)
+    def result(self):
+        tot = self.best_loss + self.best_cost + self.best_KL
+        idx = torch.argmin(tot)
+        return dict(idx=idx, best_loss=self.best_loss, best_cost=self.best_cost, best_KL=self.best_KL,
+                    next_X=self.best_X[0][idx].reshape(1, -1), actions=self.best_A[idx].reshape(1, -1),
+                    hidden_state=self.best_HS[1][idx:idx + 1], theta=self.theta)
