@@ -1,0 +1,413 @@
+#!/usr/bin/env python
+"""Headline benchmark: HES lookahead tree-node posterior evals/s (fwd+bwd) - BASELINE.json metric.
+
+Workload (BASELINE.json configs[1], SURVEY.md 8d cfg 2b): Ackley 2-D, 50 GP training points,
+HES-TS-AM with 3 lookahead steps, 64 restarts x 64 Thompson paths = 4096 chains per GPU, FP64,
+hidden size 64, euclidean spotlight cost.  One "step" = one AdamW iteration of the reference's
+``Actor.query`` loop (actor.py:558-656): rollout forward (+ the no-grad rollout with the frozen
+network), objective + best-restart bookkeeping, reverse rollout, weight gradients, AdamW.
+A node eval = one query point evaluated under the Thompson path, forward and backward:
+4096 chains x (3 design levels + 1 action) = 16,384 per step and GPU (the no-grad rollout's
+16,384 forward-only evals are NOT counted).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W]            # this repo's CUDA path
+    python bench.py --impl reference [--gpus N] ...                  # CPU oracle on the host cores
+
+Multi-GPU (torchrun, one rank per GPU): every rank owns 64 restarts x 64 paths (weak scaling); the
+policy gradient is all-reduced (SUM) and the snapshot decision all-reduced (MIN) over NCCL.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import math
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import torch
+
+ENV, N_TRAIN, D, H, L = "Ackley", 50, 2, 64, 3
+N_RESTARTS, N_PATHS = 64, 64
+METRIC = "hes_lookahead_node_posterior_evals_per_s_fwd_bwd"
+UNIT = "node evals/s"
+FP64_PEAK_FILE = os.path.join(ROOT, "profiles", "pipe_peaks_r01.json")
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=100)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--restarts", type=int, default=N_RESTARTS)
+    ap.add_argument("--paths", type=int, default=N_PATHS)
+    ap.add_argument("--lookahead", type=int, default=L)
+    return ap.parse_args()
+
+
+# ----------------------------------------------------------------------------- workload
+def cost_hypers():
+    return dict(radius=0.075, k=1.0, max_noise=1e-5, p_norm=2.0, discount=0.0, discount_threshold=-1.0)
+
+
+def host_workload(n_restarts, n_paths, rank=0):
+    """Host-side (CPU tensors) inputs of one rank: GP data + hypers, initial policy, previous point."""
+    from nonmyopia_b200.synthetic import make_problem
+    prob = make_problem(ENV, seed=2)
+    g = torch.Generator().manual_seed(1000 + rank)
+    hidden_noise = torch.randn(n_restarts, H, generator=g).to(torch.float64)
+    N = n_restarts * n_paths
+    prev_x = prob.train_X[-1:].expand(N, -1).contiguous()
+    prev_y = prob.train_Y[-1:].expand(N, -1).contiguous()
+    prev_h = hidden_noise.repeat(n_paths, 1).contiguous()          # chain = path * n_restarts + restart
+    return prob, prev_x, prev_y, prev_h
+
+
+def init_policy(d, hidden):
+    from nonmyopia_b200.amortized_network import AmortizedNetwork
+    torch.manual_seed(2)
+    return AmortizedNetwork(d + 1, d, hidden, 1, torch.tensor([[0.0, 1.0]] * d, dtype=torch.float64)).double()
+
+
+# ----------------------------------------------------------------------------- clocks
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index=0):
+        self.idx, self.rows, self.proc = gpu_index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "200", "-i", str(self.idx)], stdout=subprocess.PIPE, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        self.t.join(timeout=2)
+        sm = sorted(float(r[1]) for r in self.rows if len(r) >= 9 and r[1].replace(".", "").isdigit())
+        mx = [float(r[2]) for r in self.rows if len(r) >= 9 and r[2].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for r in self.rows if len(r) >= 9 for n, v in zip(names, r[5:9]) if v.lower() == "active"})
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(self.rows)}
+
+
+# ----------------------------------------------------------------------------- CPU oracle leg
+def cpu_oracle_rate(n_restarts, lookahead, target_s, threads):
+    """Time the CPU oracle (oracle/hes_oracle.py: plain-PyTorch restatement of the reference's
+    Actor.query loop - forward, no-grad forward, autograd backward, AdamW, bookkeeping) on a bounded
+    sample of the workload: ``n_restarts`` chains (the same chain count as one B200 step when called with
+    restarts x paths) of ONE Thompson path - the reference's path object holds a single sample, the
+    per-node arithmetic is identical - for as many Adam iterations as fit in ``target_s`` seconds."""
+    from oracle import gp_math, hes_oracle as ho
+    torch.set_num_threads(threads)
+    prob, prev_x, prev_y, prev_h = host_workload(n_restarts, 1)
+    ls = torch.full((1, D), prob.lengthscale, dtype=torch.float64)
+    gp = gp_math.DenseGP.fit_caches(prob.train_X, prob.train_Y, kind=prob.kernel, lengthscale=ls,
+                                    outputscale=prob.outputscale, noise=prob.noise, mean_const=prob.mean_const)
+    torch.manual_seed(2)
+    path = gp_math.draw_matheron_path(gp, prob.train_Y, 1)
+    net = init_policy(D, H)
+    spec = ho.HESSpec(lookahead, [1] * lookahead, 1, ho.CostSpec(**cost_hypers()), enable_ts=True)
+    budget = 2 * math.sqrt(D)
+
+    def run(n_iter):
+        P = {k: v.detach().clone() for k, v in net.state_dict().items()}
+        t0 = time.perf_counter()
+        ho.query_loop(spec, prev_x, prev_y, prev_h, P, budget=budget, lr=1e-3, n_iter=n_iter, past_initial=False,
+                      path=path)
+        return time.perf_counter() - t0
+
+    run(2)                                   # warm-up (thread pools, allocator)
+    t_cal = run(4) / 4
+    n_iter = int(max(4, min(190, target_s / max(t_cal, 1e-6))))      # < 200: the early-stop gate stays shut
+    dt = run(n_iter)
+    evals = n_restarts * (lookahead + 1) * n_iter
+    return dict(value=evals / dt, ms_per_step=dt / n_iter * 1e3, n_iter=n_iter, seconds=dt,
+                sample=f"{n_restarts} chains x {lookahead + 1} levels (one Thompson path), {n_iter} Adam iterations "
+                       f"({dt:.1f} s) of the same Ackley-2D HES-TS-AM-{lookahead} workload")
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the reference's CPU path for this metric.  BoTorch/GPyTorch are not installable
+    here (no network, absent from /opt/wheelhouse) and /root/reference does not exist on the GPU box, so the
+    arm times the oracle port - the reference's algorithm restated in plain PyTorch and pinned against the
+    reference's own files in the build container (oracle/make_golden.py) - on all host cores."""
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    per_step_s = 3.0
+    rates, ms = [], []
+    chains = args.restarts * args.paths
+    t_all = time.perf_counter()
+    for _ in range(args.steps):
+        r = cpu_oracle_rate(chains, args.lookahead, per_step_s, cores)
+        rates.append(r["value"])
+        ms.append(r["ms_per_step"])
+        if time.perf_counter() - t_all > 240:          # keep the whole arm within a few minutes
+            break
+    rates.sort()
+    value = rates[len(rates) // 2]
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": len(rates), "warmup": args.warmup, "ms_per_step": sorted(ms)[len(ms) // 2],
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": f"Ackley-2D HES-TS-AM-{args.lookahead}, n=50 GP points, H=64, FP64; each step = a "
+                               f"bounded sample ({chains} chains, ~{per_step_s:.0f} s of Adam iterations) of the "
+                               f"{args.restarts}x{args.paths}-chain workload, CPU oracle port on all host cores"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": r["sample"]},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ----------------------------------------------------------------------------- B200 arm
+def algorithmic_flops_per_node(d, hidden, n_train, n_freq):
+    """FP64 flops per node eval, FMA = 2, transcendental = 1: Thompson path fwd+bwd
+    (value and input gradient share one pass) + policy step fwd, bwd (dgrad) and weight gradient."""
+    M = 2 * n_freq
+    ts = 2 * M * d + 6 * M + 2 * n_train * (3 * d + 12)
+    net = 2 * (10 * hidden * hidden + (2 * d + 1) * hidden)
+    return ts, net
+
+
+def run_b200(args, rank, world, local_rank):
+    import ctypes as C
+    import torch.distributed as dist
+    from nonmyopia_b200 import _lib, ts_engine as te
+    from nonmyopia_b200.gp import SurrogateGP, draw_thompson_path
+    from nonmyopia_b200.ts_loop import TSAMLoop
+
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback exists)"
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    group = None
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+        group = dist.group.WORLD
+    n_r, S, Lk = args.restarts, args.paths, args.lookahead
+    N = n_r * S
+    prob, prev_x, prev_y, prev_h = host_workload(n_r, S, rank)
+    gp = SurrogateGP(prob.train_X, prob.train_Y, kernel=prob.kernel, lengthscale=torch.full((D,), prob.lengthscale),
+                     outputscale=prob.outputscale, noise=prob.noise, mean_const=prob.mean_const, device=dev)
+    torch.manual_seed(2)
+    path = draw_thompson_path(gp, S)
+    net = init_policy(D, H)
+    theta0 = net.flat_parameters().detach()
+    budget = 2 * math.sqrt(D)
+    eng = te.TSRollout(path, D, H, Lk, N, cost_hypers(), device=dev, chains_per_path=n_r, seed=12345 + rank)
+    loop = TSAMLoop(eng, theta0, prev_x, prev_y, prev_h, budget=budget, lr=1e-3, past_initial=False,
+                    n_global=N * world, max_iter=10**9, patience=-1, group=group)
+    stream = torch.cuda.Stream(device=dev)
+    nodes_per_step = N * (Lk + 1)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- value: device-resident loop, inputs already in HBM, one CUDA graph replay per step
+    with torch.cuda.stream(stream):
+        try:
+            loop.capture()
+            replay = loop.graph.replay
+            mode = "cuda-graph"
+        except Exception as e:                                  # NCCL capture unsupported: eager launches
+            if world == 1:
+                raise
+            loop.graph = None
+            replay = loop._iteration
+            mode = f"eager ({type(e).__name__})"
+        for _ in range(max(args.warmup, 3)):
+            replay()
+        barrier()
+        clocks = ClockSampler(local_rank)
+        if rank == 0:
+            clocks.start()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        e0.record(stream)
+        for _ in range(args.steps):
+            replay()
+        e1.record(stream)
+        barrier()
+        ms_total = e0.elapsed_time(e1)
+        # per-kernel timing of the same steps (eager launches, events on the launching stream)
+        kern = time_kernels(loop, stream, min(args.steps, 20)) if rank == 0 else {}
+        # ---- e2e: the public class API with HOST buffers, copies inside the timed region
+        e2e = run_e2e(args, gp, path, net, prev_x, prev_y, prev_h, budget, dev, stream, barrier)
+    clk = clocks.stop() if rank == 0 else None
+    t = torch.tensor([ms_total, e2e["ms_total"]], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_total, e2e_ms = float(t[0]), float(t[1])
+    st = loop.read_state()
+    assert st.step >= args.steps and not st.done, "timed steps did not run"
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    value = nodes_per_step * world * args.steps / (ms_total * 1e-3)
+    f_ts, f_net = algorithmic_flops_per_node(D, H, gp.n, path.W.shape[0])
+    # dominant kernel = largest share of the step
+    dom = max(kern, key=lambda k: kern[k]["ms"]) if kern else None
+    peaks = json.load(open(FP64_PEAK_FILE)) if os.path.isfile(FP64_PEAK_FILE) else {}
+    fp64_peak = peaks.get("f64_fma_flops", 36.4e12) / 1e12
+    roof = None
+    if dom:
+        flops = kern[dom]["flops"]
+        ach = flops / (kern[dom]["ms"] * 1e-3) / 1e12
+        roof = {"bound": "fp64", "kernel": dom, "achieved": ach, "peak": fp64_peak, "unit": "TFLOP/s",
+                "frac": ach / fp64_peak, "traffic": None,
+                "peak_source": "own-measured FP64 DFMA peak on this pool's B200 (profiles/pipe_peaks_r01.json); "
+                               "MEASURED_PEAKS.json has no FP64 entry",
+                "per_kernel_ms": {k: round(v["ms"], 4) for k, v in kern.items()}}
+    cpu = None
+    if not args.no_cpu_baseline:
+        cores = os.cpu_count() or 1
+        r = cpu_oracle_rate(N, Lk, 12.0, cores)
+        cpu = {"value": r["value"], "unit": UNIT, "cores": cores, "kind": "port", "sample": r["sample"]}
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+        "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f64", "data": "synthetic",
+        "config": {"workload": f"Ackley-2D HES-TS-AM-{Lk}: {n_r} restarts x {S} Thompson paths = {N} chains/GPU x "
+                               f"{Lk + 1} levels, n=50 GP points, M=1024 features, H=64, FP64 (BASELINE configs[1])",
+                   "step": "one AdamW iteration of Actor.query: 2 rollouts fwd, objective, snapshot, rollout bwd, "
+                           "weight gradients, AdamW", "launch_mode": mode,
+                   "l2": "no flush: the per-step working set (backward workspace "
+                         f"{loop.main.save.numel() * 8 / 1e6:.0f} MB + partials) exceeds the 126 MB L2",
+                   "nodes_per_step": nodes_per_step * world, "flops_per_node": {"thompson_path": f_ts, "policy_fwd": f_net,
+                                                                               "policy_fwd_bwd_wgrad": 3 * f_net}},
+        "roofline": roof, "cpu_baseline": cpu,
+        "e2e": {"value": nodes_per_step * world * e2e["steps"] / (e2e_ms * 1e-3), "unit": UNIT,
+                "h2d_bytes_per_step": e2e["h2d"], "d2h_bytes_per_step": e2e["d2h"], "ms_per_step": e2e_ms / e2e["steps"],
+                "api": "acqfs.qMultiStepHEntropySearch.forward x2 + torch.autograd.grad + AdamW (eager, per-step "
+                       "H2D of prev_X/prev_y/prev_hid_state from pinned memory, D2H of loss/cost)"},
+        "gpu_launches": loop.n_launches_per_iter * args.steps, "clocks": clk,
+    }
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def time_kernels(loop, stream, n_steps):
+    """Average device time of every kernel of the step, CUDA events on the launching stream (eager
+    launches of the same sequence the graph replays) + the algorithmic FP64 flops of each."""
+    eng = loop.eng
+    names, evs = [], []
+
+    def mark(name):
+        e = torch.cuda.Event(enable_timing=True)
+        e.record(stream)
+        names.append(name)
+        evs.append(e)
+
+    for _ in range(3):
+        loop._iteration()
+    torch.cuda.synchronize()
+    for _ in range(n_steps):
+        mark("start")
+        loop._iteration(mark=mark)
+    torch.cuda.synchronize()
+    acc = {}
+    for i in range(1, len(evs)):
+        if names[i] == "start":
+            continue
+        acc.setdefault(names[i], []).append(evs[i - 1].elapsed_time(evs[i]))
+    nodes = eng.N * (eng.L + 1)
+    f_ts, f_net = algorithmic_flops_per_node(eng.d, eng.H, eng.path.train_X.shape[0], eng.path.W.shape[0])
+    flops = {"ts_rollout_fwd": nodes * (2 * f_net + 1.5 * f_ts), "ts_rollout_bwd": nodes * f_net,
+             "policy_wgrad": nodes * f_net, "objective+snapshot": 0.0, "adamw": 0.0}
+    return {k: {"ms": sum(v) / len(v), "flops": flops.get(k, 0.0)} for k, v in acc.items()}
+
+
+def run_e2e(args, gp, path, net, prev_x, prev_y, prev_h, budget, dev, stream, barrier):
+    """Same step through the public class API, host buffers in, host results out."""
+    import copy
+    from nonmyopia_b200 import acqfs
+    Lk = args.lookahead
+    acqf = acqfs.qMultiStepHEntropySearch(
+        model=gp, loss_function_class=acqfs.qLossFunctionTopK, loss_func_hypers=dict(dist_weight=1, dist_threshold=0.5),
+        cost_function_class=acqfs.qCostFunction, cost_func_hypers=cost_hypers(), lookahead_steps=Lk, n_actions=1,
+        n_fantasy_at_design_pts=[1] * Lk, n_fantasy_at_action_pts=64, enable_ts=True)
+    acqf.dump_model(f=path)
+    maps = copy.deepcopy(net).to(dev)
+    frozen = copy.deepcopy(net).to(dev)
+    params = list(maps.parameters())
+    opt = torch.optim.AdamW(params, lr=1e-3)
+    hx, hy, hh = prev_x.pin_memory(), prev_y.pin_memory(), prev_h.pin_memory()
+    N = hx.shape[0]
+    out_host = torch.empty(2, N, dtype=torch.float64).pin_memory()
+    cos = torch.nn.CosineSimilarity(dim=-1, eps=1e-6)
+
+    def step():
+        x = hx.to(dev, non_blocking=True)
+        y = hy.to(dev, non_blocking=True)
+        h = hh.to(dev, non_blocking=True)
+        rd = acqf.forward(prev_X=x, prev_y=y, prev_hid_state=h, maps=maps, prev_cost=0.0, enable_noise=False)
+        with torch.no_grad():
+            od = acqf.forward(prev_X=x, prev_y=y, prev_hid_state=h, maps=frozen, prev_cost=0.0)
+        KL = 0
+        for s in range(Lk):
+            KL = KL + 1 - cos(od["X"][s], rd["X"][s]).flatten()
+        KL = KL + 1 - cos(od["actions"], rd["actions"]).flatten()
+        loss = rd["acqf_loss"] + abs(budget - rd["acqf_cost"]) + KL
+        grads = torch.autograd.grad(loss.mean(), params, allow_unused=True)
+        for p_, g_ in zip(params, grads):
+            p_.grad = g_
+        opt.step()
+        opt.zero_grad()
+        out_host[0].copy_(rd["acqf_loss"].detach(), non_blocking=True)
+        out_host[1].copy_(rd["acqf_cost"].detach(), non_blocking=True)
+        stream.synchronize()                    # the reference reads loss / cost on the host every iteration
+
+    steps = max(5, min(args.steps, 50))
+    for _ in range(3):
+        step()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(steps):
+        step()
+    e1.record(stream)
+    barrier()
+    h2d = (hx.numel() + hy.numel() + hh.numel()) * 8
+    return dict(ms_total=e0.elapsed_time(e1), steps=steps, h2d=h2d, d2h=out_host.numel() * 8)
+
+
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    local_rank = int(os.environ.get("LOCAL_RANK", 0))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+    else:
+        run_b200(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

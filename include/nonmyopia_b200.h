@@ -80,6 +80,15 @@ int nmb_path_eval(const nmb_path_t* path, int dtype, const void* x, int64_t n_po
                   int64_t points_per_path, void* y, void* dydx, void* stream);
 
 /* ------------------------------------------------------------------------
+ * Dense kernel matrix  K[i][j] = amplitude * kappa(x1_i, x2_j) (+ diag_add where i == j),
+ * x1 [n1][d], x2 [n2][d], K [n1][ldk].  Replaces the GPyTorch kernel evaluations behind
+ * SingleTaskGP(...).posterior and draw_matheron_paths (reference main.py:479-484,
+ * acqfs.py:264,366,414).  diag_add = noise builds K + sigma^2 I.
+ * ---------------------------------------------------------------------- */
+int nmb_kernel_matrix(int dtype, int kernel_id, int d, const void* x1, int64_t n1, const void* x2, int64_t n2,
+                      const void* inv_ls, double amplitude, double diag_add, void* K, int64_t ldk, void* stream);
+
+/* ------------------------------------------------------------------------
  * Amortized policy network (reference amortized_network.py:15-139, continuous branch):
  *   Linear(d+1,H) ELU Linear(H,H) ELU -> GRUCell(H,H) -> cat -> Linear(2H,H) ELU
  *   Linear(H,H) ELU Linear(H,d*n_a) -> sigmoid [-> random planar rotation about x]
@@ -99,6 +108,25 @@ typedef struct nmb_cost {
     double k, max_noise, p_norm, discount, discount_threshold;
     double prev_cost;          /* cost already spent before this BO step (actor.py:482-486) */
 } nmb_cost_t;
+
+/* ------------------------------------------------------------------------
+ * Accumulated spotlight cost along every root-to-leaf chain of a lookahead tree: the L + n_a
+ * qCostFunction calls of reference acqfs.py:421-441 (free-parameter HES-TS, HES-MC and the
+ * baselines; the amortized rollout has the same arithmetic fused in).
+ * Level s holds counts[s] = n_r * prod(nf[:s]) points, restart index fastest (the reference's
+ * [*nf_rev[:s], n_r, 1, d] flattened), stored back to back in `pts`; node i of level s has
+ * parent i % counts[s-1]; level-0 node i moves away from root[i % n_root].
+ *   fwd: acc[leaf] = sum over the chain of  mult * (max(k (|move|_p - r), 0) + noise * max_noise);
+ *        noise [sum counts] (one N(0,1) draw per node, NULL = 0), mult [sum counts] (out, saved).
+ *   bwd: g_pts [sum counts][d], g_root [n_root][d] (optional) from g_acc [counts[n_levels-1]];
+ *        deterministic (no atomics).
+ * ---------------------------------------------------------------------- */
+int nmb_tree_cost_fwd(int dtype, int d, int n_levels, const int64_t* counts_host, const nmb_cost_t* cost,
+                      const void* root, int64_t n_root, const void* pts, const void* noise, void* acc, void* mult,
+                      void* stream);
+int nmb_tree_cost_bwd(int dtype, int d, int n_levels, const int64_t* counts_host, const nmb_cost_t* cost,
+                      const void* root, int64_t n_root, const void* pts, const void* mult, const void* g_acc,
+                      void* g_pts, void* g_root, void* stream);
 
 /* ------------------------------------------------------------------------
  * Fused HES-TS-AM rollout: for every chain (restart x path) run L design steps and
@@ -177,6 +205,8 @@ typedef struct nmb_loop_state {
     int32_t n_snapshots;
     double  best_min;      /* min over restarts of best_loss + best_cost + best_KL */
     double  loss_mean, cost_mean;   /* acqf_loss.mean(), acqf_cost.mean() of the last iteration (actor.py:618-619) */
+    double  cand_total;    /* this iteration's min over restarts of the total loss (offset 56) */
+    double  cand_lck;      /* this iteration's min over restarts of loss + cost + KL (offset 64) */
 } nmb_loop_state_t;
 
 /* Per-restart objective of one iteration + bookkeeping (one CTA):
@@ -184,12 +214,18 @@ typedef struct nmb_loop_state {
  *   total[c] = loss[c] + |budget - cost[c]| + KL[c]                                   (actor.py:620)
  *   seeds of d mean_c(total) / d{loss, cost, X, A}  (the mean is over n_global restarts)
  *   chosen = argmin total; snapshot decision and early-stop counter (actor.py:622-639).
- * past_initial = (iteration > n_initial_points).  hist_loss/hist_cost [max_iter][N] optional. */
+ * past_initial = (iteration > n_initial_points).  patience = early-stop threshold (reference: 50,
+ * actor.py:655; < 0 disables early stopping).  hist_loss/hist_cost [max_iter][N] and hist_X optional
+ * (the per-iteration records of actor.py:561-564,580-581). */
 int nmb_ts_objective(int dtype, int d, int L, int64_t n_chains, int64_t n_global, double budget, int past_initial,
-                     const void* loss, const void* cost, const void* X, const void* A, const void* X_orig,
-                     const void* A_orig, void* KL, void* total, void* g_loss, void* g_cost, void* g_X, void* g_A,
-                     const void* best_sum /* [N] best_loss+best_cost+best_KL, unused */, void* hist_loss,
-                     void* hist_cost, int64_t hist_capacity, nmb_loop_state_t* state, void* stream);
+                     int patience, const void* loss, const void* cost, const void* X, const void* A,
+                     const void* X_orig, const void* A_orig, void* KL, void* total, void* g_loss, void* g_cost,
+                     void* g_X, void* g_A, void* hist_loss, void* hist_cost, void* hist_X /* [max_iter][L][N][d] */,
+                     int64_t hist_capacity, int defer_decision, nmb_loop_state_t* state, void* stream);
+/* The snapshot / early-stop decision of actor.py:622-639 from state->cand_total / cand_lck.  With restarts
+ * sharded over ranks: nmb_ts_objective(defer_decision = 1), all-reduce(MIN) the two candidates in place
+ * (16 bytes at offset 56 of the state), then this. */
+int nmb_loop_decide(nmb_loop_state_t* state, int past_initial, int patience, void* stream);
 
 /* if (state->improved) dst[i] <- src[i] for up to 8 (src, dst, n_elems) triples (snapshot, actor.py:624-635) */
 int nmb_snapshot_if_improved(int dtype, int n_copies, const void* const* src_host, void* const* dst_host,

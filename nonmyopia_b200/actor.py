@@ -1,0 +1,369 @@
+"""Actor - host-side mirror of the reference's ``synthetic_experiment/actor.py``:
+``Actor(parms)``, ``construct_acqf``, ``reset_parameters``, ``query`` with the same arguments
+and the same return dictionary.
+
+``query`` (reference actor.py:439-734) runs the AdamW loop over the acquisition objective:
+
+* HES-TS-AM: the device-resident loop of ``ts_loop.TSAMLoop`` - one CUDA graph per Adam
+  iteration (two rollouts in one launch, objective + best-restart bookkeeping, snapshot,
+  reverse rollout, split-K weight gradients, fused AdamW), no host synchronisation except a
+  poll of the early-stop flag every ``poll_every`` iterations;
+* every other algorithm (free-parameter HES-TS, HES-MC, qEI/qPI/qSR/qUCB/qKG): the same loop
+  in eager form over ``acqf.forward`` (custom autograd nodes around the kernels) with the
+  fused ``nmb_adamw_flat`` optimiser step.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import gc
+import math
+import os
+import pickle
+import random
+from typing import List, Optional
+
+import torch
+from torch import Tensor
+
+from . import _lib
+from . import ts_engine as te
+from .acqfs import SobolQMCNormalSampler, qBOAcqf, qMultiStepHEntropySearch
+from .amortized_network import AmortizedNetwork
+from .ts_loop import TSAMLoop
+
+
+# ---- helpers restated from the reference's utils.py:313-365 (host-side random initialisation)
+def generate_random_points_batch(inputs: Tensor, radius: float, n: int) -> Tensor:
+    """``n`` uniform points in the radius-ball around every input point; new leading dim ``n``.
+    float32 host draws cast to the input dtype, like the reference."""
+    batch, dim = inputs.shape[:-1], inputs.shape[-1]
+    direction = torch.randn(n, *batch, dim).to(inputs)
+    direction = direction / torch.norm(direction, dim=-1, keepdim=True)
+    r = torch.rand(n, *batch).pow(1 / dim).unsqueeze(-1).to(inputs) * radius
+    return inputs.unsqueeze(0).expand(n, *batch, dim) + r * direction
+
+
+def generate_random_rotation_matrix(D: int) -> Tensor:
+    Q, _ = torch.linalg.qr(torch.randn(D, D))
+    if torch.det(Q) < 0:
+        Q[:, random.randint(0, D - 1)] *= -1
+    return Q
+
+
+def rotate_points(inputs: Tensor, R: Tensor, p: Tensor) -> Tensor:
+    return torch.matmul(inputs - p, R.transpose(-1, -2).to(inputs)) + p
+
+
+def fantasy_widths(parms, lookahead: int) -> List[int]:
+    """reference actor.py:89-104 (duplicated at :399-414)."""
+    if parms.algo_ts:
+        return [1] * lookahead
+    if "MSL" in parms.algo:
+        return [32, 2, 1, 1][:lookahead]
+    table = {0: [], 1: [64], 2: [64, 8], 3: [64, 4, 2]}
+    return table[lookahead] if lookahead in table else [64, 4, 2, 1] + [1] * (lookahead - 4)
+
+
+def _logit(x: Tensor) -> Tensor:
+    return -torch.log(1 / x - 1)
+
+
+class Actor:
+    def __init__(self, parms):
+        self.parms = parms
+        if parms.algo == "HES":
+            self.acqf_class = qMultiStepHEntropySearch
+            if parms.amortized:
+                self.maps = AmortizedNetwork(
+                    input_dim=parms.x_dim + parms.y_dim, output_dim=parms.x_dim, hidden_dim=parms.hidden_dim,
+                    n_actions=parms.n_actions, output_bounds=parms.bounds, discrete=parms.env_discretized,
+                    num_categories=parms.num_categories).to(dtype=parms.torch_dtype, device=parms.device)
+                print("Number of AmortizedNet params:",
+                      sum(p.numel() for p in self.maps.parameters() if p.requires_grad))
+                self._parameters = list(self.maps.parameters())
+            else:
+                self.maps = []
+        else:
+            self.acqf_class = qBOAcqf
+            self.maps = []
+        self.algo_lookahead_steps = parms.algo_lookahead_steps
+        self.acqf = None
+        # "device" (default): rotation angles / cost noise drawn in-kernel, CUDA-graph loop;
+        # "host": drawn by the host generators in the reference's order (seed-stream parity)
+        self.rng_mode = getattr(parms, "rng_mode", "device")
+
+    # ------------------------------------------------------------------ construct_acqf
+    def construct_acqf(self, surr_model, buffer, **kwargs):
+        """reference actor.py:382-437."""
+        self.acqf = None
+        gc.collect()
+        p = self.parms
+        nf = fantasy_widths(p, self.algo_lookahead_steps)
+        sampler = SobolQMCNormalSampler(sample_shape=p.n_samples, seed=0, resample=False) if p.algo != "HES" else None
+        self.acqf = self.acqf_class(
+            name=p.algo, model=surr_model, lookahead_steps=self.algo_lookahead_steps, n_actions=p.n_actions,
+            n_fantasy_at_design_pts=nf, n_fantasy_at_action_pts=p.n_samples,
+            loss_function_class=p.loss_function_class, loss_func_hypers=p.loss_func_hypers,
+            cost_function_class=p.cost_function_class, cost_func_hypers=p.cost_func_hypers,
+            enable_ts=p.algo_ts, sampler=sampler, best_f=buffer["y"].max(), rng_mode=self.rng_mode)
+
+    # ------------------------------------------------------------------ reset_parameters
+    def _random_tree(self, prev_point: Tensor, nf: List[int], n_first: int) -> List[Tensor]:
+        """Random designs level by level, each in the radius-ball of its parent
+        (reference actor.py:116-160 / 226-293).  Returns L+1 host tensors [cnt_s, d]."""
+        p = self.parms
+        L, r = self.algo_lookahead_steps, p.cost_func_hypers["radius"]
+        out: List[Tensor] = []
+        for s in range(L + 1):
+            parent = prev_point if s == 0 else out[-1]
+            if s == 0:
+                n = n_first if L > 0 else n_first * p.n_actions
+            elif s < L:
+                n = nf[s - 1]
+            else:
+                n = nf[-1] * p.n_actions
+            out.append(generate_random_points_batch(parent, r, n))
+        return out
+
+    def reset_parameters(self, buffer, bo_iter=0, embedder=None, prev_chosen_idx=0):
+        """reference actor.py:66-380.  Amortized: imitation pre-training of the network on
+        random ball designs (<= 300 AdamW epochs); otherwise random (or rotated previous-best)
+        designs stored as logits."""
+        if embedder is not None:
+            raise NotImplementedError("discrete environments are outside the B200 hot-path scope")
+        print("Resetting actor parameters...")
+        p = self.parms
+        L, d = self.algo_lookahead_steps, p.x_dim
+        prev_X = buffer["x"][-1:].expand(p.n_restarts, -1)
+        prev_y = buffer["y"][-1:].expand(p.n_restarts, -1)
+        nf = fantasy_widths(p, L)
+        dev, dt = p.device, p.torch_dtype
+        if p.amortized:
+            self._pretrain(buffer, prev_X, prev_y, nf)
+            return
+        if bo_iter == 0 or not p.algo_ts:
+            tree = self._random_tree(prev_X[0], nf, p.n_restarts)
+            self.maps = [_logit(torch.clamp(x.reshape(-1, d).to(device=dev, dtype=dt), min=0.01, max=0.99))
+                         .requires_grad_(True) for x in tree]
+        else:
+            # warm start: rotate the previous best trajectory about its first point (actor.py:294-379)
+            maps = [torch.sigmoid(x.detach()) for x in self.maps]
+            idx = prev_chosen_idx.long() if torch.is_tensor(prev_chosen_idx) else int(prev_chosen_idx)
+            R = [torch.eye(d).to(prev_X)] + [generate_random_rotation_matrix(d).to(prev_X)
+                                             for _ in range(p.n_restarts - 1)]
+            R = torch.stack(R, dim=0)
+            maps[0][:] = maps[1][idx]
+            for lah in range(2, L + 1):
+                pts = maps[lah].reshape(*nf[:lah], p.n_restarts, d)[..., idx, :]
+                rot = rotate_points(pts.reshape(-1, d), R, maps[0][idx]).transpose(0, 1)
+                maps[lah - 1] = torch.clamp(rot, min=0.01, max=0.99).reshape(-1, d)
+            a = generate_random_points_batch(maps[L - 1], p.cost_func_hypers["radius"], nf[-1] * p.n_actions)
+            maps[L] = torch.clamp(a.to(device=dev, dtype=dt), min=0.01, max=0.99).reshape(-1, d)
+            self.maps = [_logit(x).requires_grad_(True) for x in maps]
+        self._parameters = self.maps
+
+    def _pretrain(self, buffer, prev_X, prev_y, nf):
+        """reference actor.py:106-220: fit the network to random ball designs, with draws of
+        the surrogate as the observations fed to the next step."""
+        p = self.parms
+        L, d, n = self.algo_lookahead_steps, p.x_dim, p.n_restarts
+        dev, dt = p.device, p.torch_dtype
+        prev_h = buffer["h"][-1:].clone().expand(n, -1)
+        opt = torch.optim.AdamW(self._parameters, lr=0.01)
+        tree = self._random_tree(prev_X[0:1], nf, n)
+        target = torch.stack([torch.clamp(x.to(device=dev, dtype=dt).reshape(-1, d), min=0.01, max=0.99)
+                              for x in tree], dim=0).detach()
+        self.hidden_noise = torch.randn(n, p.hidden_dim).to(target[-1])
+        prev_h = prev_h + self.hidden_noise
+        gp = self.acqf.gp()
+        stall, best = 0, float("inf")
+        for ep in range(300):
+            outs, h = [], prev_h
+            x, y = prev_X[0].expand(n, d), prev_y[0].expand(n, p.y_dim)
+            for j in range(L):
+                x, h = self.maps(x, y, h, return_actions=False, enable_noise=False)
+                outs.append(x)
+                y = _prior_free_sample(gp, x.detach()).reshape(-1, 1)
+            a, h = self.maps(x, y, h, return_actions=True, enable_noise=False)
+            outs.append(a)
+            loss = torch.mean(abs(target - torch.stack(outs, dim=0)))
+            if ep % 10 == 0:
+                print("Loss:", loss.item())
+            if loss < best:
+                best, stall = loss, 0
+            else:
+                stall += 1
+            loss.backward()
+            opt.step()
+            opt.zero_grad()
+            if stall >= 50:
+                break
+
+    # ------------------------------------------------------------------ query
+    def query(self, buffer, iteration: int, embedder=None, f_posterior=None, save_trajectory=True):
+        """reference actor.py:439-734: optimise the acquisition objective over all restarts and
+        return the best restart's next design."""
+        assert self.acqf is not None, "Acquisition function is not initialized."
+        if embedder is not None:
+            raise NotImplementedError("discrete environments are outside the B200 hot-path scope")
+        p = self.parms
+        n_r = p.n_restarts
+        prev_X = buffer["x"][iteration - 1:iteration].expand(n_r, -1)
+        prev_y = buffer["y"][iteration - 1:iteration].expand(n_r, -1)
+        prev_h = buffer["h"][iteration - 1:iteration].expand(n_r, -1)
+        if p.amortized:
+            prev_h = prev_h + self.hidden_noise
+        prev_cost = (float(buffer["cost"][p.n_initial_points:iteration].sum())
+                     if iteration > p.n_initial_points else 0.0)
+        is_hes = p.algo.startswith("HES")
+        if is_hes:
+            self.acqf.dump_model(f=f_posterior)
+            if p.algo_ts and f_posterior is None:
+                with open(os.path.join(p.save_dir, f"posterior_sample_{iteration}.pkl"), "wb") as fh:
+                    pickle.dump(self.acqf.f, fh)
+        past_initial = iteration > p.n_initial_points
+        if p.amortized:
+            res = self._query_amortized(prev_X, prev_y, prev_h, prev_cost, past_initial, save_trajectory)
+        else:
+            res = self._query_free(prev_X, prev_y, prev_h, prev_cost, past_initial, save_trajectory)
+        if is_hes:
+            self.acqf.clean_dump_model()
+        best_loss, best_cost, best_KL = res["best_loss"], res["best_cost"], res["best_KL"]
+        idx = torch.argmin(best_loss + best_cost + best_KL)
+        if save_trajectory:
+            with open(p.save_dir + f"/trajectory_{iteration}.pkl", "wb") as fh:
+                pickle.dump((res["saved_trajectory"], idx), fh)
+            with open(p.save_dir + f"/lossncost_{iteration}.pkl", "wb") as fh:
+                pickle.dump((res["saved_loss"], res["saved_cost"]), fh)
+        next_X = res["best_next_X"][0][idx].reshape(1, -1)
+        actions = res["best_actions"][..., idx, :, :]
+        hidden_state = res["best_hidden_state"][0][idx:idx + 1] if p.amortized else None
+        acqf_cost = self.acqf.cost_function(prev_X=buffer["x"][iteration - 1:iteration], current_X=next_X,
+                                            previous_cost=prev_cost).detach()
+        return {"all_losses": best_loss, "all_costs": best_cost, "loss": best_loss[idx], "cost": acqf_cost,
+                "next_X": next_X, "actions": actions, "hidden_state": hidden_state, "chosen_idx": idx}
+
+    def _query_amortized(self, prev_X, prev_y, prev_h, prev_cost, past_initial, save_trajectory):
+        """HES-TS-AM: device-resident AdamW loop (one CUDA graph per iteration)."""
+        p, acqf = self.parms, self.acqf
+        L, d, H, N = self.algo_lookahead_steps, p.x_dim, p.hidden_dim, p.n_restarts
+        eng = acqf._ts_engine(acqf.f, d, H, N, p.torch_dtype)
+        eng.seed = acqf.rng_seed
+        theta0 = self.maps.flat_parameters().detach()
+        record = bool(save_trajectory)
+        loop = TSAMLoop(eng, theta0, prev_X, prev_y, prev_h, budget=float(p.budget), lr=p.acq_opt_lr,
+                        past_initial=past_initial, prev_cost=prev_cost, max_iter=p.acq_opt_iter,
+                        record_history=record, record_trajectory=record)
+        if self.rng_mode == "host":
+            draws = _HostDraws(acqf, L, N, d, prev_X)
+            st = loop.run(p.acq_opt_iter, draws_per_iter=draws)
+        else:
+            st = loop.run(p.acq_opt_iter)
+        n_done = int(st.step)
+        # last-iterate weights go back into the module: the reference's best_map holds references to
+        # the live parameters, so its load_state_dict(best_map) is a no-op
+        flat = loop.theta
+        o = 0
+        with torch.no_grad():
+            for prm in self.maps.parameters():
+                prm.copy_(flat[o:o + prm.numel()].view_as(prm))
+                o += prm.numel()
+        r = loop.result()
+        out = dict(best_loss=r["best_loss"], best_cost=r["best_cost"], best_KL=r["best_KL"],
+                   best_next_X=[loop.best_X[s].reshape(*([1] * s), N, 1, d) for s in range(L)],
+                   best_actions=loop.best_A.reshape(*([1] * L), N, p.n_actions, d),
+                   best_hidden_state=[loop.best_HS[s + 1] for s in range(L)],
+                   saved_trajectory=[], saved_loss=[], saved_cost=[])
+        if record:
+            out["saved_loss"] = loop.hist_loss[:n_done].tolist()
+            out["saved_cost"] = loop.hist_cost[:n_done].tolist()
+            tr = loop.hist_X[:n_done].cpu()
+            out["saved_trajectory"] = [[tr[e, s].reshape(*([1] * s), N, 1, d).tolist() for s in range(L)]
+                                       for e in range(n_done)]
+        return out
+
+    def _query_free(self, prev_X, prev_y, prev_h, prev_cost, past_initial, save_trajectory):
+        """Free-parameter algorithms: eager loop over ``acqf.forward`` + fused AdamW kernel."""
+        p, acqf = self.parms, self.acqf
+        params = list(self._parameters)
+        opt = _FlatAdamW(params, lr=p.acq_opt_lr)
+        best = dict(loss=torch.tensor([float("inf")], device=p.device), cost=torch.tensor([float("inf")],
+                    device=p.device), KL=0)
+        snap, stall = {}, 0
+        saved_trajectory, saved_loss, saved_cost = [], [], []
+        for ep in range(p.acq_opt_iter):
+            local_maps = [torch.sigmoid(x) for x in params]
+            if save_trajectory:
+                saved_trajectory.append([x.cpu().detach().tolist() for x in local_maps])
+            rd = acqf.forward(prev_X=prev_X, prev_y=prev_y, prev_hid_state=prev_h, maps=local_maps, embedder=None,
+                              prev_cost=prev_cost, enable_noise=False)
+            acqf_loss, acqf_cost = rd["acqf_loss"], rd["acqf_cost"]
+            if save_trajectory:
+                saved_loss.append(acqf_loss.tolist())
+                saved_cost.append(acqf_cost.tolist())
+            loss = acqf_loss + abs(p.budget - acqf_cost)
+            chosen = torch.argmin(loss)
+            if ep == 0 or bool(loss[chosen] < (best["loss"] + best["cost"]).min()):
+                best = dict(loss=acqf_loss.detach(), cost=acqf_cost.detach(), KL=0)
+                snap = dict(X=[x.detach() for x in rd["X"]], actions=rd["actions"].detach())
+                stall = 0
+            elif past_initial or ep >= 200:
+                stall += 1
+            grads = torch.autograd.grad(loss.mean(), params, allow_unused=True)
+            opt.step(grads)
+            if ep % 50 == 0:
+                print(f"Epoch {ep:05d}\tLoss {acqf_loss[chosen].item():.5f}\tCost: {acqf_cost[chosen].item():.5f}")
+            if stall > 50:
+                break
+        return dict(best_loss=best["loss"], best_cost=best["cost"], best_KL=0, best_next_X=snap["X"],
+                    best_actions=snap["actions"], best_hidden_state=None, saved_trajectory=saved_trajectory,
+                    saved_loss=saved_loss, saved_cost=saved_cost)
+
+
+def _prior_free_sample(gp, x: Tensor) -> Tensor:
+    """One draw of the surrogate's marginal posterior at each point of ``x`` [n, d]: the
+    reference calls ``model(x.unsqueeze(-2)).sample()`` (actor.py:186-191), i.e. independent
+    q = 1 posteriors."""
+    k = gp.k(x, gp.train_X)                                    # [n, n_train]
+    u = k @ gp.Linv.T
+    mean = gp.mean_const + u @ gp.beta
+    var = (gp.amplitude - (u * u).sum(-1)).clamp_min(1e-12)
+    return mean + var.sqrt() * torch.randn(x.shape[0], dtype=x.dtype, device=x.device)
+
+
+class _HostDraws:
+    """Per-iteration draws in the reference's order: main rollout (action rotation, cost noise),
+    then the frozen "original" rollout (every call rotated)."""
+
+    def __init__(self, acqf, L, N, d, like):
+        self.args = (acqf, L, N, d, like)
+
+    def __len__(self):
+        return 1 << 30
+
+    def __getitem__(self, ep):
+        acqf, L, N, d, like = self.args
+        return (*acqf._host_draws(L, N, d, like, False), *acqf._host_draws(L, N, d, like, True))
+
+
+class _FlatAdamW:
+    """torch.optim.AdamW semantics (actor.py:489,646-648) on a list of free tensors through the
+    ``nmb_adamw_flat`` kernel; a ``None`` gradient leaves its tensor untouched."""
+
+    def __init__(self, params, lr, betas=(0.9, 0.999), eps=1e-8, weight_decay=1e-2):
+        self.params = params
+        self.hp = te.AdamWStruct(lr=lr, beta1=betas[0], beta2=betas[1], eps=eps, weight_decay=weight_decay)
+        self.m = [torch.zeros_like(q) for q in params]
+        self.v = [torch.zeros_like(q) for q in params]
+        self.t = [0] * len(params)
+        self.state = [torch.zeros(C.sizeof(te.LoopState), dtype=torch.uint8, device=q.device) for q in params]
+
+    def step(self, grads):
+        lib = _lib.lib()
+        for i, (q, g) in enumerate(zip(self.params, grads)):
+            if g is None:
+                continue
+            _lib.check(lib.nmb_adamw_flat(_lib.dtype_code(q.dtype), C.c_int64(q.numel()), C.byref(self.hp),
+                                          _lib.ptr(q.data), _lib.ptr(self.m[i]), _lib.ptr(self.v[i]),
+                                          _lib.ptr(g.contiguous()), C.c_void_p(self.state[i].data_ptr()), 1,
+                                          _lib.stream_ptr()), "nmb_adamw_flat")

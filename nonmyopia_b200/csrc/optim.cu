@@ -72,20 +72,38 @@ __global__ void advance_state_kernel(nmb_loop_state_t* state) {
     state->done = state->done_next;
 }
 
+// actor.py:622-639: compare this iteration's best total (with |budget - cost|) with the min of
+// best_loss + best_cost + best_KL of the last snapshot (without) - reproduced literally (SURVEY
+// App. D#5).  cand_total / cand_lck are this iteration's min total and min loss+cost+KL over ALL
+// restarts (all-reduced MIN over ranks before this runs when restarts are sharded).
+__device__ __forceinline__ void loop_decide(nmb_loop_state_t* state, int past_initial, int patience) {
+    const bool improve = state->step == 0 || state->cand_total < state->best_min;
+    state->improved = improve ? 1 : 0;
+    if (improve) {
+        state->best_min = state->cand_lck;
+        state->stall = 0;
+        state->n_snapshots += 1;
+    } else if (past_initial || state->step >= 200) {
+        state->stall += 1;
+    }
+    state->done_next = (patience >= 0 && state->stall > patience) ? 1 : 0;
+}
+
 // ---- objective + bookkeeping: one CTA of 1024 threads
 template <typename T>
 __global__ void __launch_bounds__(1024) objective_kernel(int d, int L, long long N, long long n_global, T budget,
-                                                         int past_initial, const T* __restrict__ loss,
+                                                         int past_initial, int patience, const T* __restrict__ loss,
                                                          const T* __restrict__ cost, const T* __restrict__ X,
                                                          const T* __restrict__ A, const T* __restrict__ Xo,
                                                          const T* __restrict__ Ao, T* __restrict__ KL,
                                                          T* __restrict__ total, T* __restrict__ g_loss,
                                                          T* __restrict__ g_cost, T* __restrict__ g_X,
                                                          T* __restrict__ g_A, T* __restrict__ hist_loss,
-                                                         T* __restrict__ hist_cost, long long hist_cap,
-                                                         nmb_loop_state_t* state) {
+                                                         T* __restrict__ hist_cost, T* __restrict__ hist_X,
+                                                         long long hist_cap, int defer_decision, nmb_loop_state_t* state) {
     if (state->done) return;
     __shared__ double s_val[32];
+    __shared__ double s_lck[32];
     __shared__ long long s_idx[32];
     __shared__ double s_sum[2][32];
     const int tid = threadIdx.x;
@@ -93,7 +111,7 @@ __global__ void __launch_bounds__(1024) objective_kernel(int d, int L, long long
     const T eps = T(1e-6);
     double best = 1.0 / 0.0;
     long long best_i = 0x7fffffffffffffffLL;
-    double sl = 0.0, sc = 0.0;
+    double sl = 0.0, sc = 0.0, lck_min = 1.0 / 0.0;
     for (long long c = tid; c < N; c += blockDim.x) {
         T kl = T(0);
         for (int l = 0; l <= L; ++l) {
@@ -131,8 +149,15 @@ __global__ void __launch_bounds__(1024) objective_kernel(int d, int L, long long
             hist_loss[(size_t)state->step * N + c] = lc;
             hist_cost[(size_t)state->step * N + c] = cc;
         }
+        if (hist_X && state->step < hist_cap) {
+            for (int l = 0; l < L; ++l)
+                for (int k = 0; k < d; ++k)
+                    hist_X[(((size_t)state->step * L + l) * N + c) * d + k] = X[((size_t)l * N + c) * d + k];
+        }
         sl += (double)lc; sc += (double)cc;
         if ((double)tot < best) { best = (double)tot; best_i = c; }   // strided ascending: first minimum kept
+        const double lck = (double)((lc + cc) + kl);                  // best_loss + best_cost + best_KL of a snapshot
+        lck_min = lck < lck_min ? lck : lck_min;
     }
     // block argmin (lowest index among equal minima, like torch.argmin)
     for (int m = 16; m > 0; m >>= 1) {
@@ -141,51 +166,30 @@ __global__ void __launch_bounds__(1024) objective_kernel(int d, int L, long long
         if (ov < best || (ov == best && oi < best_i)) { best = ov; best_i = oi; }
         sl += __shfl_xor_sync(0xffffffffu, sl, m);
         sc += __shfl_xor_sync(0xffffffffu, sc, m);
+        const double ol = __shfl_xor_sync(0xffffffffu, lck_min, m);
+        lck_min = ol < lck_min ? ol : lck_min;
     }
-    if ((tid & 31) == 0) { s_val[tid >> 5] = best; s_idx[tid >> 5] = best_i; s_sum[0][tid >> 5] = sl; s_sum[1][tid >> 5] = sc; }
+    if ((tid & 31) == 0) { s_lck[tid >> 5] = lck_min; s_val[tid >> 5] = best; s_idx[tid >> 5] = best_i; s_sum[0][tid >> 5] = sl; s_sum[1][tid >> 5] = sc; }
     __syncthreads();
     if (tid == 0) {
         const int nw = blockDim.x >> 5;
         for (int w = 1; w < nw; ++w) {
             if (s_val[w] < best || (s_val[w] == best && s_idx[w] < best_i)) { best = s_val[w]; best_i = s_idx[w]; }
             sl += s_sum[0][w]; sc += s_sum[1][w];
+            lck_min = s_lck[w] < lck_min ? s_lck[w] : lck_min;
         }
         state->chosen_idx = (int)best_i;
         state->loss_mean = sl / (double)N;
         state->cost_mean = sc / (double)N;
-        // actor.py:623: compare this iteration's best total (with |budget - cost|) with the min of
-        // best_loss + best_cost + best_KL (without) - reproduced literally.
-        // best_min is refreshed by nmb_snapshot bookkeeping below after the copy decision.
-        const bool improve = state->step == 0 || best < state->best_min;
-        state->improved = improve ? 1 : 0;
-        if (improve) {
-            state->stall = 0;
-            state->n_snapshots += 1;
-        } else if (past_initial || state->step >= 200) {
-            state->stall += 1;
-        }
-        state->done_next = state->stall > 50 ? 1 : 0;
+        state->cand_total = best;
+        state->cand_lck = lck_min;
+        if (!defer_decision) loop_decide(state, past_initial, patience);
     }
 }
 
-// after the decision: best_min <- min_c(loss + cost + KL) of the snapshot just taken
-template <typename T>
-__global__ void __launch_bounds__(1024) best_min_kernel(long long N, const T* __restrict__ loss, const T* __restrict__ cost,
-                                                        const T* __restrict__ KL, nmb_loop_state_t* state) {
-    if (state->done || !state->improved) return;
-    __shared__ double s_val[32];
-    double best = 1.0 / 0.0;
-    for (long long c = threadIdx.x; c < N; c += blockDim.x) {
-        const double v = (double)(loss[c] + cost[c] + (KL ? KL[c] : T(0)));
-        best = v < best ? v : best;
-    }
-    for (int m = 16; m > 0; m >>= 1) { const double o = __shfl_xor_sync(0xffffffffu, best, m); best = o < best ? o : best; }
-    if ((threadIdx.x & 31) == 0) s_val[threadIdx.x >> 5] = best;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        for (int w = 1; w < (int)(blockDim.x >> 5); ++w) best = s_val[w] < best ? s_val[w] : best;
-        state->best_min = best;
-    }
+__global__ void decide_kernel(nmb_loop_state_t* state, int past_initial, int patience) {
+    if (state->done) return;
+    loop_decide(state, past_initial, patience);
 }
 
 struct CopyList { const void* src[8]; void* dst[8]; long long n[8]; int count; };
@@ -220,25 +224,24 @@ extern "C" int nmb_policy_transpose(int dtype, int d, int H, int n_actions, cons
 }
 
 extern "C" int nmb_ts_objective(int dtype, int d, int L, int64_t n_chains, int64_t n_global, double budget,
-                                int past_initial, const void* loss, const void* cost, const void* X, const void* A,
+                                int past_initial, int patience, const void* loss, const void* cost, const void* X, const void* A,
                                 const void* X_orig, const void* A_orig, void* KL, void* total, void* g_loss,
-                                void* g_cost, void* g_X, void* g_A, const void* best_sum, void* hist_loss,
-                                void* hist_cost, int64_t hist_capacity, nmb_loop_state_t* state, void* stream) {
-    (void)best_sum;
+                                void* g_cost, void* g_X, void* g_A, void* hist_loss, void* hist_cost, void* hist_X,
+                                int64_t hist_capacity, int defer_decision, nmb_loop_state_t* state, void* stream) {
     NMB_REQUIRE(loss && cost && A && total && g_loss && g_cost && state, NMB_EINVAL, "nmb_ts_objective: null argument");
     NMB_REQUIRE((X_orig == nullptr) == (A_orig == nullptr), NMB_EINVAL, "nmb_ts_objective: X_orig/A_orig mismatch");
     NMB_REQUIRE(L == 0 || X, NMB_EINVAL, "nmb_ts_objective: X is null");
     cudaStream_t st = (cudaStream_t)stream;
     if (dtype == NMB_F64) {
-        objective_kernel<double><<<1, 1024, 0, st>>>(d, L, n_chains, n_global, budget, past_initial, (const double*)loss,
+        objective_kernel<double><<<1, 1024, 0, st>>>(d, L, n_chains, n_global, budget, past_initial, patience, (const double*)loss,
             (const double*)cost, (const double*)X, (const double*)A, (const double*)X_orig, (const double*)A_orig,
             (double*)KL, (double*)total, (double*)g_loss, (double*)g_cost, (double*)g_X, (double*)g_A,
-            (double*)hist_loss, (double*)hist_cost, hist_capacity, state);
+            (double*)hist_loss, (double*)hist_cost, (double*)hist_X, hist_capacity, defer_decision, state);
     } else if (dtype == NMB_F32) {
-        objective_kernel<float><<<1, 1024, 0, st>>>(d, L, n_chains, n_global, (float)budget, past_initial, (const float*)loss,
+        objective_kernel<float><<<1, 1024, 0, st>>>(d, L, n_chains, n_global, (float)budget, past_initial, patience, (const float*)loss,
             (const float*)cost, (const float*)X, (const float*)A, (const float*)X_orig, (const float*)A_orig,
             (float*)KL, (float*)total, (float*)g_loss, (float*)g_cost, (float*)g_X, (float*)g_A,
-            (float*)hist_loss, (float*)hist_cost, hist_capacity, state);
+            (float*)hist_loss, (float*)hist_cost, (float*)hist_X, hist_capacity, defer_decision, state);
     } else { set_error("nmb_ts_objective: dtype %d", dtype); return NMB_EINVAL; }
     NMB_LAUNCH_CHECK();
     return 0;
@@ -264,17 +267,6 @@ extern "C" int nmb_snapshot_if_improved(int dtype, int n_copies, const void* con
     else if (dtype == NMB_F32) snapshot_kernel<float><<<(unsigned)blocks, 256, 0, st>>>(cl, state);
     else { set_error("nmb_snapshot_if_improved: dtype %d", dtype); return NMB_EINVAL; }
     NMB_LAUNCH_CHECK();
-    // keep best_min in step with the snapshot: copies 0,1,2 are by convention loss, cost, KL
-    if (n_copies >= 2) {
-        const void* kl = n_copies >= 3 ? src_host[2] : nullptr;
-        if (dtype == NMB_F64)
-            best_min_kernel<double><<<1, 1024, 0, st>>>(n_elems_host[0], (const double*)src_host[0], (const double*)src_host[1],
-                                                        (const double*)kl, const_cast<nmb_loop_state_t*>(state));
-        else
-            best_min_kernel<float><<<1, 1024, 0, st>>>(n_elems_host[0], (const float*)src_host[0], (const float*)src_host[1],
-                                                       (const float*)kl, const_cast<nmb_loop_state_t*>(state));
-        NMB_LAUNCH_CHECK();
-    }
     return 0;
 }
 
@@ -317,4 +309,11 @@ extern "C" int nmb_adamw_flat(int dtype, int64_t n, const nmb_adamw_t* hp, void*
     if (dtype == NMB_F32) return launch_adamw<float>(tb, 0, hp, param, nullptr, exp_avg, exp_avg_sq, grad, n, state, advance_state, st);
     set_error("nmb_adamw_flat: dtype %d", dtype);
     return NMB_EINVAL;
+}
+
+extern "C" int nmb_loop_decide(nmb_loop_state_t* state, int past_initial, int patience, void* stream) {
+    NMB_REQUIRE(state, NMB_EINVAL, "nmb_loop_decide: null state");
+    decide_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(state, past_initial, patience);
+    NMB_LAUNCH_CHECK();
+    return 0;
 }

@@ -82,7 +82,8 @@ class LoopState(C.Structure):
     """``nmb_loop_state_t`` (device resident; this mirror is for host reads)."""
     _fields_ = [("step", C.c_int64), ("done", C.c_int32), ("done_next", C.c_int32), ("stall", C.c_int32),
                 ("improved", C.c_int32), ("chosen_idx", C.c_int32), ("n_snapshots", C.c_int32),
-                ("best_min", C.c_double), ("loss_mean", C.c_double), ("cost_mean", C.c_double)]
+                ("best_min", C.c_double), ("loss_mean", C.c_double), ("cost_mean", C.c_double),
+                ("cand_total", C.c_double), ("cand_lck", C.c_double)]
 
 
 class AdamWStruct(C.Structure):

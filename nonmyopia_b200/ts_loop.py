@@ -34,13 +34,15 @@ from . import ts_engine as te
 class TSAMLoop:
     def __init__(self, eng: te.TSRollout, theta0: Tensor, prev_x: Tensor, prev_y: Tensor, prev_h: Tensor, *,
                  budget: float, lr: float, past_initial: bool, prev_cost: float = 0.0, n_global: Optional[int] = None,
-                 max_iter: int = 500, record_history: bool = False, betas=(0.9, 0.999), eps: float = 1e-8,
-                 weight_decay: float = 1e-2):
+                 max_iter: int = 500, record_history: bool = False, record_trajectory: bool = False,
+                 patience: int = 50, betas=(0.9, 0.999), eps: float = 1e-8,
+                 weight_decay: float = 1e-2, group=None):
         self.eng = eng
         d, H, L, N = eng.d, eng.H, eng.L, eng.N
         dt, dev = eng.dtype, eng.device
         self.budget, self.past_initial, self.max_iter = float(budget), bool(past_initial), int(max_iter)
         self.n_global = int(n_global) if n_global else N
+        self.patience = int(patience)
         self.hp = te.AdamWStruct(lr=lr, beta1=betas[0], beta2=betas[1], eps=eps, weight_decay=weight_decay)
         # parameters: live copy, frozen "original maps" (actor.py:525-535), Adam moments
         self.theta = theta0.detach().to(dev, dt).clone().contiguous()
@@ -65,16 +67,27 @@ class TSAMLoop:
         self.best_X, self.best_A, self.best_HS = z(max(L, 1), N, d), z(N, d), z(L + 2, N, H)
         self.hist_loss = z(self.max_iter, N) if record_history else None
         self.hist_cost = z(self.max_iter, N) if record_history else None
+        self.hist_X = z(self.max_iter, max(L, 1), N, d) if record_trajectory else None
         srcs = [self.main.loss, self.main.cost, self.KL, self.main.X, self.main.A, self.main.HS]
         dsts = [self.best_loss, self.best_cost, self.best_KL, self.best_X, self.best_A, self.best_HS]
         self._src = (C.c_void_p * 6)(*[t.data_ptr() for t in srcs])
         self._dst = (C.c_void_p * 6)(*[t.data_ptr() for t in dsts])
         self._cnt = (C.c_int64 * 6)(*[t.numel() for t in srcs])
         self.graph = None
-        self.n_launches_per_iter = 8
+        # process group over which the restarts are sharded (None: single GPU)
+        self.group = group
+        if group is not None:
+            import torch.distributed as dist
+            self._dist = dist
+            self._cand = self.state[56:72].view(torch.float64)
+            self.grad = torch.zeros_like(self.theta)
+            self._one_split = (C.c_int32 * 20)()
+        # rollout_fwd, objective, snapshot, rollout_bwd, wgrad, adamw, advance (+ decide, reduce when sharded)
+        self.n_launches_per_iter = 7 if group is None else 9
 
     # ------------------------------------------------------------------ one iteration
-    def _iteration(self, draws=None) -> None:
+    def _iteration(self, draws=None, mark=None) -> None:
+        mark = mark or (lambda name: None)
         eng, lib = self.eng, self.eng.lib
         st = _lib.stream_ptr()
         if draws is None:
@@ -85,22 +98,43 @@ class TSAMLoop:
             rm = eng.rollout_struct(self.main, self.theta, self.theta_t, False, mq, md, mn, 0)
             ro = eng.rollout_struct(self.orig, self.theta0, self.theta0_t, True, oq, od, on, 1)
         eng.forward(self.prob, [rm, ro])
+        mark("ts_rollout_fwd")
         state_p = C.c_void_p(self.state.data_ptr())
         _lib.check(lib.nmb_ts_objective(
             eng.dt, eng.d, eng.L, C.c_int64(eng.N), C.c_int64(self.n_global), C.c_double(self.budget),
-            int(self.past_initial), _lib.ptr(self.main.loss), _lib.ptr(self.main.cost), _lib.ptr(self.main.X),
+            int(self.past_initial), self.patience, _lib.ptr(self.main.loss), _lib.ptr(self.main.cost), _lib.ptr(self.main.X),
             _lib.ptr(self.main.A), _lib.ptr(self.orig.X), _lib.ptr(self.orig.A), _lib.ptr(self.KL),
             _lib.ptr(self.total), _lib.ptr(self.g_loss), _lib.ptr(self.g_cost), _lib.ptr(self.g_X),
-            _lib.ptr(self.g_A), None, _lib.ptr(self.hist_loss), _lib.ptr(self.hist_cost),
-            C.c_int64(self.max_iter), state_p, st), "nmb_ts_objective")
+            _lib.ptr(self.g_A), _lib.ptr(self.hist_loss), _lib.ptr(self.hist_cost), _lib.ptr(self.hist_X),
+            C.c_int64(self.max_iter), int(self.group is not None), state_p, st), "nmb_ts_objective")
+        if self.group is not None:
+            # restarts sharded over ranks: one MIN all-reduce of (min total, min loss+cost+KL) keeps the
+            # snapshot / early-stop decision identical on every rank
+            self._dist.all_reduce(self._cand, op=self._dist.ReduceOp.MIN, group=self.group)
+            _lib.check(lib.nmb_loop_decide(state_p, int(self.past_initial), self.patience, st), "nmb_loop_decide")
         _lib.check(lib.nmb_snapshot_if_improved(eng.dt, 6, self._src, self._dst, self._cnt, state_p, st),
                    "nmb_snapshot_if_improved")
+        mark("objective+snapshot")
         eng.backward(self.prob, rm, self.g_loss, self.g_cost, self.g_X, self.g_A)
+        mark("ts_rollout_bwd")
         partials = eng.weight_grad_partials(self.prob, self.main)
+        mark("policy_wgrad")
+        if self.group is not None:
+            # data-parallel policy gradient: reduce the split-K partials locally, SUM over ranks (C2)
+            _lib.check(lib.nmb_policy_reduce_partials(eng.dt, eng.d, eng.H, 1, _lib.ptr(partials), eng.seg_splits,
+                                                      _lib.ptr(self.grad), st), "nmb_policy_reduce_partials")
+            self._dist.all_reduce(self.grad, op=self._dist.ReduceOp.SUM, group=self.group)
+            partials = self.grad
+            for i in range(20):
+                self._one_split[i] = 1 if eng.seg_splits[i] > 0 else 0
+            splits = self._one_split
+        else:
+            splits = eng.seg_splits
         _lib.check(lib.nmb_policy_adamw_step(eng.dt, eng.d, eng.H, 1, C.byref(self.hp), _lib.ptr(self.theta),
                                              _lib.ptr(self.theta_t), _lib.ptr(self.m), _lib.ptr(self.v),
-                                             _lib.ptr(partials), eng.seg_splits, state_p, 1, st),
+                                             _lib.ptr(partials), splits, state_p, 1, st),
                    "nmb_policy_adamw_step")
+        mark("adamw")
 
     def read_state(self) -> te.LoopState:
         raw = self.state.cpu().numpy().tobytes()

@@ -1,0 +1,192 @@
+"""GPU parity of the drop-in class API (nonmyopia_b200.acqfs / actor / amortized_network) against
+the golden vectors recorded from the reference's own classes (oracle/make_golden.py)."""
+import tempfile
+import types
+
+import pytest
+import torch
+
+from tests import helpers as H
+from tests.test_path_gpu import _product_path
+from tests.test_ts_rollout_gpu import pack_draws
+
+pytestmark = pytest.mark.gpu
+F64 = torch.float64
+
+
+def product_gp(g):
+    from nonmyopia_b200.gp import SurrogateGP
+    d = g["train_X"].shape[-1]
+    ls = torch.full((d if g["ard"] else 1,), g["lengthscale"], dtype=F64)
+    return SurrogateGP(g["train_X"], g["train_Y"], kernel=g["kernel"], lengthscale=ls, outputscale=g["outputscale"],
+                       noise=g["noise"], mean_const=g["mean_const"])
+
+
+def make_acqf(fx, nf, enable_ts, n_samples=64, design_samplers=None, action_sampler=None):
+    from nonmyopia_b200 import acqfs
+    return acqfs.qMultiStepHEntropySearch(
+        model=product_gp(fx["gp"]), loss_function_class=acqfs.qLossFunctionTopK,
+        loss_func_hypers=dict(dist_weight=1, dist_threshold=0.5), cost_function_class=acqfs.qCostFunction,
+        cost_func_hypers=fx["cost"], lookahead_steps=fx["L"], n_actions=1, n_fantasy_at_design_pts=nf,
+        n_fantasy_at_action_pts=n_samples, enable_ts=enable_ts, design_samplers=design_samplers,
+        action_sampler=action_sampler)
+
+
+def make_net(fx):
+    from nonmyopia_b200.amortized_network import AmortizedNetwork
+    d, Hh = fx["d"], fx["H"]
+    net = AmortizedNetwork(d + 1, d, Hh, 1, torch.tensor([[0.0, 1.0]] * d, dtype=F64)).to(dtype=F64, device="cuda")
+    net.load_state_dict({k: v.clone() for k, v in fx["policy"].items()})
+    return net
+
+
+def test_gp_state_matches_oracle():
+    fx = H.load("mc_hartmann_L3")
+    ref = H.dense_gp(fx["gp"])
+    gp = product_gp(fx["gp"])
+    assert H.rel_err(gp.L, ref.L, atol=1e-3) < 1e-8
+    assert H.rel_err(gp.alpha, ref.alpha, atol=1e-3) < 1e-8
+    x = torch.rand(37, fx["d"], dtype=F64)
+    from oracle import gp_math
+    K = gp_math.kernel_matrix(x, ref.train_X, ref.kind, ref.lengthscale, ref.outputscale)
+    assert H.rel_err(gp.k(x.cuda(), gp.train_X), K, atol=1e-6) < 1e-8
+
+
+@pytest.mark.parametrize("name", ["ts_am_ackley_L3", "ts_am_cosine8_L3", "ts_am_ackley_rbf_disc"])
+@pytest.mark.parametrize("mode", ["main", "orig"])
+def test_acqf_forward_ts_amortized(name, mode):
+    fx = H.load(name)
+    g = fx["out"][mode]
+    L, N, d = fx["L"], fx["n_r"], fx["d"]
+    acqf = make_acqf(fx, [1] * L, True)
+    acqf.dump_model(f=_product_path(fx))
+    net = make_net(fx)
+    acqf._given_draws = pack_draws(g["rot"], g["cost_noise"], L, N)
+    out = acqf.forward(fx["prev_X"].cuda(), fx["prev_y"].cuda(), fx["prev_h"].cuda(), net,
+                       enable_noise=(mode == "orig"))
+    assert out["acqf_loss"].shape == (N,) and out["actions"].shape == g["actions"].shape
+    assert H.rel_err(out["acqf_loss"], g["acqf_loss"], atol=1e-2) < 1e-8
+    assert H.rel_err(out["acqf_cost"], g["acqf_cost"], atol=1e-3) < 1e-8
+    for s in range(L):
+        assert out["X"][s].shape == g["X"][s].shape
+        assert H.rel_err(out["X"][s], g["X"][s], atol=1e-3) < 1e-8
+        assert H.rel_err(out["hidden_state"][s], g["hidden_state"][s], atol=1e-3) < 1e-8
+    tot = (out["acqf_loss"] + (fx["budget"] - out["acqf_cost"]).abs()).mean()
+    params = list(net.parameters())
+    grads = torch.autograd.grad(tot, params, allow_unused=True)
+    for (k, _), gr in zip(net.named_parameters(), grads):
+        ref = g["grads"][k]
+        assert gr is not None, k
+        assert float((gr.cpu() - ref).abs().max()) / max(float(ref.abs().max()), 1e-6) < 1e-8, k
+
+
+def test_acqf_forward_ts_free():
+    fx = H.load("ts_free_ackley_L2")
+    L, N, d = fx["L"], fx["n_r"], fx["d"]
+    acqf = make_acqf(fx, [1] * L, True)
+    acqf.dump_model(f=_product_path(fx))
+    lg = [l.clone().cuda().requires_grad_(True) for l in fx["logits"]]
+    acqf._given_draws = torch.stack([z.reshape(N) for z in fx["out"]["cost_noise"]]).cuda()
+    out = acqf.forward(fx["prev_X"].cuda(), fx["prev_y"].cuda(), torch.zeros(N, 4, dtype=F64, device="cuda"),
+                       [torch.sigmoid(x) for x in lg], enable_noise=False)
+    assert H.rel_err(out["acqf_loss"], fx["out"]["acqf_loss"], atol=1e-2) < 1e-8
+    assert H.rel_err(out["acqf_cost"], fx["out"]["acqf_cost"], atol=1e-3) < 1e-8
+    grads = torch.autograd.grad((out["acqf_loss"] + (fx["budget"] - out["acqf_cost"]).abs()).mean(), lg)
+    for a, b in zip(grads, fx["out"]["grads"]):
+        assert float((a.cpu() - b).abs().max()) / max(float(b.abs().max()), 1e-6) < 1e-8
+
+
+def test_tree_cost_branching_vs_oracle():
+    """nmb_tree_cost on a branching tree with the non-Markovian discount vs the oracle's level loop."""
+    from nonmyopia_b200.acqfs import _TreeCostFn
+    from oracle import hes_oracle as ho
+    g = torch.Generator().manual_seed(3)
+    n_r, d, nf = 5, 3, [4, 3, 2]
+    spec = ho.CostSpec(radius=0.1, k=2.0, max_noise=1e-3, p_norm=2.0, discount=0.1, discount_threshold=0.9)
+    hyp = dict(radius=0.1, k=2.0, max_noise=1e-3, p_norm=2.0, discount=0.1, discount_threshold=0.9)
+    cnt = [n_r, n_r * 4, n_r * 12, n_r * 24]
+    root = torch.rand(n_r, d, dtype=F64, generator=g)
+    lv = [torch.rand(c, d, dtype=F64, generator=g).requires_grad_(True) for c in cnt]
+    nz = [torch.randn(c, dtype=F64, generator=g) for c in cnt]
+    # oracle: level tensors [*nf_rev[:s], n_r, 1, d]
+    shp = lambda s: nf[:s][::-1] + [n_r, 1, d]
+    X = [lv[s].reshape(*shp(s)) for s in range(4)]
+    Z = [nz[s].reshape(*shp(s)[:-1], 1) for s in range(4)]
+    cost = ho.spotlight_cost(root[:, None, :], X[0], spec, Z[0], 0.3)
+    for s in range(1, 4):
+        cost = cost + ho.spotlight_cost(X[s - 1].unsqueeze(0).expand_as(X[s]), X[s], spec, Z[s], cost + 0.3)
+    ref = cost.squeeze(-1).sum(-1).reshape(-1)
+    wts = torch.rand(ref.shape, dtype=F64, generator=g)
+    gref = torch.autograd.grad((ref * wts).sum(), lv)
+    lc = [l.detach().cuda().requires_grad_(True) for l in lv]
+    acc = _TreeCostFn.apply(root.cuda(), torch.cat(nz).cuda(), hyp, 0.3, *lc)
+    assert H.rel_err(acc, ref, atol=1e-3) < 1e-10
+    gd = torch.autograd.grad((acc * wts.cuda()).sum(), lc)
+    for a, b in zip(gd, gref):
+        assert H.rel_err(a, b, atol=1e-3) < 1e-10
+
+
+def _parms(fx, tmp, n_iter, rng_mode):
+    from nonmyopia_b200 import acqfs
+    d = fx["d"]
+    return types.SimpleNamespace(
+        algo="HES", algo_ts=True, amortized=True, algo_lookahead_steps=fx["L"], x_dim=d, y_dim=1,
+        hidden_dim=fx["H"], n_actions=1, n_restarts=fx["n_r"], n_samples=64, env_discretized=False,
+        num_categories=None, bounds=torch.tensor([[0.0, 1.0]] * d, dtype=F64), torch_dtype=F64, device="cuda",
+        acq_opt_lr=fx["lr"], acq_opt_iter=n_iter, n_initial_points=fx["gp"]["train_X"].shape[0], save_dir=tmp,
+        budget=fx["budget"], plot=False, loss_function_class=acqfs.qLossFunctionTopK,
+        loss_func_hypers=dict(dist_weight=1, dist_threshold=0.5), cost_function_class=acqfs.qCostFunction,
+        cost_func_hypers=fx["cost"], rng_mode=rng_mode)
+
+
+def test_actor_query_matches_reference_golden():
+    """Actor.query through the class API, fed the recorded draws: identical argmin and next_X."""
+    from nonmyopia_b200 import actor as A
+    fx = H.load("query_ts_am_ackley_L1")
+    L, N, d, n = fx["L"], fx["n_r"], fx["d"], fx["gp"]["train_X"].shape[0]
+    tmp = tempfile.mkdtemp()
+    parms = _parms(fx, tmp, fx["n_iter"], "host")
+    act = A.Actor(parms)
+    act.maps.load_state_dict({k: v.clone() for k, v in fx["policy"].items()})
+    g = fx["gp"]
+    buffer = dict(x=g["train_X"].cuda(), y=g["train_Y"].cuda(), h=torch.zeros(n, fx["H"], dtype=F64, device="cuda"),
+                  cost=torch.zeros(n, dtype=F64, device="cuda"))
+    act.construct_acqf(product_gp(g), buffer)
+    act.hidden_noise = fx["prev_h"].cuda()           # buffer h is zero: prev_h == hidden_noise
+    draws = []
+    for dr in fx["draws"]:
+        draws.append((*pack_draws(dr["main_rot"], dr["main_noise"], L, N),
+                      *pack_draws(dr["orig_rot"], dr["orig_noise"], L, N)))
+    A._HostDraws.__getitem__ = lambda self, ep: draws[ep]
+    out = act.query(buffer, iteration=n, f_posterior=_product_path(fx), save_trajectory=True)
+    ref = fx["out"]
+    assert int(out["chosen_idx"]) == ref["chosen_idx"]
+    assert H.rel_err(out["next_X"], ref["next_X"], atol=1e-3) < 1e-8
+    assert H.rel_err(out["all_losses"], ref["all_losses"], atol=1e-2) < 1e-8
+    assert H.rel_err(out["all_costs"], ref["all_costs"], atol=1e-3) < 1e-8
+    assert H.rel_err(out["actions"], ref["actions"], atol=1e-3) < 1e-8
+    assert H.rel_err(out["hidden_state"], ref["hidden_state"], atol=1e-3) < 1e-8
+    import os
+    import pickle
+    traj, idx = pickle.load(open(os.path.join(tmp, f"trajectory_{n}.pkl"), "rb"))
+    assert len(traj) == fx["n_iter"] and int(idx) == ref["chosen_idx"]
+
+
+def test_actor_query_device_rng_runs_and_stops():
+    """Default mode (in-kernel RNG, CUDA graph): runs end to end and returns a design in the unit cube."""
+    from nonmyopia_b200 import actor as A
+    fx = H.load("query_ts_am_ackley_L1")
+    n = fx["gp"]["train_X"].shape[0]
+    tmp = tempfile.mkdtemp()
+    parms = _parms(fx, tmp, 60, "device")
+    torch.manual_seed(0)
+    act = A.Actor(parms)
+    g = fx["gp"]
+    buffer = dict(x=g["train_X"].cuda(), y=g["train_Y"].cuda(), h=torch.zeros(n, fx["H"], dtype=F64, device="cuda"),
+                  cost=torch.zeros(n, dtype=F64, device="cuda"))
+    act.construct_acqf(product_gp(g), buffer)
+    act.reset_parameters(buffer)
+    out = act.query(buffer, iteration=n, save_trajectory=False)
+    assert out["next_X"].shape == (1, fx["d"]) and bool(((out["next_X"] > 0) & (out["next_X"] < 1)).all())
+    assert out["hidden_state"].shape == (1, fx["H"])
+    assert torch.isfinite(out["all_losses"]).all()
