@@ -245,6 +245,79 @@ int nmb_adamw_flat(int dtype, int64_t n, const nmb_adamw_t* hp, void* param, voi
                    const void* grad, nmb_loop_state_t* state, int advance_state, void* stream);
 
 /* ------------------------------------------------------------------------
+ * Exact-GP posterior over a fantasy tree (HES-MC and the qEI/qPI/qSR/qUCB/qKG baselines):
+ * replaces model.posterior -> sampler -> condition_on_observations per level and the leaf
+ * posterior + sampler (reference acqfs.py:363-373, 413-415; BoTorch/GPyTorch arithmetic of
+ * SURVEY App. A.3-A.5) without materialising any per-node (n+s)x(n+s) root.
+ *
+ * With u(x) = L^-1 k(X_tr, x) for the base root L (one shared triangular product per query
+ * point), conditioning on the q = 1 ancestors z_0..z_{s-1} of a node is the tail recursion
+ *   w_t(x) = (k(z_t, x) - u(z_t).u(x) - sum_{t'<t} w_t'(z_t) w_t'(x)) / c_t,
+ *   c_t    = sqrt(var_t(z_t) + noise),   var_s(x) = k(x,x) - |u(x)|^2 - sum_t w_t(x)^2,
+ *   mean_s(x) = c + k(x, X_tr).alpha + sum_t w_t(x) b_t,   b_t = sigma_t(z_t) z_t^base[f_t] / c_t
+ * (SURVEY App. A.4 "structural identity").  Tree layout as in nmb_tree_cost_*.
+ * ---------------------------------------------------------------------- */
+#define NMB_MAX_LEVELS 16
+typedef struct nmb_gp {
+    int32_t d, n, kernel_id;
+    int32_t ldu;            /* row stride of U / gU (>= n, multiple of 4) */
+    double amplitude, noise, mean_const;
+    const void* train_x;    /* [n][d] */
+    const void* inv_ls;     /* [d] */
+    const void* linv;       /* [n][n] inverse Cholesky root, row-major, lower triangular */
+    const void* linv_t;     /* [n][n] its transpose */
+    const void* alpha;      /* [n] (K + s2 I)^-1 (y - c) */
+} nmb_gp_t;
+
+typedef struct nmb_tree {
+    int32_t n_levels;                 /* design levels + the action level */
+    int32_t obs_noise_fantasy;        /* 1: fantasies drawn with observation noise (qKG) */
+    int64_t counts[NMB_MAX_LEVELS];   /* nodes per level, counts[0] = n_restarts */
+    const void* base[NMB_MAX_LEVELS]; /* device: base samples of level s < n_levels-1, [counts[s+1]/counts[s]] */
+    double action_base_mean;          /* mean of the action sampler's base samples (n_actions = 1) */
+} nmb_tree_t;
+
+/* U[p][:] = L^-1 (amp k(X_tr, x_p)), m0[p] = amp k(x_p, X_tr).alpha, q[p] = |U[p]|^2 for n_pts points */
+int nmb_gp_whiten_fwd(const nmb_gp_t* gp, int dtype, const void* pts, int64_t n_pts, void* U, void* m0, void* q,
+                      void* stream);
+/* g_pts[p][:] += d/dx_p of ( gU[p].u(x_p) + g_m0[p] m0(x_p) ) */
+int nmb_gp_whiten_bwd(const nmb_gp_t* gp, int dtype, const void* pts, int64_t n_pts, const void* gU,
+                      const void* g_m0, void* g_pts, void* stream);
+
+/* per-node state of a tree evaluation; every array is caller-allocated, [total] = sum(counts) */
+typedef struct nmb_tree_state {
+    const void* pts;    /* [total][d] all levels back to back */
+    void *U, *m0, *q;   /* whitened vectors [total][ldu], base mean part, squared norm */
+    void *W;            /* [total][n_levels] tails w_t(x) */
+    void *var, *mean, *cst, *sig, *bv;   /* [total]: posterior variance / mean, c, sigma, b of the node's branch */
+    void *leaf_loss;    /* [counts[n_levels-1]] -(mean + sigma * action_base_mean) */
+    /* backward */
+    void *Gw, *Gdot;    /* [total][n_levels] */
+    void *Gc, *Gb, *Gq, *Gm0;   /* [total] */
+    void *gU;           /* [total][ldu] */
+    void *g_pts;        /* [total][d] */
+} nmb_tree_state_t;
+
+/* forward of one level (levels must be issued in order 0..n_levels-1 after nmb_gp_whiten_fwd on all points) */
+int nmb_mc_level_fwd(const nmb_gp_t* gp, const nmb_tree_t* tree, const nmb_tree_state_t* st, int dtype, int level,
+                     void* stream);
+/* backward of one level (issue levels n_levels-1..0; Gw/Gc/Gb/g_pts zeroed by the caller first);
+ * g_leaf_sig == NULL: g_leaf [counts[n_levels-1]] is the adjoint of leaf_loss; otherwise g_leaf / g_leaf_sig are
+ * the adjoints of the leaf nodes' posterior mean / sigma (baselines) */
+int nmb_mc_level_bwd(const nmb_gp_t* gp, const nmb_tree_t* tree, const nmb_tree_state_t* st, int dtype, int level,
+                     const void* g_leaf, const void* g_leaf_sig, void* stream);
+/* gU of every node from Gq / Gdot (own, ancestors', descendants' terms) */
+int nmb_mc_gather_gu(const nmb_gp_t* gp, const nmb_tree_t* tree, const nmb_tree_state_t* st, int dtype, void* stream);
+/* out[r] = mean over the leaves of restart r (leaf l belongs to restart l % n_r); reference acqfs.py:443-447 */
+int nmb_tree_restart_mean(int dtype, const void* leaf, int64_t n_leaf, int64_t n_r, void* out, void* stream);
+
+/* Monte-Carlo utilities of the myopic baselines at q = 1: value[r] = mean_s u(mean_r + sigma_r z_s)
+ * and its derivatives w.r.t. mean and sigma.  which: 0 qEI relu(y - best_f), 1 qPI sigmoid((y - best_f)/1e-3),
+ * 2 qSR y, 3 qUCB mu^ + sqrt(beta pi/2) |y - mu^| with mu^ = mean_s y. */
+int nmb_mc_utility(int dtype, int which, double best_f, double beta, const void* mean, const void* sig, int64_t n,
+                   const void* base, int n_samples, void* value, void* d_mean, void* d_sig, void* stream);
+
+/* ------------------------------------------------------------------------
  * FP64 / FP32 pipe micro-benchmarks used for the roofline denominators
  * (MEASURED_PEAKS.json has no FP64 entry).
  * which: 0 = dependent-chain-free FMA throughput, 1 = sincospi, 2 = exp.

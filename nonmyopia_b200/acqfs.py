@@ -227,11 +227,6 @@ class _TreeCostFn(torch.autograd.Function):
         return (g_root, None, None, None, *outs)
 
 
-def _restart_mean(leaf_vals: Tensor, n_r: int) -> Tensor:
-    """mean over every leading tree dim of [*nf_rev, n_r] -> [n_r] (reference acqfs.py:443-447)."""
-    return leaf_vals.reshape(-1, n_r).mean(0) if leaf_vals.numel() != n_r else leaf_vals.reshape(n_r)
-
-
 # --------------------------------------------------------------------------------------
 # H-entropy search
 # --------------------------------------------------------------------------------------
@@ -404,7 +399,7 @@ class qMultiStepHEntropySearch(nn.Module):
         acc = _TreeCostFn.apply(prev_X, noise.contiguous(), self.cost_function.hypers(), prev_cost, *levels)
         nf_rev = lambda s: nf[:s][::-1]
         X_ret = [levels[s].reshape(*nf_rev(s), n_r, 1, d) for s in range(L)]
-        return {"acqf_loss": _restart_mean(leaf_loss, n_r), "acqf_cost": _restart_mean(acc, n_r), "X": X_ret,
+        return {"acqf_loss": self._mc.restart_mean(leaf_loss), "acqf_cost": self._mc.restart_mean(acc), "X": X_ret,
                 "actions": levels[L].reshape(*nf[::-1], n_r, self.n_actions, d),
                 "hidden_state": [prev_h] * L}
 

@@ -1,0 +1,676 @@
+// Exact-GP posterior over a fantasy tree: shared-root whitening (GEMM against the explicit
+// inverse Cholesky root, kernel rows generated on the fly), per-level tail recursion, the
+// hand-derived reverse pass, and the per-restart reductions (reference acqfs.py:363-373,
+// 413-415, 443-447).
+//
+//   whiten_fwd : CTA = 32 query points.  K tile [n][32] (k-major) is generated in shared memory
+//                from the points and X_tr (one coalesced pass, fused m0 = k.alpha), then
+//                U[32 x 64 cols] = K^T L^-T column block by column block with the L^-T operand
+//                streamed from L2 through the double-buffered stage of policy_dev.cuh
+//                (only the j <= i part is touched: half the flops of a dense product).
+//   whiten_bwd : same tiling, g_K = gU L^-1 fused with the kernel-gradient contraction
+//                g_x = sum_j (g_K[j] + g_m0 alpha_j) d k(x, X_j) / dx  (K rows are recomputed).
+//   level_fwd  : one warp per node: the s dots u(z_t).u(x) against its ancestors (contiguous
+//                n-vectors), then the O(s^2) scalar recursion.
+//   level_bwd  : one thread per node: reverse recursion; contributions to ancestors go to their
+//                adjoint slots with FP64 atomics (levels are issued leaf -> root, so a node's
+//                slots are complete when its own level runs).
+//   gather_gu  : one warp per node: gU = 2 g_q u + sum_t g_dot_t u(z_t) + sum_desc g_dot u(desc),
+//                descendants visited in a fixed order.
+#include "policy_dev.cuh"
+
+namespace nmb {
+
+template <typename T> struct GpDev {
+    int d, n, kernel_id, ldu;
+    T amp, noise, mean_const;
+    const T *train_x, *inv_ls, *linv, *linv_t, *alpha;
+};
+
+template <typename T> static GpDev<T> to_dev(const nmb_gp_t& g) {
+    GpDev<T> o;
+    o.d = g.d; o.n = g.n; o.kernel_id = g.kernel_id; o.ldu = g.ldu;
+    o.amp = (T)g.amplitude; o.noise = (T)g.noise; o.mean_const = (T)g.mean_const;
+    o.train_x = (const T*)g.train_x; o.inv_ls = (const T*)g.inv_ls; o.linv = (const T*)g.linv;
+    o.linv_t = (const T*)g.linv_t; o.alpha = (const T*)g.alpha;
+    return o;
+}
+
+extern __shared__ __align__(16) unsigned char mc_smem_raw[];
+
+// ------------------------------------------------------------------ whiten forward
+template <typename T, int DMAX>
+__global__ void __launch_bounds__(kNT, 1) whiten_fwd_kernel(GpDev<T> g, const T* __restrict__ pts, long long n_pts,
+                                                            T* __restrict__ U, T* __restrict__ m0,
+                                                            T* __restrict__ q) {
+    const int n = g.n, d = g.d, tid = threadIdx.x;
+    const int npad = (n + 3) & ~3;
+    T* Kt = reinterpret_cast<T*>(mc_smem_raw);        // [npad][kRS]
+    T* stage = Kt + (size_t)npad * kRS;               // [2][kKC][kOB]
+    T* xs = stage + 2 * kKC * kOB;                    // [kR][DMAX] scaled points
+    T* red = xs + kR * DMAX;                          // [8][kR]
+    const long long p0 = (long long)blockIdx.x * kR;
+    const int nvalid = (int)min((long long)kR, n_pts - p0);
+    for (int e = tid; e < kR * DMAX; e += kNT) {
+        const int r = e / DMAX, k = e - r * DMAX;
+        xs[e] = (r < nvalid && k < d) ? pts[(p0 + r) * d + k] * __ldg(g.inv_ls + k) : T(0);
+    }
+    __syncthreads();
+    // ---- kernel rows: warp w handles training points j = w, w+8, ...; lane = query point
+    {
+        const int r = tid & 31, w = tid >> 5;
+        T xr[DMAX];
+#pragma unroll
+        for (int k = 0; k < DMAX; ++k) xr[k] = xs[r * DMAX + k];
+        T macc = T(0);
+        for (int j = w; j < npad; j += 8) {
+            T kv = T(0);
+            if (j < n) {
+                T r2 = T(0);
+#pragma unroll
+                for (int k = 0; k < DMAX; ++k) {
+                    if (k < d) {
+                        const T df = xr[k] - __ldg(g.train_x + (size_t)j * d + k) * __ldg(g.inv_ls + k);
+                        r2 = fma(df, df, r2);
+                    }
+                }
+                T kap, gc;
+                kernel_profile<T>(g.kernel_id, r2, kap, gc);
+                kv = g.amp * kap;
+                macc = fma(kv, __ldg(g.alpha + j), macc);
+            }
+            Kt[(size_t)j * kRS + r] = (r < nvalid) ? kv : T(0);
+        }
+        red[w * kR + r] = macc;
+    }
+    __syncthreads();
+    if (tid < nvalid) {
+        T s = T(0);
+#pragma unroll
+        for (int w = 0; w < 8; ++w) s += red[w * kR + tid];
+        m0[p0 + tid] = s;
+    }
+    // ---- U tile = K^T L^-T, 64 output columns at a time; only k < cb + 64 contributes
+    const TileCoord tc;
+    T qacc[2] = {T(0), T(0)};
+    for (int cb = 0; cb < n; cb += kOB) {
+        T acc[2][4];
+        zero_acc(acc);
+        const int nc = min(kOB, n - cb);
+        gemm_block<T>(Kt, min(n, cb + kOB), g.linv_t, n, cb, nc, stage, tc, acc);
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+            const int r = tc.r0 + i;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const int c = cb + tc.c0 + j;
+                if (c < n) {
+                    qacc[i] = fma(acc[i][j], acc[i][j], qacc[i]);
+                    if (r < nvalid) U[(size_t)(p0 + r) * g.ldu + c] = acc[i][j];
+                }
+            }
+        }
+    }
+    // |u|^2: 4 lanes (lane & 3) x 4 warps (warp & 3) share a row
+#pragma unroll
+    for (int i = 0; i < 2; ++i) { qacc[i] += shfl_xor_(qacc[i], 1); qacc[i] += shfl_xor_(qacc[i], 2); }
+    __syncthreads();
+    if ((tid & 3) == 0) {
+        const int cw = (tid >> 5) & 3;
+        red[cw * kR + tc.r0] = qacc[0];
+        red[cw * kR + tc.r0 + 1] = qacc[1];
+    }
+    __syncthreads();
+    if (tid < nvalid) q[p0 + tid] = red[tid] + red[kR + tid] + red[2 * kR + tid] + red[3 * kR + tid];
+}
+
+// ------------------------------------------------------------------ whiten backward
+template <typename T, int DMAX>
+__global__ void __launch_bounds__(kNT, 1) whiten_bwd_kernel(GpDev<T> g, const T* __restrict__ pts, long long n_pts,
+                                                            const T* __restrict__ gU, const T* __restrict__ g_m0,
+                                                            T* __restrict__ g_pts) {
+    const int n = g.n, d = g.d, tid = threadIdx.x;
+    const int npad = (n + 3) & ~3;
+    T* Gt = reinterpret_cast<T*>(mc_smem_raw);        // [npad][kRS]  gU tile, k-major
+    T* stage = Gt + (size_t)npad * kRS;
+    T* xs = stage + 2 * kKC * kOB;                    // [kR][DMAX]
+    T* red = xs + kR * DMAX;                          // [4][kR][DMAX]
+    const long long p0 = (long long)blockIdx.x * kR;
+    const int nvalid = (int)min((long long)kR, n_pts - p0);
+    for (int e = tid; e < kR * DMAX; e += kNT) {
+        const int r = e / DMAX, k = e - r * DMAX;
+        xs[e] = (r < nvalid && k < d) ? pts[(p0 + r) * d + k] * __ldg(g.inv_ls + k) : T(0);
+    }
+    // gU tile: coalesced global reads along i, transposed into the k-major tile
+    for (int e = tid; e < kR * npad; e += kNT) {
+        const int r = e / npad, i = e - r * npad;
+        Gt[(size_t)i * kRS + r] = (r < nvalid && i < n) ? gU[(size_t)(p0 + r) * g.ldu + i] : T(0);
+    }
+    __syncthreads();
+    const TileCoord tc;
+    T gx[2][DMAX];
+#pragma unroll
+    for (int i = 0; i < 2; ++i)
+#pragma unroll
+        for (int k = 0; k < DMAX; ++k) gx[i][k] = T(0);
+    T gm[2], xr[2][DMAX];
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+        gm[i] = (tc.r0 + i < nvalid) ? g_m0[p0 + tc.r0 + i] : T(0);
+#pragma unroll
+        for (int k = 0; k < DMAX; ++k) xr[i][k] = xs[(tc.r0 + i) * DMAX + k];
+    }
+    for (int cb = 0; cb < n; cb += kOB) {
+        T acc[2][4];
+        zero_acc(acc);
+        const int nc = min(kOB, n - cb);
+        // g_K[r][j] = sum_{i >= j} gU[r][i] Linv[i][j]: rows i >= cb of Linv, columns cb..cb+63
+        gemm_block<T>(Gt + (size_t)cb * kRS, n - cb, g.linv + (size_t)cb * n, n, cb, nc, stage, tc, acc);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int c = cb + tc.c0 + j;
+            if (c < n) {
+                const T al = __ldg(g.alpha + c);
+                T tj[DMAX];
+#pragma unroll
+                for (int k = 0; k < DMAX; ++k) tj[k] = k < d ? __ldg(g.train_x + (size_t)c * d + k) * __ldg(g.inv_ls + k) : T(0);
+#pragma unroll
+                for (int i = 0; i < 2; ++i) {
+                    T sd[DMAX], r2 = T(0);
+#pragma unroll
+                    for (int k = 0; k < DMAX; ++k) { sd[k] = xr[i][k] - tj[k]; r2 = fma(sd[k], sd[k], r2); }
+                    T kap, gc;
+                    kernel_profile<T>(g.kernel_id, r2, kap, gc);
+                    const T coef = (acc[i][j] + gm[i] * al) * g.amp * gc;
+#pragma unroll
+                    for (int k = 0; k < DMAX; ++k) gx[i][k] = fma(coef, sd[k], gx[i][k]);
+                }
+            }
+        }
+    }
+    // reduce over the 4 lanes (lane & 3) and the 4 column warps (warp & 3) that share a row
+#pragma unroll
+    for (int i = 0; i < 2; ++i)
+#pragma unroll
+        for (int k = 0; k < DMAX; ++k) { gx[i][k] += shfl_xor_(gx[i][k], 1); gx[i][k] += shfl_xor_(gx[i][k], 2); }
+    __syncthreads();
+    if ((tid & 3) == 0) {
+        const int cw = (tid >> 5) & 3;
+#pragma unroll
+        for (int i = 0; i < 2; ++i)
+#pragma unroll
+            for (int k = 0; k < DMAX; ++k) red[(cw * kR + tc.r0 + i) * DMAX + k] = gx[i][k];
+    }
+    __syncthreads();
+    for (int e = tid; e < kR * DMAX; e += kNT) {
+        const int r = e / DMAX, k = e - r * DMAX;
+        if (r < nvalid && k < d) {
+            const T s = red[e] + red[kR * DMAX + e] + red[2 * kR * DMAX + e] + red[3 * kR * DMAX + e];
+            g_pts[(p0 + r) * d + k] += s * __ldg(g.inv_ls + k);
+        }
+    }
+}
+
+template <typename T, int DMAX> static size_t whiten_smem(int n, bool bwd) {
+    const size_t npad = (n + 3) & ~3;
+    return (npad * kRS + 2 * kKC * kOB + kR * DMAX + (bwd ? 4 * kR * DMAX : 8 * kR)) * sizeof(T);
+}
+
+
+// ------------------------------------------------------------------ tree bookkeeping
+struct TreeDev {
+    int n_levels, obs_noise;
+    long long cnt[NMB_MAX_LEVELS], off[NMB_MAX_LEVELS + 1];
+    const void* base[NMB_MAX_LEVELS];
+    double action_base_mean;
+};
+
+static int make_tree(const nmb_tree_t* t, TreeDev& o) {
+    NMB_REQUIRE(t && t->n_levels >= 1 && t->n_levels <= NMB_MAX_LEVELS, NMB_EINVAL, "mc tree: n_levels");
+    o.n_levels = t->n_levels; o.obs_noise = t->obs_noise_fantasy; o.action_base_mean = t->action_base_mean;
+    o.off[0] = 0;
+    for (int s = 0; s < t->n_levels; ++s) {
+        NMB_REQUIRE(t->counts[s] >= 1 && (s == 0 || t->counts[s] % t->counts[s - 1] == 0), NMB_EINVAL,
+                    "mc tree: level %d has %lld nodes", s, (long long)t->counts[s]);
+        NMB_REQUIRE(s == t->n_levels - 1 || t->base[s], NMB_EINVAL, "mc tree: level %d has no base samples", s);
+        o.cnt[s] = t->counts[s]; o.off[s + 1] = o.off[s] + t->counts[s]; o.base[s] = t->base[s];
+    }
+    return 0;
+}
+
+template <typename T> struct StateDev {
+    const T* pts;
+    T *U, *m0, *q, *W, *var, *mean, *cst, *sig, *bv, *leaf_loss;
+    T *Gw, *Gdot, *Gc, *Gb, *Gq, *Gm0, *gU, *g_pts;
+};
+template <typename T> static StateDev<T> to_dev(const nmb_tree_state_t& s) {
+    StateDev<T> o;
+    o.pts = (const T*)s.pts; o.U = (T*)s.U; o.m0 = (T*)s.m0; o.q = (T*)s.q; o.W = (T*)s.W; o.var = (T*)s.var;
+    o.mean = (T*)s.mean; o.cst = (T*)s.cst; o.sig = (T*)s.sig; o.bv = (T*)s.bv; o.leaf_loss = (T*)s.leaf_loss;
+    o.Gw = (T*)s.Gw; o.Gdot = (T*)s.Gdot; o.Gc = (T*)s.Gc; o.Gb = (T*)s.Gb; o.Gq = (T*)s.Gq; o.Gm0 = (T*)s.Gm0;
+    o.gU = (T*)s.gU; o.g_pts = (T*)s.g_pts;
+    return o;
+}
+
+// sqrt of a 1x1 covariance with GPyTorch's psd_safe_cholesky jitter rule:
+// var <= 0 -> retry with var + 1e-8 (1e-6 in FP32), x10, x100.
+template <typename T> __device__ __forceinline__ T safe_sigma(T var, T& jit) {
+    jit = T(0);
+    if (var > T(0)) return Num<T>::sqrt(var);
+    T j = Num<T>::kChJitter;
+    for (int i = 0; i < 3; ++i, j *= T(10)) {
+        if (var + j > T(0)) { jit = j; return Num<T>::sqrt(var + j); }
+    }
+    jit = j;
+    return T(0);
+}
+
+// amp * kappa(a, b) and its gradient w.r.t. a (scaled points are formed here)
+template <typename T, int DMAX>
+__device__ __forceinline__ T kern_pair(const GpDev<T>& g, const T* __restrict__ a, const T* __restrict__ b, T (&ga)[DMAX]) {
+    T sd[DMAX], r2 = T(0);
+#pragma unroll
+    for (int k = 0; k < DMAX; ++k) {
+        sd[k] = k < g.d ? (a[k] - b[k]) * __ldg(g.inv_ls + k) : T(0);
+        r2 = fma(sd[k], sd[k], r2);
+    }
+    T kap, gc;
+    kernel_profile<T>(g.kernel_id, r2, kap, gc);
+#pragma unroll
+    for (int k = 0; k < DMAX; ++k) ga[k] = k < g.d ? g.amp * gc * sd[k] * __ldg(g.inv_ls + k) : T(0);
+    return g.amp * kap;
+}
+
+// ------------------------------------------------------------------ level forward: warp per node
+template <typename T, int DMAX>
+__global__ void __launch_bounds__(256) level_fwd_kernel(GpDev<T> g, const __grid_constant__ TreeDev tr, StateDev<T> st, int s) {
+    const int lane = threadIdx.x & 31;
+    const long long warp0 = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
+    const int NL = tr.n_levels;
+    const bool leaf = (s == NL - 1);
+    for (long long i = warp0; i < tr.cnt[s]; i += nwarps) {
+        const long long node = tr.off[s] + i;
+        const T* ux = st.U + (size_t)node * g.ldu;
+        T w[NMB_MAX_LEVELS];
+        T sumw2 = T(0), mb = T(0);
+        // b of this node's branch under its parent's model: sigma_parent * z_base[f] / c_parent
+        T bown = T(0);
+        if (s > 0) {
+            const long long par = tr.off[s - 1] + i % tr.cnt[s - 1];
+            const T zb = ((const T*)tr.base[s - 1])[i / tr.cnt[s - 1]];
+            bown = tr.obs_noise ? zb : st.sig[par] * zb / st.cst[par];
+        }
+        for (int t = 0; t < s; ++t) {
+            const long long anc = tr.off[t] + i % tr.cnt[t];
+            const T* uz = st.U + (size_t)anc * g.ldu;
+            T dot = T(0);
+            for (int k = lane; k < g.n; k += 32) dot = fma(ux[k], uz[k], dot);
+            dot = warp_sum(dot);
+            T ga[DMAX];
+            const T kx = kern_pair<T, DMAX>(g, st.pts + node * g.d, st.pts + anc * g.d, ga);
+            T acc = kx - dot;
+            const T* wz = st.W + (size_t)anc * NL;
+            for (int t2 = 0; t2 < t; ++t2) acc = fma(-wz[t2], w[t2], acc);
+            w[t] = acc / st.cst[anc];
+            sumw2 = fma(w[t], w[t], sumw2);
+            mb = fma(w[t], t == s - 1 ? bown : st.bv[tr.off[t + 1] + i % tr.cnt[t + 1]], mb);
+        }
+        const T var = g.amp - st.q[node] - sumw2;
+        const T mean = g.mean_const + st.m0[node] + mb;
+        T jit;
+        const T sig = safe_sigma<T>(var, jit);
+        if (lane == 0) {
+            for (int t = 0; t < s; ++t) st.W[(size_t)node * NL + t] = w[t];
+            st.var[node] = var; st.mean[node] = mean; st.sig[node] = sig;
+            st.cst[node] = Num<T>::sqrt(var + g.noise);
+            if (leaf) st.leaf_loss[i] = -(mean + sig * (T)tr.action_base_mean);
+        }
+        if (s > 0 && lane == 0) st.bv[node] = bown;
+    }
+}
+
+// ------------------------------------------------------------------ level backward: thread per node
+template <typename T, int DMAX>
+__global__ void __launch_bounds__(128) level_bwd_kernel(GpDev<T> g, const __grid_constant__ TreeDev tr, StateDev<T> st, int s,
+                                                        const T* __restrict__ g_leaf, const T* __restrict__ g_leaf_sig) {
+    const int NL = tr.n_levels;
+    const bool leaf = (s == NL - 1);
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < tr.cnt[s];
+         i += (long long)gridDim.x * blockDim.x) {
+        const long long node = tr.off[s] + i;
+        const T sig = st.sig[node], c = st.cst[node];
+        T g_var = T(0), g_mean = T(0);
+        if (leaf) {
+            // HES: g_leaf is the adjoint of leaf_loss = -(mean + sigma zbar); otherwise (g_leaf, g_leaf_sig)
+            // are the adjoints of the leaf's (mean, sigma)
+            const T gl = g_leaf[i];
+            g_mean = g_leaf_sig ? gl : -gl;
+            const T g_sig = g_leaf_sig ? g_leaf_sig[i] : -gl * (T)tr.action_base_mean;
+            g_var = sig > T(0) ? g_sig / (T(2) * sig) : T(0);
+        } else {
+            // c = sqrt(var + noise) is used by every descendant's division; sigma only through b = sigma z / c
+            T g_c = st.Gc[node], g_sig = T(0);
+            if (!tr.obs_noise) {
+                const long long nf = tr.cnt[s + 1] / tr.cnt[s];
+                const T* zb = (const T*)tr.base[s];
+                for (long long f = 0; f < nf; ++f) {
+                    const T gb = st.Gb[tr.off[s + 1] + i + f * tr.cnt[s]];
+                    g_sig = fma(gb, zb[f] / c, g_sig);
+                    g_c = fma(-gb, sig * zb[f] / (c * c), g_c);
+                }
+            }
+            g_var = g_c / (T(2) * c) + (sig > T(0) ? g_sig / (T(2) * sig) : T(0));
+        }
+        T w[NMB_MAX_LEVELS], gw[NMB_MAX_LEVELS];
+        for (int t = 0; t < s; ++t) {
+            w[t] = st.W[(size_t)node * NL + t];
+            const long long bn = tr.off[t + 1] + i % tr.cnt[t + 1];
+            gw[t] = st.Gw[(size_t)node * NL + t] - T(2) * w[t] * g_var + st.bv[bn] * g_mean;
+            if (g_mean != T(0)) atomicAdd(st.Gb + bn, w[t] * g_mean);
+        }
+        T gx[DMAX];
+#pragma unroll
+        for (int k = 0; k < DMAX; ++k) gx[k] = T(0);
+        for (int t = s - 1; t >= 0; --t) {
+            const long long anc = tr.off[t] + i % tr.cnt[t];
+            const T ct = st.cst[anc];
+            const T g_acc = gw[t] / ct;
+            atomicAdd(st.Gc + anc, -gw[t] * w[t] / ct);
+            st.Gdot[(size_t)node * NL + t] = -g_acc;
+            T ga[DMAX];
+            kern_pair<T, DMAX>(g, st.pts + node * g.d, st.pts + anc * g.d, ga);
+#pragma unroll
+            for (int k = 0; k < DMAX; ++k) {
+                if (k < g.d) {
+                    gx[k] = fma(g_acc, ga[k], gx[k]);
+                    atomicAdd(st.g_pts + anc * g.d + k, -g_acc * ga[k]);
+                }
+            }
+            const T* wz = st.W + (size_t)anc * NL;
+            for (int t2 = 0; t2 < t; ++t2) {
+                atomicAdd(st.Gw + (size_t)anc * NL + t2, -g_acc * w[t2]);
+                gw[t2] = fma(-g_acc, wz[t2], gw[t2]);
+            }
+        }
+        st.Gq[node] = -g_var;
+        st.Gm0[node] = g_mean;
+#pragma unroll
+        for (int k = 0; k < DMAX; ++k) if (k < g.d) atomicAdd(st.g_pts + node * g.d + k, gx[k]);
+    }
+}
+
+// ------------------------------------------------------------------ gU gather: warp per node
+template <typename T>
+__global__ void __launch_bounds__(256) gather_gu_kernel(GpDev<T> g, const __grid_constant__ TreeDev tr, StateDev<T> st) {
+    const int lane = threadIdx.x & 31;
+    const long long warp0 = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
+    const int NL = tr.n_levels;
+    const long long total = tr.off[NL];
+    // heavy (root-side) nodes first: node order is already level 0, 1, ...
+    for (long long node = warp0; node < total; node += nwarps) {
+        int s = 0;
+        while (node >= tr.off[s + 1]) ++s;
+        const long long i = node - tr.off[s];
+        const T* ux = st.U + (size_t)node * g.ldu;
+        T* out = st.gU + (size_t)node * g.ldu;
+        const T gq2 = T(2) * st.Gq[node];
+        for (int k0 = lane; k0 < g.n; k0 += 32 * 4) {
+            // 4 strided elements per lane per pass keeps the descendant loop's loads independent
+            T a[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) { const int k = k0 + 32 * u; a[u] = k < g.n ? gq2 * ux[k] : T(0); }
+            for (int t = 0; t < s; ++t) {
+                const T gd = st.Gdot[(size_t)node * NL + t];
+                const T* uz = st.U + (size_t)(tr.off[t] + i % tr.cnt[t]) * g.ldu;
+#pragma unroll
+                for (int u = 0; u < 4; ++u) { const int k = k0 + 32 * u; if (k < g.n) a[u] = fma(gd, uz[k], a[u]); }
+            }
+            for (int s2 = s + 1; s2 < NL; ++s2) {
+                for (long long y = i; y < tr.cnt[s2]; y += tr.cnt[s]) {
+                    const long long dn = tr.off[s2] + y;
+                    const T gd = st.Gdot[(size_t)dn * NL + s];
+                    const T* uy = st.U + (size_t)dn * g.ldu;
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) { const int k = k0 + 32 * u; if (k < g.n) a[u] = fma(gd, uy[k], a[u]); }
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) { const int k = k0 + 32 * u; if (k < g.n) out[k] = a[u]; }
+        }
+    }
+}
+
+// ------------------------------------------------------------------ per-restart mean over leaves
+template <typename T>
+__global__ void __launch_bounds__(256) restart_mean_kernel(const T* __restrict__ leaf, long long n_leaf, long long n_r,
+                                                           T* __restrict__ out) {
+    // one warp per restart: lanes stride over its leaves, shuffle tree reduction
+    const int lane = threadIdx.x & 31;
+    const long long r = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (r >= n_r) return;
+    const long long per = n_leaf / n_r;
+    T acc = T(0);
+    for (long long f = lane; f < per; f += 32) acc += leaf[r + f * n_r];
+    acc = warp_sum(acc);
+    if (lane == 0) out[r] = acc / (T)per;
+}
+
+// ------------------------------------------------------------------ baseline utilities (q = 1)
+template <typename T>
+__global__ void __launch_bounds__(256) utility_kernel(int which, T best_f, T beta, const T* __restrict__ mean,
+                                                      const T* __restrict__ sig, long long n, const T* __restrict__ base,
+                                                      int S, T* __restrict__ value, T* __restrict__ d_mean,
+                                                      T* __restrict__ d_sig) {
+    // one warp per point, lanes stride over the S base samples
+    const int lane = threadIdx.x & 31;
+    const long long p = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (p >= n) return;
+    const T m = mean[p], sg = sig[p];
+    T v = T(0), dm = T(0), ds = T(0);
+    if (which == 3) {
+        // mu^ = mean_s y = m + sg * zbar;  u_s = mu^ + k |y_s - mu^| = mu^ + k sg |z_s - zbar|
+        T zs = T(0);
+        for (int a = lane; a < S; a += 32) zs += base[a];
+        const T zbar = warp_sum(zs) / (T)S;
+        const T kq = Num<T>::sqrt(beta * Num<T>::kPi / T(2));
+        T ab = T(0);
+        for (int a = lane; a < S; a += 32) ab += Num<T>::fabs(sg * (base[a] - zbar));
+        ab = warp_sum(ab) / (T)S;
+        v = m + sg * zbar + kq * ab;
+        dm = T(1);
+        ds = zbar + (sg != T(0) ? kq * ab / sg : T(0));
+    } else {
+        for (int a = lane; a < S; a += 32) {
+            const T z = base[a];
+            const T y = fma(sg, z, m);
+            if (which == 0) {
+                if (y - best_f > T(0)) { v += y - best_f; dm += T(1); ds += z; }
+            } else if (which == 1) {
+                const T sgm = sigmoid_((y - best_f) / T(1e-3));
+                const T dd = sgm * (T(1) - sgm) / T(1e-3);
+                v += sgm; dm += dd; ds += dd * z;
+            } else {
+                v += y; dm += T(1); ds += z;
+            }
+        }
+        v = warp_sum(v) / (T)S; dm = warp_sum(dm) / (T)S; ds = warp_sum(ds) / (T)S;
+    }
+    if (lane == 0) { value[p] = v; d_mean[p] = dm; d_sig[p] = ds; }
+}
+}  // namespace nmb
+
+using namespace nmb;
+
+static int validate_gp(const nmb_gp_t* gp, int dtype, const char* who) {
+    NMB_REQUIRE(gp, NMB_EINVAL, "%s: null gp", who);
+    NMB_REQUIRE(dtype == NMB_F64 || dtype == NMB_F32, NMB_EINVAL, "%s: dtype %d", who, dtype);
+    NMB_REQUIRE(gp->d >= 1 && gp->d <= NMB_MAX_DIM, NMB_ELIMIT, "%s: d=%d outside [1,%d]", who, gp->d, NMB_MAX_DIM);
+    NMB_REQUIRE(gp->n >= 1 && gp->ldu >= gp->n, NMB_EINVAL, "%s: n=%d ldu=%d", who, gp->n, gp->ldu);
+    NMB_REQUIRE(gp->kernel_id >= 0 && gp->kernel_id <= 3, NMB_EINVAL, "%s: kernel_id %d", who, gp->kernel_id);
+    NMB_REQUIRE(gp->train_x && gp->inv_ls && gp->linv && gp->linv_t && gp->alpha, NMB_EINVAL, "%s: null gp array", who);
+    return 0;
+}
+
+#define NMB_MC_D(d, CALL)                 \
+    do {                                  \
+        if ((d) <= 2) { CALL(2); }        \
+        else if ((d) <= 4) { CALL(4); }   \
+        else if ((d) <= 8) { CALL(8); }   \
+        else { CALL(16); }                \
+    } while (0)
+
+template <typename T>
+static int launch_whiten(const nmb_gp_t* gp, bool bwd, const void* pts, int64_t n_pts, void* U, void* m0, void* q,
+                         const void* gU, const void* g_m0, void* g_pts, cudaStream_t st) {
+    GpDev<T> g = to_dev<T>(*gp);
+    const unsigned grid = (unsigned)((n_pts + kR - 1) / kR);
+#define NMB_WH(DM)                                                                                              \
+    {                                                                                                           \
+        const size_t smem = whiten_smem<T, DM>(gp->n, bwd);                                                     \
+        NMB_REQUIRE(smem <= 227 * 1024, NMB_ELIMIT, "gp whiten: n=%d training points exceed shared memory", gp->n); \
+        if (!bwd) {                                                                                             \
+            NMB_CUDA(cudaFuncSetAttribute(whiten_fwd_kernel<T, DM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+            whiten_fwd_kernel<T, DM><<<grid, kNT, smem, st>>>(g, (const T*)pts, n_pts, (T*)U, (T*)m0, (T*)q);   \
+        } else {                                                                                                \
+            NMB_CUDA(cudaFuncSetAttribute(whiten_bwd_kernel<T, DM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+            whiten_bwd_kernel<T, DM><<<grid, kNT, smem, st>>>(g, (const T*)pts, n_pts, (const T*)gU, (const T*)g_m0, (T*)g_pts); \
+        }                                                                                                       \
+    }
+    NMB_MC_D(gp->d, NMB_WH);
+#undef NMB_WH
+    NMB_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int nmb_gp_whiten_fwd(const nmb_gp_t* gp, int dtype, const void* pts, int64_t n_pts, void* U, void* m0,
+                                 void* q, void* stream) {
+    int rc = validate_gp(gp, dtype, "nmb_gp_whiten_fwd");
+    if (rc) return rc;
+    NMB_REQUIRE(pts && U && m0 && q && n_pts >= 0, NMB_EINVAL, "nmb_gp_whiten_fwd: null argument");
+    if (n_pts == 0) return 0;
+    cudaStream_t st = (cudaStream_t)stream;
+    return dtype == NMB_F64 ? launch_whiten<double>(gp, false, pts, n_pts, U, m0, q, nullptr, nullptr, nullptr, st)
+                            : launch_whiten<float>(gp, false, pts, n_pts, U, m0, q, nullptr, nullptr, nullptr, st);
+}
+
+extern "C" int nmb_gp_whiten_bwd(const nmb_gp_t* gp, int dtype, const void* pts, int64_t n_pts, const void* gU,
+                                 const void* g_m0, void* g_pts, void* stream) {
+    int rc = validate_gp(gp, dtype, "nmb_gp_whiten_bwd");
+    if (rc) return rc;
+    NMB_REQUIRE(pts && gU && g_m0 && g_pts && n_pts >= 0, NMB_EINVAL, "nmb_gp_whiten_bwd: null argument");
+    if (n_pts == 0) return 0;
+    cudaStream_t st = (cudaStream_t)stream;
+    return dtype == NMB_F64 ? launch_whiten<double>(gp, true, pts, n_pts, nullptr, nullptr, nullptr, gU, g_m0, g_pts, st)
+                            : launch_whiten<float>(gp, true, pts, n_pts, nullptr, nullptr, nullptr, gU, g_m0, g_pts, st);
+}
+
+static unsigned warp_grid(long long n_warps) {
+    long long b = (n_warps + 7) / 8;
+    const long long cap = (long long)sm_count() * 16;
+    return (unsigned)(b < 1 ? 1 : (b > cap ? cap : b));
+}
+
+template <typename T>
+static int launch_level(const nmb_gp_t* gp, const TreeDev& tr, const nmb_tree_state_t* state, int level, bool bwd,
+                        const void* g_leaf, const void* g_leaf_sig, cudaStream_t st) {
+    GpDev<T> g = to_dev<T>(*gp);
+    StateDev<T> sd = to_dev<T>(*state);
+    if (!bwd) {
+#define NMB_LF(DM) level_fwd_kernel<T, DM><<<warp_grid(tr.cnt[level]), 256, 0, st>>>(g, tr, sd, level)
+        NMB_MC_D(gp->d, NMB_LF);
+#undef NMB_LF
+    } else {
+        long long b = (tr.cnt[level] + 127) / 128;
+        const long long cap = (long long)sm_count() * 16;
+        const unsigned grid = (unsigned)(b > cap ? cap : b);
+#define NMB_LB(DM) level_bwd_kernel<T, DM><<<grid, 128, 0, st>>>(g, tr, sd, level, (const T*)g_leaf, (const T*)g_leaf_sig)
+        NMB_MC_D(gp->d, NMB_LB);
+#undef NMB_LB
+    }
+    NMB_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int nmb_mc_level_fwd(const nmb_gp_t* gp, const nmb_tree_t* tree, const nmb_tree_state_t* st, int dtype,
+                                int level, void* stream) {
+    int rc = validate_gp(gp, dtype, "nmb_mc_level_fwd");
+    if (rc) return rc;
+    TreeDev tr;
+    rc = make_tree(tree, tr);
+    if (rc) return rc;
+    NMB_REQUIRE(st && level >= 0 && level < tr.n_levels, NMB_EINVAL, "nmb_mc_level_fwd: level %d", level);
+    NMB_REQUIRE(st->pts && st->U && st->m0 && st->q && st->W && st->var && st->mean && st->cst && st->sig && st->bv,
+                NMB_EINVAL, "nmb_mc_level_fwd: null state array");
+    NMB_REQUIRE(level < tr.n_levels - 1 || st->leaf_loss, NMB_EINVAL, "nmb_mc_level_fwd: null leaf_loss");
+    cudaStream_t s = (cudaStream_t)stream;
+    return dtype == NMB_F64 ? launch_level<double>(gp, tr, st, level, false, nullptr, nullptr, s)
+                            : launch_level<float>(gp, tr, st, level, false, nullptr, nullptr, s);
+}
+
+extern "C" int nmb_mc_level_bwd(const nmb_gp_t* gp, const nmb_tree_t* tree, const nmb_tree_state_t* st, int dtype,
+                                int level, const void* g_leaf, const void* g_leaf_sig, void* stream) {
+    int rc = validate_gp(gp, dtype, "nmb_mc_level_bwd");
+    if (rc) return rc;
+    TreeDev tr;
+    rc = make_tree(tree, tr);
+    if (rc) return rc;
+    NMB_REQUIRE(st && level >= 0 && level < tr.n_levels, NMB_EINVAL, "nmb_mc_level_bwd: level %d", level);
+    NMB_REQUIRE(st->Gw && st->Gdot && st->Gc && st->Gb && st->Gq && st->Gm0 && st->g_pts, NMB_EINVAL,
+                "nmb_mc_level_bwd: null adjoint array");
+    NMB_REQUIRE(level < tr.n_levels - 1 || g_leaf, NMB_EINVAL, "nmb_mc_level_bwd: null g_leaf");
+    cudaStream_t s = (cudaStream_t)stream;
+    return dtype == NMB_F64 ? launch_level<double>(gp, tr, st, level, true, g_leaf, g_leaf_sig, s)
+                            : launch_level<float>(gp, tr, st, level, true, g_leaf, g_leaf_sig, s);
+}
+
+extern "C" int nmb_mc_gather_gu(const nmb_gp_t* gp, const nmb_tree_t* tree, const nmb_tree_state_t* st, int dtype,
+                                void* stream) {
+    int rc = validate_gp(gp, dtype, "nmb_mc_gather_gu");
+    if (rc) return rc;
+    TreeDev tr;
+    rc = make_tree(tree, tr);
+    if (rc) return rc;
+    NMB_REQUIRE(st && st->U && st->gU && st->Gq && st->Gdot, NMB_EINVAL, "nmb_mc_gather_gu: null array");
+    cudaStream_t s = (cudaStream_t)stream;
+    const unsigned grid = warp_grid(tr.off[tr.n_levels]);
+    if (dtype == NMB_F64) gather_gu_kernel<double><<<grid, 256, 0, s>>>(to_dev<double>(*gp), tr, to_dev<double>(*st));
+    else gather_gu_kernel<float><<<grid, 256, 0, s>>>(to_dev<float>(*gp), tr, to_dev<float>(*st));
+    NMB_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int nmb_tree_restart_mean(int dtype, const void* leaf, int64_t n_leaf, int64_t n_r, void* out, void* stream) {
+    NMB_REQUIRE(leaf && out && n_r >= 1 && n_leaf >= n_r && n_leaf % n_r == 0, NMB_EINVAL,
+                "nmb_tree_restart_mean: bad arguments");
+    cudaStream_t s = (cudaStream_t)stream;
+    const unsigned grid = (unsigned)((n_r * 32 + 255) / 256);
+    if (dtype == NMB_F64) restart_mean_kernel<double><<<grid, 256, 0, s>>>((const double*)leaf, n_leaf, n_r, (double*)out);
+    else if (dtype == NMB_F32) restart_mean_kernel<float><<<grid, 256, 0, s>>>((const float*)leaf, n_leaf, n_r, (float*)out);
+    else { set_error("nmb_tree_restart_mean: dtype %d", dtype); return NMB_EINVAL; }
+    NMB_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int nmb_mc_utility(int dtype, int which, double best_f, double beta, const void* mean, const void* sig,
+                              int64_t n, const void* base, int n_samples, void* value, void* d_mean, void* d_sig,
+                              void* stream) {
+    NMB_REQUIRE(mean && sig && base && value && d_mean && d_sig && n >= 0 && n_samples >= 1, NMB_EINVAL,
+                "nmb_mc_utility: bad arguments");
+    NMB_REQUIRE(which >= 0 && which <= 3, NMB_EINVAL, "nmb_mc_utility: which=%d", which);
+    if (n == 0) return 0;
+    cudaStream_t s = (cudaStream_t)stream;
+    const unsigned grid = (unsigned)((n * 32 + 255) / 256);
+    if (dtype == NMB_F64)
+        utility_kernel<double><<<grid, 256, 0, s>>>(which, best_f, beta, (const double*)mean, (const double*)sig, n,
+                                                    (const double*)base, n_samples, (double*)value, (double*)d_mean,
+                                                    (double*)d_sig);
+    else if (dtype == NMB_F32)
+        utility_kernel<float><<<grid, 256, 0, s>>>(which, (float)best_f, (float)beta, (const float*)mean,
+                                                   (const float*)sig, n, (const float*)base, n_samples, (float*)value,
+                                                   (float*)d_mean, (float*)d_sig);
+    else { set_error("nmb_mc_utility: dtype %d", dtype); return NMB_EINVAL; }
+    NMB_LAUNCH_CHECK();
+    return 0;
+}
