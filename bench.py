@@ -257,12 +257,13 @@ def run_b200(args, rank, world, local_rank):
         # per-kernel timing of the same steps (eager launches, events on the launching stream)
         kern = time_kernels(loop, stream, min(args.steps, 20)) if rank == 0 else {}
         # ---- e2e: the public class API with HOST buffers, copies inside the timed region
-        e2e = run_e2e(args, gp, path, net, prev_x, prev_y, prev_h, budget, dev, stream, barrier)
+        e2e = run_e2e_loop(args, loop, prev_x, prev_y, prev_h, stream, barrier)
+        e2e_api = run_e2e(args, gp, path, net, prev_x, prev_y, prev_h, budget, dev, stream, barrier)
     clk = clocks.stop() if rank == 0 else None
-    t = torch.tensor([ms_total, e2e["ms_total"]], dtype=torch.float64, device=dev)
+    t = torch.tensor([ms_total, e2e["ms_total"], e2e_api["ms_total"]], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_total, e2e_ms = float(t[0]), float(t[1])
+    ms_total, e2e_ms, api_ms = float(t[0]), float(t[1]), float(t[2])
     st = loop.read_state()
     assert st.step >= args.steps and not st.done, "timed steps did not run"
     if rank != 0:
@@ -304,8 +305,14 @@ def run_b200(args, rank, world, local_rank):
         "roofline": roof, "cpu_baseline": cpu,
         "e2e": {"value": nodes_per_step * world * e2e["steps"] / (e2e_ms * 1e-3), "unit": UNIT,
                 "h2d_bytes_per_step": e2e["h2d"], "d2h_bytes_per_step": e2e["d2h"], "ms_per_step": e2e_ms / e2e["steps"],
-                "api": "acqfs.qMultiStepHEntropySearch.forward x2 + torch.autograd.grad + AdamW (eager, per-step "
-                       "H2D of prev_X/prev_y/prev_hid_state from pinned memory, D2H of loss/cost)"},
+                "api": "TSAMLoop.step_host - the per-iteration engine of Actor.query (HES-TS-AM): per-step H2D of "
+                       "prev_X/prev_y/prev_hid_state from pinned memory, one iteration (same launches as `value`), "
+                       "D2H of the per-restart loss/cost, stream synchronise",
+                "class_api_eager": {
+                    "value": nodes_per_step * world * e2e_api["steps"] / (api_ms * 1e-3), "unit": UNIT,
+                    "ms_per_step": api_ms / e2e_api["steps"],
+                    "api": "acqfs.qMultiStepHEntropySearch.forward x2 + torch.autograd.grad + torch AdamW, eager, "
+                           "same per-step H2D / D2H"}},
         "gpu_launches": loop.n_launches_per_iter * args.steps, "clocks": clk,
     }
     print(json.dumps(line), flush=True)
@@ -342,6 +349,25 @@ def time_kernels(loop, stream, n_steps):
     flops = {"ts_rollout_fwd": nodes * (2 * f_net + 1.5 * f_ts), "ts_rollout_bwd": nodes * f_net,
              "policy_wgrad": nodes * f_net, "objective+snapshot": 0.0, "adamw": 0.0}
     return {k: {"ms": sum(v) / len(v), "flops": flops.get(k, 0.0)} for k, v in acc.items()}
+
+
+def run_e2e_loop(args, loop, prev_x, prev_y, prev_h, stream, barrier):
+    """The step of `value` driven from HOST buffers: pinned inputs -> HBM, one iteration, loss/cost -> host."""
+    hx, hy, hh = prev_x.pin_memory(), prev_y.pin_memory(), prev_h.pin_memory()
+    N = hx.shape[0]
+    out_host = torch.empty(2, N, dtype=torch.float64).pin_memory()
+    for _ in range(3):
+        loop.step_host(hx, hy, hh, out_host)
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(args.steps):
+        loop.step_host(hx, hy, hh, out_host)
+    e1.record(stream)
+    barrier()
+    assert torch.isfinite(out_host).all()
+    h2d = (hx.numel() + hy.numel() + hh.numel()) * 8
+    return dict(ms_total=e0.elapsed_time(e1), steps=args.steps, h2d=h2d, d2h=out_host.numel() * 8)
 
 
 def run_e2e(args, gp, path, net, prev_x, prev_y, prev_h, budget, dev, stream, barrier):
@@ -384,7 +410,7 @@ def run_e2e(args, gp, path, net, prev_x, prev_y, prev_h, budget, dev, stream, ba
         out_host[1].copy_(rd["acqf_cost"].detach(), non_blocking=True)
         stream.synchronize()                    # the reference reads loss / cost on the host every iteration
 
-    steps = max(5, min(args.steps, 50))
+    steps = max(5, min(args.steps, 20))
     for _ in range(3):
         step()
     barrier()

@@ -178,6 +178,24 @@ class TSAMLoop:
                 break
         return self.read_state()
 
+    def step_host(self, host_x: Tensor, host_y: Tensor, host_h: Tensor, host_out: Tensor) -> None:
+        """One Adam iteration driven from HOST buffers (the reference reads loss / cost on the host every
+        iteration, actor.py:580-581,618-619): pinned ``prev_X / prev_y / prev_hid_state`` -> HBM, one graph
+        replay (or eager launch sequence), this iteration's per-restart loss and cost -> pinned ``host_out[2, N]``,
+        then a stream synchronise.  The graph reads the inputs through fixed device buffers, so the copies
+        land in place."""
+        px, py, ph = self.prev
+        px.copy_(host_x.view_as(px), non_blocking=True)
+        py.copy_(host_y.view_as(py), non_blocking=True)
+        ph.copy_(host_h.view_as(ph), non_blocking=True)
+        if self.graph is not None:
+            self.graph.replay()
+        else:
+            self._iteration()
+        host_out[0].copy_(self.main.loss, non_blocking=True)
+        host_out[1].copy_(self.main.cost, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+
     # ------------------------------------------------------------------ results (actor.py:661-733)
     def result(self):
         tot = self.best_loss + self.best_cost + self.best_KL
