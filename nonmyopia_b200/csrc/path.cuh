@@ -32,7 +32,7 @@ template <typename T> inline PathDev<T> to_dev(const nmb_path_t& p) {
 
 // x: the point (registers, DMAX padded), s: path index, (lane, nl): this thread's slot
 // in its group.  Outputs are partial: y_part excludes mean_const.
-template <typename T, int DMAX>
+template <typename T, int DMAX, bool GRAD = true>
 __device__ __forceinline__ void path_partial(const PathDev<T>& P, const T (&x)[DMAX], int s, int lane,
                                              int nl, T& y_part, T (&g_part)[DMAX]) {
     const int d = P.d;
@@ -57,9 +57,11 @@ __device__ __forceinline__ void path_partial(const PathDev<T>& P, const T (&x)[D
         Num<T>::sincospi(u, &sn, &cs);
         const T ws = __ldg(wsin + m), wc = __ldg(wcos + m);
         acc = fma(sn, ws, fma(cs, wc, acc));
-        const T dphi = cs * ws - sn * wc;   // d/dz of (sin z ws + cos z wc)
+        if (GRAD) {
+            const T dphi = cs * ws - sn * wc;   // d/dz of (sin z ws + cos z wc)
 #pragma unroll
-        for (int k = 0; k < DMAX; ++k) gacc[k] = fma(dphi, wk[k], gacc[k]);
+            for (int k = 0; k < DMAX; ++k) gacc[k] = fma(dphi, wk[k], gacc[k]);
+        }
     }
     acc *= P.feat_scale;
     const T gs = P.feat_scale * Num<T>::kPi;
@@ -88,9 +90,11 @@ __device__ __forceinline__ void path_partial(const PathDev<T>& P, const T (&x)[D
         kernel_profile<T>(P.kernel_id, r2, kap, gc);
         const T vj = __ldg(vv + j);
         kacc = fma(kap, vj, kacc);
-        const T gv = gc * vj;
+        if (GRAD) {
+            const T gv = gc * vj;
 #pragma unroll
-        for (int k = 0; k < DMAX; ++k) kg[k] = fma(gv, sd[k], kg[k]);
+            for (int k = 0; k < DMAX; ++k) kg[k] = fma(gv, sd[k], kg[k]);
+        }
     }
     y_part = fma(P.amplitude, kacc, acc);
 #pragma unroll

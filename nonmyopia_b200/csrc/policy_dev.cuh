@@ -138,16 +138,18 @@ template <typename T> struct SaveAreas {
 };
 
 inline size_t save_elems(int d, int H, int L, long long N) {
+    // every area starts on a 16-byte boundary (even element count) so tiles can be stored as double2 / float4 pairs
     const size_t nodes = (size_t)(L + 1) * N;
-    return nodes * (d + 1) + nodes * H * 2 + (size_t)(L + 2) * N * H + nodes * H * 4 + nodes * H * 2 + nodes * d * 2 +
-           nodes + nodes * d + nodes * H * 8;
+    auto ev = [](size_t n) { return (n + 1) & ~(size_t)1; };
+    return ev(nodes * (d + 1)) + nodes * H * 2 + (size_t)(L + 2) * N * H + nodes * H * 4 + nodes * H * 2 +
+           ev(nodes * d) * 2 + ev(nodes) + ev(nodes * d) + nodes * H * 8;
 }
 
 template <typename T> inline SaveAreas<T> carve_save(void* base, int d, int H, int L, long long N) {
     SaveAreas<T> s;
     T* p = (T*)base;
     const size_t nodes = (size_t)(L + 1) * N;
-    auto take = [&](size_t n) { T* q = p; p += n; return q; };
+    auto take = [&](size_t n) { T* q = p; p += (n + 1) & ~(size_t)1; return q; };
     s.XY = take(nodes * (d + 1));
     s.EA = take(nodes * H); s.P = take(nodes * H);
     s.HS = take((size_t)(L + 2) * N * H);

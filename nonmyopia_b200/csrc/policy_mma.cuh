@@ -1,0 +1,357 @@
+// FP64 policy network on the FP64 tensor pipe (DMMA m8n8k4) with a TMA-fed weight stream.
+//
+// Why (measured on B200, tools/microbench.cu -> profiles/microbench_r01.jsonl):
+//   * DFMA and mma.sync.m8n8k4.f64 both peak at 36.9 TFLOP/s, but a DMMA moves 256 FMAs per warp
+//     instruction with 2 operand doubles per lane, whereas a 2x4 DFMA register tile needs three
+//     LDS.128 (2-4 data-pipe cycles each, broadcast does not help) per 8 DFMAs: the DFMA form of these
+//     32..64-row GEMMs is bound by the shared-memory data pipe at ~1/3 of the FP64 peak.
+//   * the weight chunks were staged through registers (LDG -> STS -> __syncthreads) with the L2
+//     latency exposed at the start of each of the 10 GEMMs of a policy step.
+// Here a producer warp streams the step's weight chunks ([32 k-rows][H cols], row stride 72 doubles so
+// the B fragments are bank-conflict free) with cp.async.bulk into a 4-stage mbarrier ring, running
+// ahead across layers and steps; consumer warps own 8-row x 32-col tiles of the CTA's rows x 64 block.
+// Activations are row-major [row][KS = H + 4] so A fragments are conflict free as well.
+// Reference semantics: amortized_network.py:97-133.
+#pragma once
+#include "policy_dev.cuh"
+
+namespace nmb {
+
+constexpr int kStages = 4;        // weight ring depth
+constexpr int kSW = 72;           // stage row stride (doubles): 72 = 8 mod 16 -> conflict-free B fragments
+constexpr int kStageElems = kKC * kSW;
+constexpr int kMaxRowsMma = 56;   // 14 consumer warps + 1 producer warp = 480 threads
+constexpr int kGemmsPerStep = 10;
+
+// ---------------------------------------------------------------- PTX helpers
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(unsigned bar, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_arrive(unsigned bar) {
+    asm volatile("{\n .reg .b64 st;\n mbarrier.arrive.shared::cta.b64 st, [%0];\n}" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(unsigned bar, unsigned bytes) {
+    asm volatile("{\n .reg .b64 st;\n mbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %1;\n}" ::"r"(bar), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
+    asm volatile(
+        "{\n .reg .pred p;\n"
+        "WAIT_%=:\n"
+        " mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        " @p bra DONE_%=;\n"
+        " bra WAIT_%=;\n"
+        "DONE_%=:\n}" ::"r"(bar), "r"(parity)
+        : "memory");
+}
+// global -> shared bulk copy (TMA, 1-D), completion counted in bytes on an mbarrier
+__device__ __forceinline__ void bulk_g2s(unsigned dst, const void* src, unsigned bytes, unsigned bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+                 "l"(src), "r"(bytes), "r"(bar)
+                 : "memory");
+}
+__device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+// barrier over the consumer warps only (id 1); the producer warp never joins it
+__device__ __forceinline__ void consumer_sync(int nthr) { asm volatile("bar.sync 1, %0;" ::"r"(nthr) : "memory"); }
+
+__device__ __forceinline__ void dmma884(double (&c)[2], double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                 : "+d"(c[0]), "+d"(c[1])
+                 : "d"(a), "d"(b));
+}
+
+// ---------------------------------------------------------------- geometry / shared memory
+struct MmaSmem {
+    double *IN, *OUT, *B0, *B1, *HA, *HB, *stage, *cost_acc;
+    unsigned full0, empty0;     // shared addresses of the mbarrier arrays
+    int rows, KS;
+    __device__ void carve(double* base, int d, int H, int rows_) {
+        rows = rows_;
+        KS = H + 4;
+        double* p = base;
+        stage = p; p += kStages * kStageElems;                 // 16-byte aligned bulk-copy destinations first
+        B0 = p; p += rows * KS;
+        B1 = p; p += rows * KS;
+        HA = p; p += rows * KS;
+        HB = p; p += rows * KS;
+        IN = p; p += (d + 1) * rows;
+        OUT = p; p += d * rows;
+        cost_acc = p; p += rows;
+        full0 = smem_u32(p);
+        empty0 = full0 + 8 * kStages;
+    }
+    static size_t bytes(int d, int H, int rows) {
+        return ((size_t)kStages * kStageElems + (size_t)4 * rows * (H + 4) + (size_t)(2 * d + 2) * rows + 2 * kStages) * 8;
+    }
+};
+
+// rows per CTA (multiple of 8, <= 56) minimising waves x rows for `n_rollouts` x N chains on `sms` SMs
+inline int mma_rows_per_cta(long long N, int n_rollouts, int sms) {
+    int best = 8;
+    double best_cost = 1e300;
+    for (int r = 8; r <= kMaxRowsMma; r += 8) {
+        const long long ctas = ((N + r - 1) / r) * n_rollouts;
+        const long long waves = (ctas + sms - 1) / sms;
+        // a CTA of r rows costs about (r + 8): fixed per-step latency of the serial layer chain
+        const double cost = (double)waves * (r + 8);
+        if (cost < best_cost - 1e-9) { best_cost = cost; best = r; }
+    }
+    return best;
+}
+
+// weight chunk source of GEMM g (0..9) of a policy step: element offset in theta_t and leading dimension
+__device__ __forceinline__ void gemm_src(const PolicyLayout& lay, bool head_a, int g, int& off, int& ldw) {
+    const int H = lay.H;
+    const int sW0 = head_a ? S_AW0 : S_XW0, sW3 = head_a ? S_AW3 : S_XW3;
+    switch (g) {
+        case 0: off = lay.off[S_WP]; ldw = H; break;
+        case 1: off = lay.off[S_WIH]; ldw = 3 * H; break;
+        case 2: off = lay.off[S_WHH]; ldw = 3 * H; break;
+        case 3: off = lay.off[S_WIH] + H; ldw = 3 * H; break;
+        case 4: off = lay.off[S_WHH] + H; ldw = 3 * H; break;
+        case 5: off = lay.off[S_WIH] + 2 * H; ldw = 3 * H; break;
+        case 6: off = lay.off[S_WHH] + 2 * H; ldw = 3 * H; break;
+        case 7: off = lay.off[sW0]; ldw = H; break;
+        case 8: off = lay.off[sW0] + H * H; ldw = H; break;
+        default: off = lay.off[sW3]; ldw = H; break;
+    }
+}
+
+// Producer warp: stream every weight chunk of steps 0..L in consumption order.
+__device__ __forceinline__ void mma_producer(const PolicyLayout& lay, const double* __restrict__ theta_t, int L,
+                                             const MmaSmem& sm) {
+    const int lane = threadIdx.x & 31;
+    const int H = lay.H;
+    const unsigned row_bytes = (unsigned)H * 8u;
+    unsigned c = 0;
+    for (int l = 0; l <= L; ++l) {
+        for (int g = 0; g < kGemmsPerStep; ++g) {
+            int off, ldw;
+            gemm_src(lay, l == L, g, off, ldw);
+            for (int k0 = 0; k0 < H; k0 += kKC, ++c) {
+                const unsigned slot = c % kStages, fill = c / kStages;
+                if (fill > 0) mbar_wait(sm.empty0 + 8 * slot, (fill - 1) & 1);
+                const int kn = min(kKC, H - k0);
+                const unsigned full = sm.full0 + 8 * slot;
+                if (lane == 0) mbar_arrive_expect_tx(full, row_bytes * (unsigned)kn);
+                __syncwarp();
+                if (lane < kn)
+                    bulk_g2s(smem_u32(sm.stage + (size_t)slot * kStageElems + lane * kSW),
+                             theta_t + off + (size_t)(k0 + lane) * ldw, row_bytes, full);
+            }
+        }
+    }
+}
+
+// Consumer-side state of one warp
+struct MmaWarp {
+    int lane, row0, col0, nthr;
+    bool active;           // this warp's 32 columns intersect [0, H)
+    unsigned chunk;        // running chunk counter (same order as the producer)
+    int fr, fk;            // fragment coordinates: lane >> 2, lane & 3
+    __device__ void init(int warp, int nthr_, int H) {
+        lane = threadIdx.x & 31;
+        row0 = (warp >> 1) * 8;
+        col0 = (warp & 1) * 32;
+        nthr = nthr_;
+        active = col0 < H;
+        chunk = 0;
+        fr = lane >> 2;
+        fk = lane & 3;
+    }
+};
+
+// acc[t] (t = 0..3: 8-column tiles of the warp's 32 columns) += A[row0.., 0..H) . W chunk stream
+// A: shared, row-major with stride KS, pointing at the first contraction column.
+__device__ __forceinline__ void mma_gemm(const MmaSmem& sm, MmaWarp& w, const double* __restrict__ A, int H,
+                                         double (&acc)[4][2]) {
+    const double* arow = A + (size_t)(w.row0 + w.fr) * sm.KS + w.fk;
+    for (int k0 = 0; k0 < H; k0 += kKC) {
+        const unsigned slot = w.chunk % kStages, fill = w.chunk / kStages;
+        mbar_wait(sm.full0 + 8 * slot, fill & 1);
+        if (w.active) {
+            const double* st = sm.stage + (size_t)slot * kStageElems + w.fk * kSW + w.col0 + w.fr;
+            const int kn = min(kKC, H - k0);
+#pragma unroll 4
+            for (int kk = 0; kk < kn; kk += 4) {
+                const double a = arow[k0 + kk];
+                const double b0 = st[kk * kSW], b1 = st[kk * kSW + 8], b2 = st[kk * kSW + 16], b3 = st[kk * kSW + 24];
+                dmma884(acc[0], a, b0);
+                dmma884(acc[1], a, b1);
+                dmma884(acc[2], a, b2);
+                dmma884(acc[3], a, b3);
+            }
+        }
+        __syncwarp();
+        if (w.lane == 0) mbar_arrive(sm.empty0 + 8 * slot);
+        ++w.chunk;
+    }
+}
+
+__device__ __forceinline__ void zero_acc4(double (&acc)[4][2]) {
+#pragma unroll
+    for (int t = 0; t < 4; ++t) { acc[t][0] = 0.0; acc[t][1] = 0.0; }
+}
+
+// One policy step, forward, for the CTA's `rows` chains (consumer warps only).
+//   in : sm.IN [k][rows] = [x; y];  hprev (sm.HA or sm.HB) = previous hidden state, row-major
+//   out: sm.OUT [k][rows] = sigmoid output;  hnew (the other H buffer) = new hidden state
+// B0 holds the embedding then u1, B1 holds p, u2 overwrites hprev (dead after the GRU).
+__device__ __forceinline__ void mma_policy_forward(const PolicyLayout& lay, const double* __restrict__ theta_t, bool head_a,
+                                                   const MmaSmem& sm, MmaWarp& w, double* hprev, double* hnew,
+                                                   const SaveAreas<double>* save, long long node0, int nvalid,
+                                                   double* __restrict__ hs_out) {
+    const int d = lay.d, H = lay.H, rows = sm.rows, KS = sm.KS;
+    const int tid = threadIdx.x, nthr = w.nthr;
+    // ---- embedding (K = d+1): B0 = elu(We [x;y] + be)
+    {
+        const double* Wt = theta_t + lay.off[S_WE];      // [d+1][H]
+        const double* b = theta_t + lay.off[S_BE];
+        for (int e = tid; e < rows * H; e += nthr) {
+            const int r = e / H, o = e - r * H;
+            double a = __ldg(b + o);
+            for (int k = 0; k <= d; ++k) a = fma(sm.IN[k * rows + r], __ldg(Wt + k * H + o), a);
+            const double v = elu_(a);
+            sm.B0[r * KS + o] = v;
+            if (save && r < nvalid) save->EA[(node0 + r) * H + o] = v;
+        }
+        if (save) {
+            for (int e = tid; e < rows * (d + 1); e += nthr) {
+                const int r = e / (d + 1), k = e - r * (d + 1);
+                if (r < nvalid) save->XY[(node0 + r) * (d + 1) + k] = sm.IN[k * rows + r];
+            }
+        }
+    }
+    consumer_sync(nthr);
+    const int row = w.row0 + w.fr;
+    const bool rv = row < nvalid;
+    const size_t nrow = (size_t)(node0 + row) * H;
+    double acc[4][2];
+    // ---- prepro: B1 = p = elu(Wp ea + bp)
+    zero_acc4(acc);
+    mma_gemm(sm, w, sm.B0, H, acc);
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+        const int o = w.col0 + 8 * t + 2 * w.fk;
+        if (o < H) {
+            const double2 bb = __ldg(reinterpret_cast<const double2*>(theta_t + lay.off[S_BP] + o));
+            const double2 v = make_double2(elu_(acc[t][0] + bb.x), elu_(acc[t][1] + bb.y));
+            *reinterpret_cast<double2*>(sm.B1 + row * KS + o) = v;
+            if (save && rv) *reinterpret_cast<double2*>(save->P + nrow + o) = v;
+        }
+    }
+    consumer_sync(nthr);
+    // ---- GRU cell (gates r, z, n of the same (row, col) stay in registers)
+    {
+        double rg[4][2], zg[4][2], gh[4][2];
+        const double* bih = theta_t + lay.off[S_BIH];
+        const double* bhh = theta_t + lay.off[S_BHH];
+        zero_acc4(acc);
+        mma_gemm(sm, w, sm.B1, H, acc);
+        mma_gemm(sm, w, hprev, H, acc);
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+            const int o = min(w.col0 + 8 * t + 2 * w.fk, H - 2);
+#pragma unroll
+            for (int j = 0; j < 2; ++j) rg[t][j] = sigmoid_(acc[t][j] + __ldg(bih + o + j) + __ldg(bhh + o + j));
+        }
+        zero_acc4(acc);
+        mma_gemm(sm, w, sm.B1, H, acc);
+        mma_gemm(sm, w, hprev, H, acc);
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+            const int o = min(w.col0 + 8 * t + 2 * w.fk, H - 2);
+#pragma unroll
+            for (int j = 0; j < 2; ++j) zg[t][j] = sigmoid_(acc[t][j] + __ldg(bih + H + o + j) + __ldg(bhh + H + o + j));
+        }
+        zero_acc4(acc);
+        zero_acc4(gh);
+        mma_gemm(sm, w, sm.B1, H, acc);
+        mma_gemm(sm, w, hprev, H, gh);
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+            const int o = w.col0 + 8 * t + 2 * w.fk;
+            if (o < H) {
+                double hn[2], ng[2], hv[2];
+#pragma unroll
+                for (int j = 0; j < 2; ++j) {
+                    hn[j] = gh[t][j] + __ldg(bhh + 2 * H + o + j);
+                    ng[j] = Num<double>::tanh(acc[t][j] + __ldg(bih + 2 * H + o + j) + rg[t][j] * hn[j]);
+                    const double hp = hprev[row * KS + o + j];
+                    hv[j] = (1.0 - zg[t][j]) * ng[j] + zg[t][j] * hp;
+                }
+                *reinterpret_cast<double2*>(hnew + row * KS + o) = make_double2(hv[0], hv[1]);
+                if (rv) {
+                    if (save) {
+                        *reinterpret_cast<double2*>(save->RG + nrow + o) = make_double2(rg[t][0], rg[t][1]);
+                        *reinterpret_cast<double2*>(save->ZG + nrow + o) = make_double2(zg[t][0], zg[t][1]);
+                        *reinterpret_cast<double2*>(save->NG + nrow + o) = make_double2(ng[0], ng[1]);
+                        *reinterpret_cast<double2*>(save->HN + nrow + o) = make_double2(hn[0], hn[1]);
+                    }
+                    if (hs_out) *reinterpret_cast<double2*>(hs_out + (size_t)row * H + o) = make_double2(hv[0], hv[1]);
+                }
+            }
+        }
+    }
+    consumer_sync(nthr);
+    // ---- post MLP layer 0: B0 = u1 = elu(W0 [p; h'] + b0)
+    const int sB0 = head_a ? S_AB0 : S_XB0, sB3 = head_a ? S_AB3 : S_XB3;
+    const int sW6 = head_a ? S_AW6 : S_XW6, sB6 = head_a ? S_AB6 : S_XB6;
+    zero_acc4(acc);
+    mma_gemm(sm, w, sm.B1, H, acc);
+    mma_gemm(sm, w, hnew, H, acc);
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+        const int o = w.col0 + 8 * t + 2 * w.fk;
+        if (o < H) {
+            const double2 bb = __ldg(reinterpret_cast<const double2*>(theta_t + lay.off[sB0] + o));
+            const double2 v = make_double2(elu_(acc[t][0] + bb.x), elu_(acc[t][1] + bb.y));
+            *reinterpret_cast<double2*>(sm.B0 + row * KS + o) = v;
+            if (save && rv) *reinterpret_cast<double2*>(save->U1 + nrow + o) = v;
+        }
+    }
+    consumer_sync(nthr);
+    // ---- layer 3: u2 = elu(W3 u1 + b3) -> hprev buffer (dead)
+    zero_acc4(acc);
+    mma_gemm(sm, w, sm.B0, H, acc);
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+        const int o = w.col0 + 8 * t + 2 * w.fk;
+        if (o < H) {
+            const double2 bb = __ldg(reinterpret_cast<const double2*>(theta_t + lay.off[sB3] + o));
+            const double2 v = make_double2(elu_(acc[t][0] + bb.x), elu_(acc[t][1] + bb.y));
+            *reinterpret_cast<double2*>(hprev + row * KS + o) = v;
+            if (save && rv) *reinterpret_cast<double2*>(save->U2 + nrow + o) = v;
+        }
+    }
+    consumer_sync(nthr);
+    // ---- output layer (O = d): out = sigmoid(W6 u2 + b6); 4 threads per output, 2 interleaved chains each
+    {
+        const double* Wt = theta_t + lay.off[sW6];       // [H][d]
+        const double* b = theta_t + lay.off[sB6];
+        const int sub = tid & 3;
+        for (int e = tid >> 2; e < ((rows * d + 7) & ~7); e += nthr >> 2) {
+            const bool ok = e < rows * d;
+            const int r = ok ? e / d : 0, o = ok ? e - r * d : 0;
+            double a0 = 0.0, a1 = 0.0;
+            const double* u = hprev + r * KS;
+            for (int k = sub; k < H; k += 8) {
+                a0 = fma(u[k], __ldg(Wt + k * d + o), a0);
+                if (k + 4 < H) a1 = fma(u[k + 4], __ldg(Wt + (k + 4) * d + o), a1);
+            }
+            double a = a0 + a1;
+            a += __shfl_xor_sync(0xffffffffu, a, 1);
+            a += __shfl_xor_sync(0xffffffffu, a, 2);
+            if (ok && sub == 0) {
+                const double v = sigmoid_(a + __ldg(b + o));
+                sm.OUT[o * rows + r] = v;
+                if (save && r < nvalid) save->OUT[(node0 + r) * d + o] = v;
+            }
+        }
+    }
+    consumer_sync(nthr);
+}
+
+}  // namespace nmb

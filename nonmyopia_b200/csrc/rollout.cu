@@ -11,6 +11,7 @@
 #include "cost.cuh"
 #include "path.cuh"
 #include "policy_dev.cuh"
+#include "policy_mma.cuh"
 
 namespace nmb {
 
@@ -202,6 +203,139 @@ __global__ void __launch_bounds__(kNT, 1) ts_rollout_fwd_kernel(ProblemDev<T> pb
     }
 }
 
+// ================================================================== forward, FP64 tensor pipe + TMA weight stream
+// rows (multiple of 8, <= 56) chains per CTA; rows/4 consumer warps + 1 producer warp (policy_mma.cuh).
+template <int DMAX>
+__global__ void __launch_bounds__(kMaxRowsMma * 8 + 32, 1)
+    ts_rollout_fwd_mma_kernel(ProblemDev<double> pb, RolloutDev<double> ro0, RolloutDev<double> ro1, int rows) {
+    using T = double;
+    if (pb.done_flag && *pb.done_flag) return;
+    const RolloutDev<T>& ro = blockIdx.y == 0 ? ro0 : ro1;
+    const int d = pb.d, H = pb.H, L = pb.L;
+    const long long N = pb.N;
+    const long long chain0 = (long long)blockIdx.x * rows;
+    const int nvalid = (int)min((long long)rows, N - chain0);
+    const int tid = threadIdx.x;
+    const int ncw = rows >> 2, nthr = ncw * 32;
+    const long long step = pb.step_ptr ? *pb.step_ptr : 0;
+
+    MmaSmem sm;
+    sm.carve(reinterpret_cast<T*>(nmb_smem_raw), d, H, rows);
+    if (tid == 0) {
+        for (int s = 0; s < kStages; ++s) {
+            mbar_init(sm.full0 + 8 * s, 1);
+            mbar_init(sm.empty0 + 8 * s, ncw);
+        }
+        fence_barrier_init();
+    }
+    __syncthreads();
+    if (tid >= nthr) {      // producer warp
+        mma_producer(pb.lay, ro.theta_t, L, sm);
+        return;
+    }
+    MmaWarp w;
+    w.init(tid >> 5, nthr, H);
+    const int KS = sm.KS;
+
+    // ---- load the tile's inputs
+    for (int e = tid; e < (d + 1) * rows; e += nthr) {
+        const int k = e / rows, r = e - k * rows;
+        T v = T(0);
+        if (r < nvalid) v = k < d ? pb.prev_x[(chain0 + r) * d + k] : pb.prev_y[chain0 + r];
+        sm.IN[k * rows + r] = v;
+    }
+    for (int e = tid; e < H * rows; e += nthr) {
+        const int r = e / H, k = e - r * H;
+        const T v = r < nvalid ? pb.prev_h[(chain0 + r) * H + k] : T(0);
+        sm.HA[r * KS + k] = v;
+        if (ro.has_save && r < nvalid) ro.sv.HS[(chain0 + r) * H + k] = v;
+    }
+    if (tid < rows) sm.cost_acc[tid] = T(0);
+    consumer_sync(nthr);
+
+    const SaveAreas<T>* sv = ro.has_save ? &ro.sv : nullptr;
+    for (int l = 0; l <= L; ++l) {
+        const bool head_a = (l == L);
+        const long long node0 = (long long)l * N + chain0;
+        T* hs_out = ro.has_save ? ro.sv.HS + ((size_t)(l + 1) * N + chain0) * H : nullptr;
+        T* hprev = (l & 1) ? sm.HB : sm.HA;
+        T* hnew = (l & 1) ? sm.HA : sm.HB;
+        mma_policy_forward(pb.lay, ro.theta_t, head_a, sm, w, hprev, hnew, sv, node0, nvalid, hs_out);
+
+        // ---- output point, Thompson path, cost: 8 threads per chain (nthr = 8 rows)
+        const int r = tid >> 3, lane = tid & 7;
+        const long long chain = chain0 + r;
+        const bool live = r < nvalid;
+        T xin[DMAX], pt[DMAX];
+#pragma unroll
+        for (int k = 0; k < DMAX; ++k) {
+            xin[k] = k < d ? sm.IN[k * rows + r] : T(0);
+            pt[k] = k < d ? sm.OUT[k * rows + r] : T(0);
+        }
+        const bool noisy = head_a ? ro.noisy_action : ro.noisy_design;
+        if (noisy && live) {
+            T q[4]; int di, dj;
+            get_rotation<T>(ro, pb, step, l, chain, q, di, dj);
+            T vi = T(0), vj = T(0);
+#pragma unroll
+            for (int k = 0; k < DMAX; ++k) { if (k == di) vi = pt[k] - xin[k]; if (k == dj) vj = pt[k] - xin[k]; }
+            const T ri = q[0] * vi + q[1] * vj, rj = q[2] * vi + q[3] * vj;
+#pragma unroll
+            for (int k = 0; k < DMAX; ++k) {
+                T v = pt[k] - xin[k];
+                if (k == di) v = ri;
+                if (k == dj) v = rj;
+                if (k < d) pt[k] = v + xin[k];
+            }
+        }
+        T yp = T(0), gp[DMAX];
+#pragma unroll
+        for (int k = 0; k < DMAX; ++k) gp[k] = T(0);
+        if (live) {
+            if (ro.has_save) path_partial<T, DMAX, true>(pb.path, pt, (int)(chain / pb.cpp), lane, 8, yp, gp);
+            else path_partial<T, DMAX, false>(pb.path, pt, (int)(chain / pb.cpp), lane, 8, yp, gp);
+        }
+        yp = group_sum(yp, 8);
+        if (ro.has_save) {
+#pragma unroll
+            for (int k = 0; k < DMAX; ++k) gp[k] = group_sum(gp[k], 8);
+        }
+        const T yv = yp + pb.path.mean_const;
+        consumer_sync(nthr);     // every thread has read sm.IN / sm.OUT of this step
+        if (live && lane == 0) {
+            T dir[DMAX];
+            const T dist = move_dist<T, DMAX>(pb.cost, d, pt, xin, dir);
+            const T nz = get_cost_noise<T>(ro, pb, step, l, chain);
+            T h = pb.cost.k * (dist - pb.cost.radius);
+            h = (h > T(0) ? h : T(0)) + nz * pb.cost.max_noise;
+            T mult = T(1);
+            if (pb.cost.discount > T(0)) {
+                const T acc = sm.cost_acc[r] + pb.cost.prev_cost;
+                if (acc + h > pb.cost.discount_threshold) mult = pb.cost.disc_mult;
+                h *= mult;
+            }
+            sm.cost_acc[r] += h;
+            if (ro.has_save) {
+                ro.sv.CM[node0 + r] = mult;
+#pragma unroll
+                for (int k = 0; k < DMAX; ++k) if (k < d) ro.sv.DYDX[(node0 + r) * d + k] = gp[k];
+            }
+            T* dst = head_a ? ro.A + chain * d : ro.X + ((size_t)l * N + chain) * d;
+#pragma unroll
+            for (int k = 0; k < DMAX; ++k) if (k < d) dst[k] = pt[k];
+            if (ro.Y) ro.Y[(size_t)l * N + chain] = yv;
+            if (head_a) {
+                ro.loss[chain] = -yv;
+                ro.cost[chain] = sm.cost_acc[r];
+            }
+#pragma unroll
+            for (int k = 0; k < DMAX; ++k) if (k < d) sm.IN[k * rows + r] = pt[k];
+            sm.IN[d * rows + r] = yv;
+        }
+        consumer_sync(nthr);
+    }
+}
+
 // ================================================================== backward
 template <typename T, int DMAX>
 __global__ void __launch_bounds__(kNT, 1) ts_rollout_bwd_kernel(ProblemDev<T> pb, RolloutDev<T> ro, const T* __restrict__ g_loss,
@@ -370,6 +504,29 @@ static int launch_fwd(const nmb_ts_problem_t* p, const nmb_ts_rollout_t* r, int 
     return 0;
 }
 
+// the FP64 tensor-pipe forward needs 16-byte aligned weight rows: every segment offset even (d even), aligned base
+static bool mma_fwd_ok(const nmb_ts_problem_t* p, const nmb_ts_rollout_t* r, int n) {
+    if (p->dtype != NMB_F64 || (p->d & 1) || p->H < 8) return false;
+    for (int i = 0; i < n; ++i)
+        if (((uintptr_t)r[i].theta_t & 15) != 0) return false;
+    return true;
+}
+
+template <int DMAX>
+static int launch_fwd_mma(const nmb_ts_problem_t* p, const nmb_ts_rollout_t* r, int n, cudaStream_t st) {
+    ProblemDev<double> pb = make_problem<double>(*p);
+    RolloutDev<double> r0 = make_rollout<double>(*p, r[0]);
+    RolloutDev<double> r1 = n > 1 ? make_rollout<double>(*p, r[1]) : r0;
+    const int rows = mma_rows_per_cta(p->n_chains, n, sm_count());
+    const size_t smem = MmaSmem::bytes(p->d, p->H, rows);
+    auto kern = ts_rollout_fwd_mma_kernel<DMAX>;
+    NMB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    dim3 grid((unsigned)((p->n_chains + rows - 1) / rows), (unsigned)n);
+    kern<<<grid, rows * 8 + 32, smem, st>>>(pb, r0, r1, rows);
+    NMB_LAUNCH_CHECK();
+    return 0;
+}
+
 template <typename T, int DMAX>
 static int launch_bwd(const nmb_ts_problem_t* p, const nmb_ts_rollout_t* r, const void* gl, const void* gc,
                       const void* gX, const void* gA, void* gprev, cudaStream_t st) {
@@ -400,7 +557,7 @@ extern "C" int64_t nmb_ts_save_bytes(int dtype, int d, int H, int L, int64_t n_c
 
 extern "C" int64_t nmb_ts_save_hidden_offset(int d, int H, int L, int64_t n_chains) {
     const size_t nodes = (size_t)(L + 1) * n_chains;
-    return (int64_t)(nodes * (d + 1) + nodes * H * 2);
+    return (int64_t)(((nodes * (d + 1) + 1) & ~(size_t)1) + nodes * H * 2);
 }
 
 #define NMB_DISPATCH_D(FN, T, d, ...)                   \
@@ -423,6 +580,13 @@ extern "C" int nmb_ts_rollout_fwd(const nmb_ts_problem_t* prob, const nmb_ts_rol
                     "nmb_ts_rollout_fwd: rot_q and rot_dims must be given together");
     }
     cudaStream_t st = (cudaStream_t)stream;
+    if (mma_fwd_ok(prob, rollouts, n_rollouts)) {
+        const int d = prob->d;
+        return d <= 2 ? launch_fwd_mma<2>(prob, rollouts, n_rollouts, st)
+               : d <= 4 ? launch_fwd_mma<4>(prob, rollouts, n_rollouts, st)
+               : d <= 8 ? launch_fwd_mma<8>(prob, rollouts, n_rollouts, st)
+                        : launch_fwd_mma<16>(prob, rollouts, n_rollouts, st);
+    }
     if (prob->dtype == NMB_F64) return NMB_DISPATCH_D(launch_fwd, double, prob->d, prob, rollouts, n_rollouts, st);
     return NMB_DISPATCH_D(launch_fwd, float, prob->d, prob, rollouts, n_rollouts, st);
 }
