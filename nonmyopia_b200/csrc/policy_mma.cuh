@@ -63,6 +63,13 @@ __device__ __forceinline__ void dmma884(double (&c)[2], double a, double b) {
 }
 
 // ---------------------------------------------------------------- geometry / shared memory
+// weight ring as seen by producer and consumers
+struct MmaRing {
+    double* stage;
+    unsigned full0, empty0;     // shared addresses of the mbarrier arrays
+    int KS;                     // activation row stride
+};
+
 struct MmaSmem {
     double *IN, *OUT, *B0, *B1, *HA, *HB, *stage, *cost_acc;
     unsigned full0, empty0;     // shared addresses of the mbarrier arrays
@@ -85,13 +92,14 @@ struct MmaSmem {
     static size_t bytes(int d, int H, int rows) {
         return ((size_t)kStages * kStageElems + (size_t)4 * rows * (H + 4) + (size_t)(2 * d + 2) * rows + 2 * kStages) * 8;
     }
+    __device__ MmaRing ring() const { return MmaRing{stage, full0, empty0, KS}; }
 };
 
 // rows per CTA (multiple of 8, <= 56) minimising waves x rows for `n_rollouts` x N chains on `sms` SMs
-inline int mma_rows_per_cta(long long N, int n_rollouts, int sms) {
+inline int mma_rows_per_cta(long long N, int n_rollouts, int sms, int max_rows = kMaxRowsMma) {
     int best = 8;
     double best_cost = 1e300;
-    for (int r = 8; r <= kMaxRowsMma; r += 8) {
+    for (int r = 8; r <= max_rows; r += 8) {
         const long long ctas = ((N + r - 1) / r) * n_rollouts;
         const long long waves = (ctas + sms - 1) / sms;
         // a CTA of r rows costs about (r + 8): fixed per-step latency of the serial layer chain
@@ -119,27 +127,50 @@ __device__ __forceinline__ void gemm_src(const PolicyLayout& lay, bool head_a, i
     }
 }
 
-// Producer warp: stream every weight chunk of steps 0..L in consumption order.
-__device__ __forceinline__ void mma_producer(const PolicyLayout& lay, const double* __restrict__ theta_t, int L,
-                                             const MmaSmem& sm) {
+// weight chunk source of GEMM g (0..9) of a BACKWARD policy step: element offset in theta ([O][K] torch layout,
+// contraction over O) and leading dimension
+__device__ __forceinline__ void gemm_src_bwd(const PolicyLayout& lay, bool head_a, int g, int& off, int& ldw) {
+    const int H = lay.H;
+    const int sW0 = head_a ? S_AW0 : S_XW0, sW3 = head_a ? S_AW3 : S_XW3;
+    switch (g) {
+        case 0: off = lay.off[sW3]; ldw = H; break;
+        case 1: off = lay.off[sW0]; ldw = 2 * H; break;
+        case 2: off = lay.off[sW0] + H; ldw = 2 * H; break;
+        case 3: off = lay.off[S_WIH]; ldw = H; break;
+        case 4: off = lay.off[S_WIH] + H * H; ldw = H; break;
+        case 5: off = lay.off[S_WIH] + 2 * H * H; ldw = H; break;
+        case 6: off = lay.off[S_WHH]; ldw = H; break;
+        case 7: off = lay.off[S_WHH] + H * H; ldw = H; break;
+        case 8: off = lay.off[S_WHH] + 2 * H * H; ldw = H; break;
+        default: off = lay.off[S_WP]; ldw = H; break;
+    }
+}
+
+// Producer warp: stream every weight chunk of all L+1 steps in consumption order (forward: steps 0..L from
+// theta_t; backward: steps L..0 from theta).
+template <int NST, bool BWD>
+__device__ __forceinline__ void mma_producer(const PolicyLayout& lay, const double* __restrict__ weights, int L,
+                                             const MmaRing& rg) {
     const int lane = threadIdx.x & 31;
     const int H = lay.H;
     const unsigned row_bytes = (unsigned)H * 8u;
     unsigned c = 0;
-    for (int l = 0; l <= L; ++l) {
+    for (int it = 0; it <= L; ++it) {
+        const int l = BWD ? L - it : it;
         for (int g = 0; g < kGemmsPerStep; ++g) {
             int off, ldw;
-            gemm_src(lay, l == L, g, off, ldw);
+            if (BWD) gemm_src_bwd(lay, l == L, g, off, ldw);
+            else gemm_src(lay, l == L, g, off, ldw);
             for (int k0 = 0; k0 < H; k0 += kKC, ++c) {
-                const unsigned slot = c % kStages, fill = c / kStages;
-                if (fill > 0) mbar_wait(sm.empty0 + 8 * slot, (fill - 1) & 1);
+                const unsigned slot = c % NST, fill = c / NST;
+                if (fill > 0) mbar_wait(rg.empty0 + 8 * slot, (fill - 1) & 1);
                 const int kn = min(kKC, H - k0);
-                const unsigned full = sm.full0 + 8 * slot;
+                const unsigned full = rg.full0 + 8 * slot;
                 if (lane == 0) mbar_arrive_expect_tx(full, row_bytes * (unsigned)kn);
                 __syncwarp();
                 if (lane < kn)
-                    bulk_g2s(smem_u32(sm.stage + (size_t)slot * kStageElems + lane * kSW),
-                             theta_t + off + (size_t)(k0 + lane) * ldw, row_bytes, full);
+                    bulk_g2s(smem_u32(rg.stage + (size_t)slot * kStageElems + lane * kSW),
+                             weights + off + (size_t)(k0 + lane) * ldw, row_bytes, full);
             }
         }
     }
@@ -165,11 +196,12 @@ struct MmaWarp {
 
 // acc[t] (t = 0..3: 8-column tiles of the warp's 32 columns) += A[row0.., 0..H) . W chunk stream
 // A: shared, row-major with stride KS, pointing at the first contraction column.
-__device__ __forceinline__ void mma_gemm(const MmaSmem& sm, MmaWarp& w, const double* __restrict__ A, int H,
+template <int NST>
+__device__ __forceinline__ void mma_gemm(const MmaRing& sm, MmaWarp& w, const double* __restrict__ A, int H,
                                          double (&acc)[4][2]) {
     const double* arow = A + (size_t)(w.row0 + w.fr) * sm.KS + w.fk;
     for (int k0 = 0; k0 < H; k0 += kKC) {
-        const unsigned slot = w.chunk % kStages, fill = w.chunk / kStages;
+        const unsigned slot = w.chunk % NST, fill = w.chunk / NST;
         mbar_wait(sm.full0 + 8 * slot, fill & 1);
         if (w.active) {
             const double* st = sm.stage + (size_t)slot * kStageElems + w.fk * kSW + w.col0 + w.fr;
@@ -205,6 +237,7 @@ __device__ __forceinline__ void mma_policy_forward(const PolicyLayout& lay, cons
                                                    double* __restrict__ hs_out) {
     const int d = lay.d, H = lay.H, rows = sm.rows, KS = sm.KS;
     const int tid = threadIdx.x, nthr = w.nthr;
+    const MmaRing ring = sm.ring();
     // ---- embedding (K = d+1): B0 = elu(We [x;y] + be)
     {
         const double* Wt = theta_t + lay.off[S_WE];      // [d+1][H]
@@ -231,7 +264,7 @@ __device__ __forceinline__ void mma_policy_forward(const PolicyLayout& lay, cons
     double acc[4][2];
     // ---- prepro: B1 = p = elu(Wp ea + bp)
     zero_acc4(acc);
-    mma_gemm(sm, w, sm.B0, H, acc);
+    mma_gemm<kStages>(ring, w, sm.B0, H, acc);
 #pragma unroll
     for (int t = 0; t < 4; ++t) {
         const int o = w.col0 + 8 * t + 2 * w.fk;
@@ -249,8 +282,8 @@ __device__ __forceinline__ void mma_policy_forward(const PolicyLayout& lay, cons
         const double* bih = theta_t + lay.off[S_BIH];
         const double* bhh = theta_t + lay.off[S_BHH];
         zero_acc4(acc);
-        mma_gemm(sm, w, sm.B1, H, acc);
-        mma_gemm(sm, w, hprev, H, acc);
+        mma_gemm<kStages>(ring, w, sm.B1, H, acc);
+        mma_gemm<kStages>(ring, w, hprev, H, acc);
 #pragma unroll
         for (int t = 0; t < 4; ++t) {
             const int o = min(w.col0 + 8 * t + 2 * w.fk, H - 2);
@@ -258,8 +291,8 @@ __device__ __forceinline__ void mma_policy_forward(const PolicyLayout& lay, cons
             for (int j = 0; j < 2; ++j) rg[t][j] = sigmoid_(acc[t][j] + __ldg(bih + o + j) + __ldg(bhh + o + j));
         }
         zero_acc4(acc);
-        mma_gemm(sm, w, sm.B1, H, acc);
-        mma_gemm(sm, w, hprev, H, acc);
+        mma_gemm<kStages>(ring, w, sm.B1, H, acc);
+        mma_gemm<kStages>(ring, w, hprev, H, acc);
 #pragma unroll
         for (int t = 0; t < 4; ++t) {
             const int o = min(w.col0 + 8 * t + 2 * w.fk, H - 2);
@@ -268,8 +301,8 @@ __device__ __forceinline__ void mma_policy_forward(const PolicyLayout& lay, cons
         }
         zero_acc4(acc);
         zero_acc4(gh);
-        mma_gemm(sm, w, sm.B1, H, acc);
-        mma_gemm(sm, w, hprev, H, gh);
+        mma_gemm<kStages>(ring, w, sm.B1, H, acc);
+        mma_gemm<kStages>(ring, w, hprev, H, gh);
 #pragma unroll
         for (int t = 0; t < 4; ++t) {
             const int o = w.col0 + 8 * t + 2 * w.fk;
@@ -300,8 +333,8 @@ __device__ __forceinline__ void mma_policy_forward(const PolicyLayout& lay, cons
     const int sB0 = head_a ? S_AB0 : S_XB0, sB3 = head_a ? S_AB3 : S_XB3;
     const int sW6 = head_a ? S_AW6 : S_XW6, sB6 = head_a ? S_AB6 : S_XB6;
     zero_acc4(acc);
-    mma_gemm(sm, w, sm.B1, H, acc);
-    mma_gemm(sm, w, hnew, H, acc);
+    mma_gemm<kStages>(ring, w, sm.B1, H, acc);
+    mma_gemm<kStages>(ring, w, hnew, H, acc);
 #pragma unroll
     for (int t = 0; t < 4; ++t) {
         const int o = w.col0 + 8 * t + 2 * w.fk;
@@ -315,7 +348,7 @@ __device__ __forceinline__ void mma_policy_forward(const PolicyLayout& lay, cons
     consumer_sync(nthr);
     // ---- layer 3: u2 = elu(W3 u1 + b3) -> hprev buffer (dead)
     zero_acc4(acc);
-    mma_gemm(sm, w, sm.B0, H, acc);
+    mma_gemm<kStages>(ring, w, sm.B0, H, acc);
 #pragma unroll
     for (int t = 0; t < 4; ++t) {
         const int o = w.col0 + 8 * t + 2 * w.fk;
@@ -349,6 +382,221 @@ __device__ __forceinline__ void mma_policy_forward(const PolicyLayout& lay, cons
                 sm.OUT[o * rows + r] = v;
                 if (save && r < nvalid) save->OUT[(node0 + r) * d + o] = v;
             }
+        }
+    }
+    consumer_sync(nthr);
+}
+
+// ================================================================== backward step
+constexpr int kStagesBwd = 3;
+constexpr int kMaxRowsMmaBwd = 40;    // 7 row-major adjoint buffers + 3 weight stages in 227 KB
+
+struct MmaBwdSmem {
+    double *X0, *X1, *X2, *X3, *X4, *X5, *GH, *GO, *GXY, *carry, *stage;
+    unsigned full0, empty0;
+    int rows, KS;
+    __device__ void carve(double* base, int d, int dmax, int H, int rows_) {
+        rows = rows_;
+        KS = H + 4;
+        double* p = base;
+        stage = p; p += kStagesBwd * kStageElems;
+        X0 = p; p += rows * KS;
+        X1 = p; p += rows * KS;
+        X2 = p; p += rows * KS;
+        X3 = p; p += rows * KS;
+        X4 = p; p += rows * KS;
+        X5 = p; p += rows * KS;
+        GH = p; p += rows * KS;
+        GO = p; p += d * rows;
+        GXY = p; p += (d + 1) * rows;
+        carry = p; p += (dmax + 1) * rows;
+        full0 = smem_u32(p);
+        empty0 = full0 + 8 * kStagesBwd;
+    }
+    static size_t bytes(int d, int dmax, int H, int rows) {
+        return ((size_t)kStagesBwd * kStageElems + (size_t)7 * rows * (H + 4) + (size_t)(2 * d + dmax + 2) * rows +
+                2 * kStagesBwd) * 8;
+    }
+    __device__ MmaRing ring() const { return MmaRing{stage, full0, empty0, KS}; }
+};
+
+// One policy step backward for the CTA's rows (consumer warps only).
+//   in : sm.GO [k][rows] adjoint of the sigmoid output;  sm.GH adjoint of the new hidden state (row-major)
+//   out: sm.GXY [(d+1)][rows] adjoint of [x; y];  sm.GH adjoint of the previous hidden state
+// Leaves the pre-activation adjoints (DO, DU2, DU1, DR, DZ, DN, DNH, DP, DE) of the node in the save
+// workspace for the weight-gradient kernel.  theta: torch layout [O][K].
+__device__ __forceinline__ void mma_policy_backward(const PolicyLayout& lay, const double* __restrict__ theta, bool head_a,
+                                                    const MmaBwdSmem& sm, MmaWarp& w, const SaveAreas<double>& sv,
+                                                    long long node0, int nvalid) {
+    const int d = lay.d, H = lay.H, rows = sm.rows, KS = sm.KS;
+    const int tid = threadIdx.x, nthr = w.nthr;
+    const MmaRing ring = sm.ring();
+    const int sW6 = head_a ? S_AW6 : S_XW6;
+    // ---- output layer: do_pre = go * o (1 - o)
+    for (int e = tid; e < d * rows; e += nthr) {
+        const int o = e / rows, r = e - o * rows;
+        double v = 0.0;
+        if (r < nvalid) {
+            const double out = sv.OUT[(node0 + r) * d + o];
+            v = sm.GO[o * rows + r] * out * (1.0 - out);
+            sv.DO[(node0 + r) * d + o] = v;
+        }
+        sm.GO[o * rows + r] = v;
+    }
+    consumer_sync(nthr);
+    // ---- du2_pre = (do_pre . W6) * elu'(u2)  (K = d) -> X0
+    {
+        const double* W = theta + lay.off[sW6];      // [d][H]
+        for (int e = tid; e < rows * H; e += nthr) {
+            const int r = e / H, k = e - r * H;
+            double v = 0.0;
+            if (r < nvalid) {
+                double a = 0.0;
+                for (int o = 0; o < d; ++o) a = fma(sm.GO[o * rows + r], __ldg(W + o * H + k), a);
+                v = a * elu_grad_from_out(sv.U2[(node0 + r) * H + k]);
+                sv.DU2[(node0 + r) * H + k] = v;
+            }
+            sm.X0[r * KS + k] = v;
+        }
+    }
+    consumer_sync(nthr);
+    const int row = w.row0 + w.fr;
+    const bool rv = row < nvalid;
+    const size_t nrow = (size_t)(node0 + row) * H;
+    double acc[4][2];
+    // ---- du1_pre = (du2_pre . W3) * elu'(u1) -> X1
+    zero_acc4(acc);
+    mma_gemm<kStagesBwd>(ring, w, sm.X0, H, acc);
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+        const int k = w.col0 + 8 * t + 2 * w.fk;
+        if (k < H) {
+            double2 v = make_double2(0.0, 0.0);
+            if (rv) {
+                const double2 u = *reinterpret_cast<const double2*>(sv.U1 + nrow + k);
+                v = make_double2(acc[t][0] * elu_grad_from_out(u.x), acc[t][1] * elu_grad_from_out(u.y));
+                *reinterpret_cast<double2*>(sv.DU1 + nrow + k) = v;
+            }
+            *reinterpret_cast<double2*>(sm.X1 + row * KS + k) = v;
+        }
+    }
+    consumer_sync(nthr);
+    // ---- d[p; h'] = du1_pre . W0 : first H columns -> raw dp (X2), second H columns -> GRU backward
+    zero_acc4(acc);
+    mma_gemm<kStagesBwd>(ring, w, sm.X1, H, acc);
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+        const int k = w.col0 + 8 * t + 2 * w.fk;
+        if (k < H) *reinterpret_cast<double2*>(sm.X2 + row * KS + k) = make_double2(acc[t][0], acc[t][1]);
+    }
+    zero_acc4(acc);
+    mma_gemm<kStagesBwd>(ring, w, sm.X1, H, acc);
+    // X0 (du2_pre), X3..X5 are dead for every warp here (barriers above / end of the previous step)
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+        const int k = w.col0 + 8 * t + 2 * w.fk;
+        if (k < H) {
+            double dr[2] = {0, 0}, dz[2] = {0, 0}, dn[2] = {0, 0}, dnh[2] = {0, 0}, dhp[2] = {0, 0};
+            if (rv) {
+                const double2 rg = *reinterpret_cast<const double2*>(sv.RG + nrow + k);
+                const double2 zg = *reinterpret_cast<const double2*>(sv.ZG + nrow + k);
+                const double2 ng = *reinterpret_cast<const double2*>(sv.NG + nrow + k);
+                const double2 hn = *reinterpret_cast<const double2*>(sv.HN + nrow + k);
+                const double2 hp = *reinterpret_cast<const double2*>(sv.HS + nrow + k);   // HS[level] = h before the step
+                const double2 gh = *reinterpret_cast<const double2*>(sm.GH + row * KS + k);
+                const double rgv[2] = {rg.x, rg.y}, zgv[2] = {zg.x, zg.y}, ngv[2] = {ng.x, ng.y};
+                const double hnv[2] = {hn.x, hn.y}, hpv[2] = {hp.x, hp.y}, ghv[2] = {gh.x, gh.y};
+#pragma unroll
+                for (int j = 0; j < 2; ++j) {
+                    const double dh = acc[t][j] + ghv[j];
+                    const double dng = dh * (1.0 - zgv[j]);
+                    dn[j] = dng * (1.0 - ngv[j] * ngv[j]);
+                    dz[j] = dh * (hpv[j] - ngv[j]) * zgv[j] * (1.0 - zgv[j]);
+                    dr[j] = dn[j] * hnv[j] * rgv[j] * (1.0 - rgv[j]);
+                    dnh[j] = dn[j] * rgv[j];
+                    dhp[j] = dh * zgv[j];
+                }
+                *reinterpret_cast<double2*>(sv.DR + nrow + k) = make_double2(dr[0], dr[1]);
+                *reinterpret_cast<double2*>(sv.DZ + nrow + k) = make_double2(dz[0], dz[1]);
+                *reinterpret_cast<double2*>(sv.DN + nrow + k) = make_double2(dn[0], dn[1]);
+                *reinterpret_cast<double2*>(sv.DNH + nrow + k) = make_double2(dnh[0], dnh[1]);
+            }
+            *reinterpret_cast<double2*>(sm.X0 + row * KS + k) = make_double2(dr[0], dr[1]);
+            *reinterpret_cast<double2*>(sm.X3 + row * KS + k) = make_double2(dz[0], dz[1]);
+            *reinterpret_cast<double2*>(sm.X4 + row * KS + k) = make_double2(dn[0], dn[1]);
+            *reinterpret_cast<double2*>(sm.X5 + row * KS + k) = make_double2(dnh[0], dnh[1]);
+            *reinterpret_cast<double2*>(sm.GH + row * KS + k) = make_double2(dhp[0], dhp[1]);   // own element only
+        }
+    }
+    consumer_sync(nthr);
+    // ---- dp_pre = (raw dp + dgi . Wih) * elu'(p) -> X2
+    zero_acc4(acc);
+    mma_gemm<kStagesBwd>(ring, w, sm.X0, H, acc);
+    mma_gemm<kStagesBwd>(ring, w, sm.X3, H, acc);
+    mma_gemm<kStagesBwd>(ring, w, sm.X4, H, acc);
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+        const int k = w.col0 + 8 * t + 2 * w.fk;
+        if (k < H) {
+            double2 v = make_double2(0.0, 0.0);
+            if (rv) {
+                const double2 pp = *reinterpret_cast<const double2*>(sv.P + nrow + k);
+                const double2 raw = *reinterpret_cast<const double2*>(sm.X2 + row * KS + k);
+                v = make_double2((acc[t][0] + raw.x) * elu_grad_from_out(pp.x), (acc[t][1] + raw.y) * elu_grad_from_out(pp.y));
+                *reinterpret_cast<double2*>(sv.DP + nrow + k) = v;
+            }
+            *reinterpret_cast<double2*>(sm.X2 + row * KS + k) = v;     // own element only
+        }
+    }
+    // ---- dh_prev += dr . Whh_r + dz . Whh_z + dnh . Whh_n
+    zero_acc4(acc);
+    mma_gemm<kStagesBwd>(ring, w, sm.X0, H, acc);
+    mma_gemm<kStagesBwd>(ring, w, sm.X3, H, acc);
+    mma_gemm<kStagesBwd>(ring, w, sm.X5, H, acc);
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+        const int k = w.col0 + 8 * t + 2 * w.fk;
+        if (k < H) {
+            double2* g = reinterpret_cast<double2*>(sm.GH + row * KS + k);
+            const double2 o = *g;
+            *g = make_double2(o.x + acc[t][0], o.y + acc[t][1]);
+        }
+    }
+    consumer_sync(nthr);
+    // ---- de_pre = (dp_pre . Wp) * elu'(ea) -> X1
+    zero_acc4(acc);
+    mma_gemm<kStagesBwd>(ring, w, sm.X2, H, acc);
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+        const int k = w.col0 + 8 * t + 2 * w.fk;
+        if (k < H) {
+            double2 v = make_double2(0.0, 0.0);
+            if (rv) {
+                const double2 ea = *reinterpret_cast<const double2*>(sv.EA + nrow + k);
+                v = make_double2(acc[t][0] * elu_grad_from_out(ea.x), acc[t][1] * elu_grad_from_out(ea.y));
+                *reinterpret_cast<double2*>(sv.DE + nrow + k) = v;
+            }
+            *reinterpret_cast<double2*>(sm.X1 + row * KS + k) = v;
+        }
+    }
+    consumer_sync(nthr);
+    // ---- d[x; y] = de_pre . We  (We is [H][d+1]); 4 threads per output
+    {
+        const double* W = theta + lay.off[S_WE];
+        const int sub = tid & 3, nout = rows * (d + 1);
+        for (int e = tid >> 2; e < ((nout + 7) & ~7); e += nthr >> 2) {
+            const bool ok = e < nout;
+            const int r = ok ? e / (d + 1) : 0, k = ok ? e - r * (d + 1) : 0;
+            const double* g = sm.X1 + r * KS;
+            double a0 = 0.0, a1 = 0.0;
+            for (int o = sub; o < H; o += 8) {
+                a0 = fma(g[o], __ldg(W + o * (d + 1) + k), a0);
+                if (o + 4 < H) a1 = fma(g[o + 4], __ldg(W + (o + 4) * (d + 1) + k), a1);
+            }
+            double a = a0 + a1;
+            a += __shfl_xor_sync(0xffffffffu, a, 1);
+            a += __shfl_xor_sync(0xffffffffu, a, 2);
+            if (ok && sub == 0) sm.GXY[k * rows + r] = a;
         }
     }
     consumer_sync(nthr);

@@ -230,7 +230,7 @@ __global__ void __launch_bounds__(kMaxRowsMma * 8 + 32, 1)
     }
     __syncthreads();
     if (tid >= nthr) {      // producer warp
-        mma_producer(pb.lay, ro.theta_t, L, sm);
+        mma_producer<kStages, false>(pb.lay, ro.theta_t, L, sm.ring());
         return;
     }
     MmaWarp w;
@@ -449,6 +449,131 @@ __global__ void __launch_bounds__(kNT, 1) ts_rollout_bwd_kernel(ProblemDev<T> pb
     }
 }
 
+// ================================================================== backward, FP64 tensor pipe + TMA weight stream
+template <int DMAX>
+__global__ void __launch_bounds__(kMaxRowsMmaBwd * 8 + 32, 1)
+    ts_rollout_bwd_mma_kernel(ProblemDev<double> pb, RolloutDev<double> ro, const double* __restrict__ g_loss,
+                              const double* __restrict__ g_cost, const double* __restrict__ g_X,
+                              const double* __restrict__ g_A, double* __restrict__ g_prev, int rows) {
+    using T = double;
+    if (pb.done_flag && *pb.done_flag) return;
+    const int d = pb.d, H = pb.H, L = pb.L;
+    const long long N = pb.N;
+    const long long chain0 = (long long)blockIdx.x * rows;
+    const int nvalid = (int)min((long long)rows, N - chain0);
+    const int tid = threadIdx.x;
+    const int ncw = rows >> 2, nthr = ncw * 32;
+    const long long step = pb.step_ptr ? *pb.step_ptr : 0;
+
+    MmaBwdSmem sm;
+    sm.carve(reinterpret_cast<T*>(nmb_smem_raw), d, DMAX, H, rows);
+    if (tid == 0) {
+        for (int s = 0; s < kStagesBwd; ++s) {
+            mbar_init(sm.full0 + 8 * s, 1);
+            mbar_init(sm.empty0 + 8 * s, ncw);
+        }
+        fence_barrier_init();
+    }
+    __syncthreads();
+    if (tid >= nthr) {
+        mma_producer<kStagesBwd, true>(pb.lay, ro.theta, L, sm.ring());
+        return;
+    }
+    MmaWarp w;
+    w.init(tid >> 5, nthr, H);
+    const int KS = sm.KS;
+    T* carry = sm.carry;      // [(DMAX+1)][rows]: adjoint of (x_{l+1}, y_{l+1}) from the level above
+
+    for (int e = tid; e < rows * KS; e += nthr) sm.GH[e] = T(0);
+    for (int e = tid; e < (DMAX + 1) * rows; e += nthr) carry[e] = T(0);
+    consumer_sync(nthr);
+
+    const SaveAreas<T>& sv = ro.sv;
+    for (int l = L; l >= 0; --l) {
+        const bool head_a = (l == L);
+        const long long node0 = (long long)l * N + chain0;
+        if (tid < rows) {
+            const int r = tid;
+            if (r < nvalid) {
+                const long long chain = chain0 + r;
+                const size_t node = (size_t)(node0 + r);
+                T pt[DMAX], xin[DMAX], gout[DMAX];
+                const T* psrc = head_a ? ro.A + chain * d : ro.X + ((size_t)l * N + chain) * d;
+#pragma unroll
+                for (int k = 0; k < DMAX; ++k) {
+                    pt[k] = k < d ? psrc[k] : T(0);
+                    xin[k] = k < d ? sv.XY[node * (d + 1) + k] : T(0);
+                }
+                const T gy = head_a ? -g_loss[chain] : carry[DMAX * rows + r];
+#pragma unroll
+                for (int k = 0; k < DMAX; ++k) {
+                    T g = T(0);
+                    if (k < d) {
+                        g = carry[k * rows + r] + gy * sv.DYDX[node * d + k];
+                        if (head_a) { if (g_A) g += g_A[chain * d + k]; }
+                        else if (g_X) g += g_X[((size_t)l * N + chain) * d + k];
+                    }
+                    gout[k] = g;
+                }
+                T dir[DMAX];
+                const T dist = move_dist<T, DMAX>(pb.cost, d, pt, xin, dir);
+                const T hinge = pb.cost.k * (dist - pb.cost.radius);
+                const T gc = hinge > T(0) ? g_cost[chain] * pb.cost.k * sv.CM[node] : T(0);
+                T gprev[DMAX];
+#pragma unroll
+                for (int k = 0; k < DMAX; ++k) { gout[k] += gc * dir[k]; gprev[k] = -gc * dir[k]; }
+                const bool noisy = head_a ? ro.noisy_action : ro.noisy_design;
+                T go[DMAX];
+#pragma unroll
+                for (int k = 0; k < DMAX; ++k) go[k] = gout[k];
+                if (noisy) {
+                    T q[4]; int di, dj;
+                    get_rotation<T>(ro, pb, step, l, chain, q, di, dj);
+                    T gi = T(0), gj = T(0);
+#pragma unroll
+                    for (int k = 0; k < DMAX; ++k) { if (k == di) gi = gout[k]; if (k == dj) gj = gout[k]; }
+                    const T ti = q[0] * gi + q[2] * gj, tj = q[1] * gi + q[3] * gj;
+#pragma unroll
+                    for (int k = 0; k < DMAX; ++k) {
+                        if (k == di) go[k] = ti;
+                        if (k == dj) go[k] = tj;
+                        gprev[k] += gout[k] - go[k];
+                    }
+                }
+#pragma unroll
+                for (int k = 0; k < DMAX; ++k) {
+                    if (k < d) sm.GO[k * rows + r] = go[k];
+                    carry[k * rows + r] = gprev[k];
+                }
+            } else {
+                for (int k = 0; k < d; ++k) sm.GO[k * rows + r] = T(0);
+            }
+        }
+        consumer_sync(nthr);
+        mma_policy_backward(pb.lay, ro.theta, head_a, sm, w, sv, node0, nvalid);
+        if (tid < rows) {
+            const int r = tid;
+#pragma unroll
+            for (int k = 0; k < DMAX; ++k) if (k < d) carry[k * rows + r] += sm.GXY[k * rows + r];
+            carry[DMAX * rows + r] = sm.GXY[d * rows + r];
+        }
+        consumer_sync(nthr);
+    }
+    if (g_prev) {
+        const int wd = d + 1 + H;
+        for (int e = tid; e < wd * rows; e += nthr) {
+            const int r = e / wd, k = e - r * wd;
+            if (r < nvalid) {
+                T v;
+                if (k < d) v = carry[k * rows + r];
+                else if (k == d) v = carry[DMAX * rows + r];
+                else v = sm.GH[r * KS + (k - d - 1)];
+                g_prev[(chain0 + r) * wd + k] = v;
+            }
+        }
+    }
+}
+
 // ================================================================== host side
 template <typename T> static ProblemDev<T> make_problem(const nmb_ts_problem_t& p) {
     ProblemDev<T> o;
@@ -541,6 +666,26 @@ static int launch_bwd(const nmb_ts_problem_t* p, const nmb_ts_rollout_t* r, cons
     return 0;
 }
 
+static bool mma_bwd_ok(const nmb_ts_problem_t* p, const nmb_ts_rollout_t* r) {
+    return p->dtype == NMB_F64 && !(p->d & 1) && p->H >= 8 && ((uintptr_t)r->theta & 15) == 0;
+}
+
+template <int DMAX>
+static int launch_bwd_mma(const nmb_ts_problem_t* p, const nmb_ts_rollout_t* r, const void* gl, const void* gc,
+                          const void* gX, const void* gA, void* gprev, cudaStream_t st) {
+    ProblemDev<double> pb = make_problem<double>(*p);
+    RolloutDev<double> r0 = make_rollout<double>(*p, *r);
+    const int rows = mma_rows_per_cta(p->n_chains, 1, sm_count(), kMaxRowsMmaBwd);
+    const size_t smem = MmaBwdSmem::bytes(p->d, DMAX, p->H, rows);
+    auto kern = ts_rollout_bwd_mma_kernel<DMAX>;
+    NMB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    dim3 grid((unsigned)((p->n_chains + rows - 1) / rows));
+    kern<<<grid, rows * 8 + 32, smem, st>>>(pb, r0, (const double*)gl, (const double*)gc, (const double*)gX,
+                                            (const double*)gA, (double*)gprev, rows);
+    NMB_LAUNCH_CHECK();
+    return 0;
+}
+
 }  // namespace nmb
 
 using namespace nmb;
@@ -599,6 +744,13 @@ extern "C" int nmb_ts_rollout_bwd(const nmb_ts_problem_t* prob, const nmb_ts_rol
                 "nmb_ts_rollout_bwd: needs the saved rollout and theta");
     NMB_REQUIRE(g_loss && g_cost, NMB_EINVAL, "nmb_ts_rollout_bwd: null seeds");
     cudaStream_t st = (cudaStream_t)stream;
+    if (mma_bwd_ok(prob, rollout)) {
+        const int d = prob->d;
+        return d <= 2 ? launch_bwd_mma<2>(prob, rollout, g_loss, g_cost, g_X, g_A, g_prev, st)
+               : d <= 4 ? launch_bwd_mma<4>(prob, rollout, g_loss, g_cost, g_X, g_A, g_prev, st)
+               : d <= 8 ? launch_bwd_mma<8>(prob, rollout, g_loss, g_cost, g_X, g_A, g_prev, st)
+                        : launch_bwd_mma<16>(prob, rollout, g_loss, g_cost, g_X, g_A, g_prev, st);
+    }
     if (prob->dtype == NMB_F64)
         return NMB_DISPATCH_D(launch_bwd, double, prob->d, prob, rollout, g_loss, g_cost, g_X, g_A, g_prev, st);
     return NMB_DISPATCH_D(launch_bwd, float, prob->d, prob, rollout, g_loss, g_cost, g_X, g_A, g_prev, st);

@@ -8,6 +8,7 @@
 // partials[split][param]; the reduction over splits is done in a fixed order by the
 // AdamW kernel (optim.cu) or nmb_policy_reduce_partials -> bitwise deterministic.
 #include "policy_dev.cuh"
+#include "policy_mma.cuh"
 
 namespace nmb {
 
@@ -118,6 +119,113 @@ __global__ void __launch_bounds__(256, 2) wgrad_kernel(const __grid_constant__ W
     if (tk.bias_dst >= 0 && tid < tk.On) out[tk.bias_dst + tid] = bacc;
 }
 
+// ------------------------------------------------------------------ FP64 tensor-pipe variant (H x H tasks)
+// 8 consumer warps own 16 (o) x 32 (k) tiles of the 64 x 64 weight tile; the contraction runs over nodes,
+// so BOTH operands (dY and A, node-major in the save workspace) are k-major: a producer warp streams 32-node
+// chunks of both with cp.async.bulk row copies into a 3-stage ring (row stride 72 doubles: conflict-free
+// fragments), 2 CTAs per SM.
+constexpr int kWgStages = 3;
+constexpr int kWgStageElems = 2 * kNC * kSW;      // dY rows then A rows
+
+__global__ void __launch_bounds__(288, 2) wgrad_mma_kernel(const __grid_constant__ WgArgs<double> args) {
+    if (args.done_flag && *args.done_flag) return;
+    extern __shared__ __align__(16) unsigned char wg_smem_raw[];
+    double* stage = reinterpret_cast<double*>(wg_smem_raw);
+    const unsigned full0 = smem_u32(stage + kWgStages * kWgStageElems), empty0 = full0 + 8 * kWgStages;
+    const int item = blockIdx.x;
+    int ti = 0;
+    while (ti + 1 < args.n_tasks && item >= args.t[ti + 1].item0) ++ti;
+    const WgTask<double>& tk = args.t[ti];
+    const int split = item - tk.item0;
+    const long long nb = tk.n_begin + (long long)split * args.chunk;
+    const long long ne = min(tk.n_end, nb + args.chunk);
+    const int nch = (int)((ne - nb + kNC - 1) / kNC);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    if (tid == 0) {
+        for (int s = 0; s < kWgStages; ++s) {
+            mbar_init(full0 + 8 * s, 1);
+            mbar_init(empty0 + 8 * s, 8);
+        }
+        fence_barrier_init();
+    }
+    __syncthreads();
+    if (warp == 8) {
+        // ---- producer: lane = node row of the chunk
+        const unsigned ybytes = (unsigned)tk.On * 8u, abytes = (unsigned)tk.Kn * 8u;
+        for (int ch = 0; ch < nch; ++ch) {
+            const unsigned slot = ch % kWgStages, fill = ch / kWgStages;
+            if (fill > 0) mbar_wait(empty0 + 8 * slot, (fill - 1) & 1);
+            const long long n0 = nb + (long long)ch * kNC;
+            const int valid = (int)min((long long)kNC, ne - n0);
+            double* ys = stage + (size_t)slot * kWgStageElems + lane * kSW;
+            double* as = ys + kNC * kSW;
+            if (lane >= valid) {      // ragged tail: zero rows
+                for (int c = 0; c < 64; ++c) { ys[c] = 0.0; as[c] = 0.0; }
+            }
+            __syncwarp();
+            const unsigned full = full0 + 8 * slot;
+            if (lane == 0) mbar_arrive_expect_tx(full, (ybytes + abytes) * (unsigned)valid);
+            __syncwarp();
+            if (lane < valid) {
+                const long long node = n0 + lane;
+                bulk_g2s(smem_u32(ys), tk.dY + (size_t)node * tk.ldY + tk.o0, ybytes, full);
+                bulk_g2s(smem_u32(as), tk.A + (size_t)node * tk.ldA + tk.k0, abytes, full);
+            }
+        }
+        return;
+    }
+    // ---- consumers
+    const int fr = lane >> 2, fk = lane & 3;
+    const int o0 = (warp >> 1) * 16, k0 = (warp & 1) * 32;
+    double acc[2][4][2];
+#pragma unroll
+    for (int i = 0; i < 2; ++i)
+#pragma unroll
+        for (int t = 0; t < 4; ++t) { acc[i][t][0] = 0.0; acc[i][t][1] = 0.0; }
+    double bacc = 0.0;
+    for (int ch = 0; ch < nch; ++ch) {
+        const unsigned slot = ch % kWgStages, fill = ch / kWgStages;
+        mbar_wait(full0 + 8 * slot, fill & 1);
+        const double* ys = stage + (size_t)slot * kWgStageElems + fk * kSW + o0 + fr;
+        const double* as = stage + (size_t)slot * kWgStageElems + kNC * kSW + fk * kSW + k0 + fr;
+#pragma unroll
+        for (int kk = 0; kk < kNC; kk += 4) {
+            const double a0 = ys[kk * kSW], a1 = ys[kk * kSW + 8];
+            const double b0 = as[kk * kSW], b1 = as[kk * kSW + 8], b2 = as[kk * kSW + 16], b3 = as[kk * kSW + 24];
+            dmma884(acc[0][0], a0, b0); dmma884(acc[0][1], a0, b1); dmma884(acc[0][2], a0, b2); dmma884(acc[0][3], a0, b3);
+            dmma884(acc[1][0], a1, b0); dmma884(acc[1][1], a1, b1); dmma884(acc[1][2], a1, b2); dmma884(acc[1][3], a1, b3);
+        }
+        if (tk.bias_dst >= 0 && tid < 64) {
+            const double* yb = stage + (size_t)slot * kWgStageElems + tid;
+#pragma unroll 8
+            for (int nn = 0; nn < kNC; ++nn) bacc += yb[nn * kSW];
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(empty0 + 8 * slot);
+    }
+    double* out = args.partials + (size_t)split * args.n_params;
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+        const int o = o0 + 8 * i + fr;
+        if (o < tk.On) {
+#pragma unroll
+            for (int t = 0; t < 4; ++t) {
+                const int k = k0 + 8 * t + 2 * fk;
+                if (k < tk.Kn)
+                    *reinterpret_cast<double2*>(out + tk.dst + (size_t)o * tk.ldK + k) = make_double2(acc[i][t][0], acc[i][t][1]);
+            }
+        }
+    }
+    if (tk.bias_dst >= 0 && tid < tk.On) out[tk.bias_dst + tid] = bacc;
+}
+
+static void launch_wgrad_mma(const WgArgs<double>& am, int items, cudaStream_t st) {
+    const size_t smem = (size_t)kWgStages * kWgStageElems * 8 + 2 * kWgStages * 8;
+    cudaFuncSetAttribute(wgrad_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    wgrad_mma_kernel<<<items, 288, smem, st>>>(am);
+}
+static void launch_wgrad_mma(const WgArgs<float>&, int, cudaStream_t) {}
+
 static int wgrad_chunk(int L, long long N) {
     const long long nodes = (long long)(L + 1) * N;
     long long ch = (nodes + 31) / 32;          // at most 32 splits per segment
@@ -134,20 +242,26 @@ static int launch_wgrad(const nmb_ts_problem_t* p, const void* save, void* parti
     PolicyLayout lay;
     lay.init(d, H, 1);
     SaveAreas<T> sv = carve_save<T>(const_cast<void*>(save), d, H, L, N);
-    WgArgs<T> a;
+    // H x H tasks go to the FP64 tensor-pipe kernel (FP64, 16-byte aligned rows: d even), the rest (K = d+1,
+    // O = d, FP32) to the FMA kernel
+    const bool use_mma = sizeof(T) == 8 && !(d & 1) && H >= 8 && ((uintptr_t)save & 15) == 0 && ((uintptr_t)partials & 15) == 0;
+    WgArgs<T> a, am;
     memset(&a, 0, sizeof(a));
     a.chunk = wgrad_chunk(L, N);
     a.n_params = lay.total();
     a.partials = (T*)partials;
     a.done_flag = p->done_flag;
+    am = a;
     const long long all0 = 0, all1 = (long long)(L + 1) * N;
     const long long x0 = 0, x1 = (long long)L * N, a0 = (long long)L * N, a1 = all1;
-    int nt = 0, item = 0;
+    int nt = 0, item_small = 0, ntm = 0, itemm = 0;
     for (int s = 0; s < S_COUNT; ++s) seg_splits[s] = 0;
     auto add = [&](const T* dY, int ldY, int o0, int On, const T* A, int ldA, int k0, int Kn, long long nb,
                    long long ne, int wseg, int orow0, int kcol0, int bseg) {
         if (ne <= nb) return;
-        WgTask<T>& t = a.t[nt++];
+        const bool big = use_mma && On == H && Kn == H;
+        WgTask<T>& t = big ? am.t[ntm++] : a.t[nt++];
+        int& item = big ? itemm : item_small;
         t.dY = dY; t.ldY = ldY; t.o0 = o0; t.On = On;
         t.A = A; t.ldA = ldA; t.k0 = k0; t.Kn = Kn;
         t.n_begin = nb; t.n_end = ne;
@@ -178,10 +292,14 @@ static int launch_wgrad(const nmb_ts_problem_t* p, const void* save, void* parti
     add(sv.DU2, H, 0, H, sv.U1, H, 0, H, a0, a1, S_AW3, 0, 0, S_AB3);
     add(sv.DO, d, 0, d, sv.U2, H, 0, H, a0, a1, S_AW6, 0, 0, S_AB6);
     a.n_tasks = nt;
+    am.n_tasks = ntm;
     // bias rows of the gate blocks: offsets inside bih/bhh follow orow0 (handled by bias_dst above)
-    const size_t smem = 4 * kNC * 64 * sizeof(T);
-    NMB_CUDA(cudaFuncSetAttribute(wgrad_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    wgrad_kernel<T><<<item, 256, smem, st>>>(a);
+    if (itemm > 0) launch_wgrad_mma(am, itemm, st);
+    if (item_small > 0) {
+        const size_t smem = 4 * kNC * 64 * sizeof(T);
+        NMB_CUDA(cudaFuncSetAttribute(wgrad_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        wgrad_kernel<T><<<item_small, 256, smem, st>>>(a);
+    }
     NMB_LAUNCH_CHECK();
     return 0;
 }
