@@ -195,6 +195,9 @@ int nmb_policy_reduce_partials(int dtype, int d, int H, int n_actions, const voi
  * bookkeeping, early stop).  Lives in device memory so that one Adam iteration is a fixed
  * sequence of launches (CUDA-graph capturable) with no host synchronisation.
  * ---------------------------------------------------------------------- */
+/* The device buffer that holds the loop state must be NMB_LOOP_STATE_BYTES long and zero-initialised: the struct
+ * below occupies the first bytes, the rest is scratch for the multi-CTA reduction of nmb_ts_objective. */
+#define NMB_LOOP_STATE_BYTES 4096
 typedef struct nmb_loop_state {
     int64_t step;          /* iterations completed (ep) */
     int32_t done;          /* loop has stopped (early stop): kernels become no-ops */

@@ -356,7 +356,7 @@ class _FlatAdamW:
         self.m = [torch.zeros_like(q) for q in params]
         self.v = [torch.zeros_like(q) for q in params]
         self.t = [0] * len(params)
-        self.state = [torch.zeros(C.sizeof(te.LoopState), dtype=torch.uint8, device=q.device) for q in params]
+        self.state = [torch.zeros(te.LOOP_STATE_BYTES, dtype=torch.uint8, device=q.device) for q in params]
 
     def step(self, grads):
         lib = _lib.lib()

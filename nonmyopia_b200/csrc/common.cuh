@@ -5,6 +5,7 @@
 #include <stdio.h>
 #include <string.h>
 #include "../../include/nonmyopia_b200.h"
+#include "fastmath.cuh"
 
 namespace nmb {
 
@@ -33,11 +34,12 @@ int sm_count();
 // ---------------------------------------------------------------- math
 template <typename T> struct Num;
 template <> struct Num<double> {
-    static __device__ __forceinline__ void sincospi(double x, double* s, double* c) { ::sincospi(x, s, c); }
-    static __device__ __forceinline__ double exp(double x) { return ::exp(x); }
+    // straight-line DFMA kernels (fastmath.cuh): libm's versions cost 3-6x the instructions
+    static __device__ __forceinline__ void sincospi(double x, double* s, double* c) { nmb_sincospi(x, s, c); }
+    static __device__ __forceinline__ double exp(double x) { return nmb_exp(x); }
     static __device__ __forceinline__ double sqrt(double x) { return ::sqrt(x); }
-    static __device__ __forceinline__ double tanh(double x) { return ::tanh(x); }
-    static __device__ __forceinline__ double expm1(double x) { return ::expm1(x); }
+    static __device__ __forceinline__ double tanh(double x) { return nmb_tanh(x); }
+    static __device__ __forceinline__ double expm1(double x) { return nmb_expm1(x); }
     static __device__ __forceinline__ double fabs(double x) { return ::fabs(x); }
     static __device__ __forceinline__ double rsqrt(double x) { return 1.0 / ::sqrt(x); }
     static constexpr double kPi = 3.14159265358979323846;
@@ -58,8 +60,14 @@ template <> struct Num<float> {
 template <typename T> __device__ __forceinline__ T sigmoid_(T x) {
     return T(1) / (T(1) + Num<T>::exp(-x));
 }
+template <> __device__ __forceinline__ double sigmoid_<double>(double x) { return nmb_sigmoid(x); }
 template <typename T> __device__ __forceinline__ T elu_(T x) {
     return x > T(0) ? x : Num<T>::expm1(x);
+}
+// branch-free: expm1 of min(x, 0) is evaluated for every lane (no divergence), selected afterwards
+template <> __device__ __forceinline__ double elu_<double>(double x) {
+    const double e = nmb_expm1(fmin(x, 0.0));
+    return x > 0.0 ? x : e;
 }
 
 // Stationary kernel profile.  r2 = sum_k ((x_k - x'_k)/ls_k)^2.

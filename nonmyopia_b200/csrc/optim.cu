@@ -1,5 +1,6 @@
 // Optimiser-loop kernels: parameter transpose, per-restart objective + best-restart
 // bookkeeping, conditional snapshot, fused AdamW (reference actor.py:489-662).
+#include <algorithm>
 #include "policy_dev.cuh"
 
 namespace nmb {
@@ -89,9 +90,16 @@ __device__ __forceinline__ void loop_decide(nmb_loop_state_t* state, int past_in
     state->done_next = (patience >= 0 && state->stall > patience) ? 1 : 0;
 }
 
-// ---- objective + bookkeeping: one CTA of 1024 threads
+// ---- objective + bookkeeping: up to kObjMaxCtas CTAs of 256 threads; per-CTA partial results go to the scratch
+// area behind the loop state (NMB_LOOP_STATE_BYTES) and the last CTA to finish reduces them in CTA order
+// (deterministic) and takes the snapshot / early-stop decision.
+constexpr int kObjMaxCtas = 96;
+struct ObjPartial { double best, lck, sl, sc; long long idx; };
+struct ObjScratch { unsigned int count; unsigned int pad; ObjPartial part[kObjMaxCtas]; };
+static_assert(128 + sizeof(ObjScratch) <= NMB_LOOP_STATE_BYTES, "scratch must fit behind the loop state");
+
 template <typename T>
-__global__ void __launch_bounds__(1024) objective_kernel(int d, int L, long long N, long long n_global, T budget,
+__global__ void __launch_bounds__(256) objective_kernel(int d, int L, long long N, long long n_global, T budget,
                                                          int past_initial, int patience, const T* __restrict__ loss,
                                                          const T* __restrict__ cost, const T* __restrict__ X,
                                                          const T* __restrict__ A, const T* __restrict__ Xo,
@@ -112,7 +120,8 @@ __global__ void __launch_bounds__(1024) objective_kernel(int d, int L, long long
     double best = 1.0 / 0.0;
     long long best_i = 0x7fffffffffffffffLL;
     double sl = 0.0, sc = 0.0, lck_min = 1.0 / 0.0;
-    for (long long c = tid; c < N; c += blockDim.x) {
+    ObjScratch* scr = reinterpret_cast<ObjScratch*>(reinterpret_cast<char*>(state) + 128);
+    for (long long c = (long long)blockIdx.x * blockDim.x + tid; c < N; c += (long long)gridDim.x * blockDim.x) {
         T kl = T(0);
         for (int l = 0; l <= L; ++l) {
             const T* xm = l < L ? X + ((size_t)l * N + c) * d : A + (size_t)c * d;
@@ -178,6 +187,24 @@ __global__ void __launch_bounds__(1024) objective_kernel(int d, int L, long long
             sl += s_sum[0][w]; sc += s_sum[1][w];
             lck_min = s_lck[w] < lck_min ? s_lck[w] : lck_min;
         }
+        if (gridDim.x > 1) {
+            ObjPartial& me = scr->part[blockIdx.x];
+            me.best = best; me.lck = lck_min; me.sl = sl; me.sc = sc; me.idx = best_i;
+            __threadfence();
+            const unsigned prev = atomicAdd(&scr->count, 1u);
+            if (prev + 1 != gridDim.x) return;          // not the last CTA
+            __threadfence();
+            scr->count = 0;                              // ready for the next launch
+            best = 1.0 / 0.0; best_i = 0x7fffffffffffffffLL; sl = 0.0; sc = 0.0; lck_min = 1.0 / 0.0;
+            for (unsigned b = 0; b < gridDim.x; ++b) {
+                const volatile ObjPartial& o = scr->part[b];
+                const double ob = o.best; const long long oi = o.idx;
+                if (ob < best || (ob == best && oi < best_i)) { best = ob; best_i = oi; }
+                sl += o.sl; sc += o.sc;
+                const double ol = o.lck;
+                lck_min = ol < lck_min ? ol : lck_min;
+            }
+        }
         state->chosen_idx = (int)best_i;
         state->loss_mean = sl / (double)N;
         state->cost_mean = sc / (double)N;
@@ -232,13 +259,14 @@ extern "C" int nmb_ts_objective(int dtype, int d, int L, int64_t n_chains, int64
     NMB_REQUIRE((X_orig == nullptr) == (A_orig == nullptr), NMB_EINVAL, "nmb_ts_objective: X_orig/A_orig mismatch");
     NMB_REQUIRE(L == 0 || X, NMB_EINVAL, "nmb_ts_objective: X is null");
     cudaStream_t st = (cudaStream_t)stream;
+    const int obj_ctas = (int)std::min<long long>(kObjMaxCtas, (n_chains + 255) / 256);
     if (dtype == NMB_F64) {
-        objective_kernel<double><<<1, 1024, 0, st>>>(d, L, n_chains, n_global, budget, past_initial, patience, (const double*)loss,
+        objective_kernel<double><<<obj_ctas, 256, 0, st>>>(d, L, n_chains, n_global, budget, past_initial, patience, (const double*)loss,
             (const double*)cost, (const double*)X, (const double*)A, (const double*)X_orig, (const double*)A_orig,
             (double*)KL, (double*)total, (double*)g_loss, (double*)g_cost, (double*)g_X, (double*)g_A,
             (double*)hist_loss, (double*)hist_cost, (double*)hist_X, hist_capacity, defer_decision, state);
     } else if (dtype == NMB_F32) {
-        objective_kernel<float><<<1, 1024, 0, st>>>(d, L, n_chains, n_global, (float)budget, past_initial, patience, (const float*)loss,
+        objective_kernel<float><<<obj_ctas, 256, 0, st>>>(d, L, n_chains, n_global, (float)budget, past_initial, patience, (const float*)loss,
             (const float*)cost, (const float*)X, (const float*)A, (const float*)X_orig, (const float*)A_orig,
             (float*)KL, (float*)total, (float*)g_loss, (float*)g_cost, (float*)g_X, (float*)g_A,
             (float*)hist_loss, (float*)hist_cost, (float*)hist_X, hist_capacity, defer_decision, state);

@@ -219,6 +219,72 @@ __global__ void __launch_bounds__(288, 2) wgrad_mma_kernel(const __grid_constant
     if (tk.bias_dst >= 0 && tid < tk.On) out[tk.bias_dst + tid] = bacc;
 }
 
+// ------------------------------------------------------------------ thin tasks (K = d+1 or O = d)
+// dW = sum_nodes wide[node][w] * thin[node][t] with t < 17: 128 lanes over w (lane nW = a column of ones, which
+// yields the thin-side bias sum), 2 node slices, per-thread accumulators over t; HBM-bound (one pass over the
+// wide operand).
+constexpr int kThinMax = NMB_MAX_DIM + 1;
+constexpr int kThinSlices = 8;
+
+template <typename T>
+__global__ void __launch_bounds__(128 * kThinSlices) wgrad_thin_kernel(const __grid_constant__ WgArgs<T> args) {
+    if (args.done_flag && *args.done_flag) return;
+    __shared__ T red[128 * (kThinMax + 1)];
+    const int item = blockIdx.x;
+    int ti = 0;
+    while (ti + 1 < args.n_tasks && item >= args.t[ti + 1].item0) ++ti;
+    const WgTask<T>& tk = args.t[ti];
+    const int split = item - tk.item0;
+    const long long nb = tk.n_begin + (long long)split * args.chunk;
+    const long long ne = min(tk.n_end, nb + args.chunk);
+    const bool y_wide = tk.On >= tk.Kn;
+    const T* Wd = y_wide ? tk.dY : tk.A;
+    const T* Th = y_wide ? tk.A : tk.dY;
+    const int ldW = y_wide ? tk.ldY : tk.ldA, w0 = y_wide ? tk.o0 : tk.k0, nW = y_wide ? tk.On : tk.Kn;
+    const int ldT = y_wide ? tk.ldA : tk.ldY, t0 = y_wide ? tk.k0 : tk.o0, nT = y_wide ? tk.Kn : tk.On;
+    const int w = threadIdx.x & 127, q = threadIdx.x >> 7;
+    T acc[kThinMax];
+#pragma unroll
+    for (int t = 0; t < kThinMax; ++t) acc[t] = T(0);
+    T wsum = T(0);
+#pragma unroll 4
+    for (long long node = nb + q; node < ne; node += kThinSlices) {
+        const T wv = w < nW ? Wd[(size_t)node * ldW + w0 + w] : (w == nW ? T(1) : T(0));
+        const T* th = Th + (size_t)node * ldT + t0;
+#pragma unroll
+        for (int t = 0; t < kThinMax; ++t)
+            if (t < nT) acc[t] = fma(wv, __ldg(th + t), acc[t]);
+        wsum += wv;
+    }
+    // fixed-order reduction over the node slices (deterministic)
+    for (int sl = 1; sl < kThinSlices; ++sl) {
+        if (q == sl) {
+#pragma unroll
+            for (int t = 0; t < kThinMax; ++t)
+                red[w * (kThinMax + 1) + t] = sl == 1 ? acc[t] : red[w * (kThinMax + 1) + t] + acc[t];
+            red[w * (kThinMax + 1) + kThinMax] = sl == 1 ? wsum : red[w * (kThinMax + 1) + kThinMax] + wsum;
+        }
+        __syncthreads();
+    }
+    if (q == 0 && w <= nW) {
+        T* out = args.partials + (size_t)split * args.n_params;
+        wsum += red[w * (kThinMax + 1) + kThinMax];
+#pragma unroll
+        for (int t = 0; t < kThinMax; ++t) {
+            if (t < nT) {
+                const T v = acc[t] + red[w * (kThinMax + 1) + t];
+                if (w < nW) {
+                    if (y_wide) out[tk.dst + (size_t)w * tk.ldK + t] = v;
+                    else out[tk.dst + (size_t)t * tk.ldK + w] = v;
+                } else if (!y_wide && tk.bias_dst >= 0) {
+                    out[tk.bias_dst + t] = v;
+                }
+            }
+        }
+        if (y_wide && tk.bias_dst >= 0 && w < nW) out[tk.bias_dst + w] = wsum;
+    }
+}
+
 static void launch_wgrad_mma(const WgArgs<double>& am, int items, cudaStream_t st) {
     const size_t smem = (size_t)kWgStages * kWgStageElems * 8 + 2 * kWgStages * 8;
     cudaFuncSetAttribute(wgrad_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -226,11 +292,23 @@ static void launch_wgrad_mma(const WgArgs<double>& am, int items, cudaStream_t s
 }
 static void launch_wgrad_mma(const WgArgs<float>&, int, cudaStream_t) {}
 
+// nodes per work item: a multiple of 32, at most 32 splits per segment, and - for the H x H tasks (7 over all
+// nodes, 3 over the design levels, 3 over the action level) - no more items than the 2 CTAs/SM that are resident
 static int wgrad_chunk(int L, long long N) {
     const long long nodes = (long long)(L + 1) * N;
-    long long ch = (nodes + 31) / 32;          // at most 32 splits per segment
+    long long ch = (nodes + 31) / 32;
     ch = ((ch + kNC - 1) / kNC) * kNC;
     if (ch < 64) ch = 64;
+    const long long slots = 2LL * sm_count();
+    auto items = [&](long long c) {
+        return 7 * ((nodes + c - 1) / c) + (L > 0 ? 3 * (((long long)L * N + c - 1) / c) : 0) + 3 * ((N + c - 1) / c);
+    };
+    if (items(ch) > slots) {
+        // the first chunk size that fits in one wave, unless it is a poor fit anyway (then keep 2 balanced waves)
+        long long c = ch;
+        while (items(c) > slots && c < 2 * ch) c += kNC;
+        if (items(c) <= slots) ch = c;
+    }
     return (int)ch;
 }
 
@@ -296,9 +374,15 @@ static int launch_wgrad(const nmb_ts_problem_t* p, const void* save, void* parti
     // bias rows of the gate blocks: offsets inside bih/bhh follow orow0 (handled by bias_dst above)
     if (itemm > 0) launch_wgrad_mma(am, itemm, st);
     if (item_small > 0) {
-        const size_t smem = 4 * kNC * 64 * sizeof(T);
-        NMB_CUDA(cudaFuncSetAttribute(wgrad_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        wgrad_kernel<T><<<item_small, 256, smem, st>>>(a);
+        bool thin = true;      // every remaining task has one side <= d+1
+        for (int i = 0; i < nt; ++i) thin = thin && (a.t[i].On <= kThinMax || a.t[i].Kn <= kThinMax);
+        if (thin) {
+            wgrad_thin_kernel<T><<<item_small, 128 * kThinSlices, 0, st>>>(a);
+        } else {
+            const size_t smem = 4 * kNC * 64 * sizeof(T);
+            NMB_CUDA(cudaFuncSetAttribute(wgrad_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            wgrad_kernel<T><<<item_small, 256, smem, st>>>(a);
+        }
     }
     NMB_LAUNCH_CHECK();
     return 0;

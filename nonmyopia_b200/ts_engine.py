@@ -86,6 +86,9 @@ class LoopState(C.Structure):
                 ("cand_total", C.c_double), ("cand_lck", C.c_double)]
 
 
+LOOP_STATE_BYTES = 4096      # NMB_LOOP_STATE_BYTES: struct + scratch of the objective reduction
+
+
 class AdamWStruct(C.Structure):
     _fields_ = [("lr", C.c_double), ("beta1", C.c_double), ("beta2", C.c_double), ("eps", C.c_double),
                 ("weight_decay", C.c_double)]

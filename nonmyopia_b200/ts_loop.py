@@ -52,7 +52,7 @@ class TSAMLoop:
         self.m = torch.zeros_like(self.theta)
         self.v = torch.zeros_like(self.theta)
         # device loop state
-        self.state = torch.zeros(C.sizeof(te.LoopState), dtype=torch.uint8, device=dev)
+        self.state = torch.zeros(te.LOOP_STATE_BYTES, dtype=torch.uint8, device=dev)
         eng.step_ptr = self.state.data_ptr()            # offsetof(step) == 0
         eng.done_ptr = self.state.data_ptr() + 8        # offsetof(done) == 8
         self.prev = (prev_x.to(dev, dt).contiguous(), prev_y.reshape(-1).to(dev, dt).contiguous(),
@@ -82,8 +82,8 @@ class TSAMLoop:
             self._cand = self.state[56:72].view(torch.float64)
             self.grad = torch.zeros_like(self.theta)
             self._one_split = (C.c_int32 * 20)()
-        # rollout_fwd, objective, snapshot, rollout_bwd, wgrad, adamw, advance (+ decide, reduce when sharded)
-        self.n_launches_per_iter = 7 if group is None else 9
+        # rollout_fwd, objective, snapshot, rollout_bwd, wgrad (tensor-pipe + thin), adamw, advance (+ decide, reduce when sharded)
+        self.n_launches_per_iter = 8 if group is None else 10
 
     # ------------------------------------------------------------------ one iteration
     def _iteration(self, draws=None, mark=None) -> None:
@@ -137,7 +137,7 @@ class TSAMLoop:
         mark("adamw")
 
     def read_state(self) -> te.LoopState:
-        raw = self.state.cpu().numpy().tobytes()
+        raw = self.state[:C.sizeof(te.LoopState)].cpu().numpy().tobytes()
         return te.LoopState.from_buffer_copy(raw)
 
     def capture(self) -> None:
