@@ -420,6 +420,17 @@ struct MmaBwdSmem {
     __device__ MmaRing ring() const { return MmaRing{stage, full0, empty0, KS}; }
 };
 
+// the lane's 4 x double2 slice of a node-major [node][H] save area (issued BEFORE the GEMM whose epilogue uses it,
+// so the HBM/L2 latency overlaps the tensor-pipe work)
+__device__ __forceinline__ void prefetch_tile(double2 (&dst)[4], const double* __restrict__ area, size_t nrow,
+                                              const MmaWarp& w, int H, bool rv) {
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+        const int k = w.col0 + 8 * t + 2 * w.fk;
+        dst[t] = (rv && k < H) ? *reinterpret_cast<const double2*>(area + nrow + k) : make_double2(0.0, 0.0);
+    }
+}
+
 // One policy step backward for the CTA's rows (consumer warps only).
 //   in : sm.GO [k][rows] adjoint of the sigmoid output;  sm.GH adjoint of the new hidden state (row-major)
 //   out: sm.GXY [(d+1)][rows] adjoint of [x; y];  sm.GH adjoint of the previous hidden state
@@ -447,16 +458,29 @@ __device__ __forceinline__ void mma_policy_backward(const PolicyLayout& lay, con
     // ---- du2_pre = (do_pre . W6) * elu'(u2)  (K = d) -> X0
     {
         const double* W = theta + lay.off[sW6];      // [d][H]
-        for (int e = tid; e < rows * H; e += nthr) {
-            const int r = e / H, k = e - r * H;
-            double v = 0.0;
-            if (r < nvalid) {
-                double a = 0.0;
-                for (int o = 0; o < d; ++o) a = fma(sm.GO[o * rows + r], __ldg(W + o * H + k), a);
-                v = a * elu_grad_from_out(sv.U2[(node0 + r) * H + k]);
-                sv.DU2[(node0 + r) * H + k] = v;
+        for (int e0 = tid; e0 < rows * H; e0 += 4 * nthr) {
+            double u2[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {      // 4 independent loads in flight
+                const int e = e0 + i * nthr;
+                const int r = e / H, k = e - r * H;
+                u2[i] = (e < rows * H && r < nvalid) ? sv.U2[(node0 + r) * H + k] : 0.0;
             }
-            sm.X0[r * KS + k] = v;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int e = e0 + i * nthr;
+                if (e < rows * H) {
+                    const int r = e / H, k = e - r * H;
+                    double v = 0.0;
+                    if (r < nvalid) {
+                        double a = 0.0;
+                        for (int o = 0; o < d; ++o) a = fma(sm.GO[o * rows + r], __ldg(W + o * H + k), a);
+                        v = a * elu_grad_from_out(u2[i]);
+                        sv.DU2[(node0 + r) * H + k] = v;
+                    }
+                    sm.X0[r * KS + k] = v;
+                }
+            }
         }
     }
     consumer_sync(nthr);
@@ -465,6 +489,8 @@ __device__ __forceinline__ void mma_policy_backward(const PolicyLayout& lay, con
     const size_t nrow = (size_t)(node0 + row) * H;
     double acc[4][2];
     // ---- du1_pre = (du2_pre . W3) * elu'(u1) -> X1
+    double2 pf[4];
+    prefetch_tile(pf, sv.U1, nrow, w, H, rv);
     zero_acc4(acc);
     mma_gemm<kStagesBwd>(ring, w, sm.X0, H, acc);
 #pragma unroll
@@ -473,7 +499,7 @@ __device__ __forceinline__ void mma_policy_backward(const PolicyLayout& lay, con
         if (k < H) {
             double2 v = make_double2(0.0, 0.0);
             if (rv) {
-                const double2 u = *reinterpret_cast<const double2*>(sv.U1 + nrow + k);
+                const double2 u = pf[t];
                 v = make_double2(acc[t][0] * elu_grad_from_out(u.x), acc[t][1] * elu_grad_from_out(u.y));
                 *reinterpret_cast<double2*>(sv.DU1 + nrow + k) = v;
             }
@@ -482,6 +508,12 @@ __device__ __forceinline__ void mma_policy_backward(const PolicyLayout& lay, con
     }
     consumer_sync(nthr);
     // ---- d[p; h'] = du1_pre . W0 : first H columns -> raw dp (X2), second H columns -> GRU backward
+    double2 prg[4], pzg[4], png[4], phn[4], php[4];
+    prefetch_tile(prg, sv.RG, nrow, w, H, rv);
+    prefetch_tile(pzg, sv.ZG, nrow, w, H, rv);
+    prefetch_tile(png, sv.NG, nrow, w, H, rv);
+    prefetch_tile(phn, sv.HN, nrow, w, H, rv);
+    prefetch_tile(php, sv.HS, nrow, w, H, rv);      // HS[level] = h before the step
     zero_acc4(acc);
     mma_gemm<kStagesBwd>(ring, w, sm.X1, H, acc);
 #pragma unroll
@@ -498,11 +530,7 @@ __device__ __forceinline__ void mma_policy_backward(const PolicyLayout& lay, con
         if (k < H) {
             double dr[2] = {0, 0}, dz[2] = {0, 0}, dn[2] = {0, 0}, dnh[2] = {0, 0}, dhp[2] = {0, 0};
             if (rv) {
-                const double2 rg = *reinterpret_cast<const double2*>(sv.RG + nrow + k);
-                const double2 zg = *reinterpret_cast<const double2*>(sv.ZG + nrow + k);
-                const double2 ng = *reinterpret_cast<const double2*>(sv.NG + nrow + k);
-                const double2 hn = *reinterpret_cast<const double2*>(sv.HN + nrow + k);
-                const double2 hp = *reinterpret_cast<const double2*>(sv.HS + nrow + k);   // HS[level] = h before the step
+                const double2 rg = prg[t], zg = pzg[t], ng = png[t], hn = phn[t], hp = php[t];
                 const double2 gh = *reinterpret_cast<const double2*>(sm.GH + row * KS + k);
                 const double rgv[2] = {rg.x, rg.y}, zgv[2] = {zg.x, zg.y}, ngv[2] = {ng.x, ng.y};
                 const double hnv[2] = {hn.x, hn.y}, hpv[2] = {hp.x, hp.y}, ghv[2] = {gh.x, gh.y};
@@ -530,6 +558,9 @@ __device__ __forceinline__ void mma_policy_backward(const PolicyLayout& lay, con
     }
     consumer_sync(nthr);
     // ---- dp_pre = (raw dp + dgi . Wih) * elu'(p) -> X2
+    prefetch_tile(pf, sv.P, nrow, w, H, rv);
+    double2 pea[4];
+    prefetch_tile(pea, sv.EA, nrow, w, H, rv);
     zero_acc4(acc);
     mma_gemm<kStagesBwd>(ring, w, sm.X0, H, acc);
     mma_gemm<kStagesBwd>(ring, w, sm.X3, H, acc);
@@ -540,7 +571,7 @@ __device__ __forceinline__ void mma_policy_backward(const PolicyLayout& lay, con
         if (k < H) {
             double2 v = make_double2(0.0, 0.0);
             if (rv) {
-                const double2 pp = *reinterpret_cast<const double2*>(sv.P + nrow + k);
+                const double2 pp = pf[t];
                 const double2 raw = *reinterpret_cast<const double2*>(sm.X2 + row * KS + k);
                 v = make_double2((acc[t][0] + raw.x) * elu_grad_from_out(pp.x), (acc[t][1] + raw.y) * elu_grad_from_out(pp.y));
                 *reinterpret_cast<double2*>(sv.DP + nrow + k) = v;
@@ -572,7 +603,7 @@ __device__ __forceinline__ void mma_policy_backward(const PolicyLayout& lay, con
         if (k < H) {
             double2 v = make_double2(0.0, 0.0);
             if (rv) {
-                const double2 ea = *reinterpret_cast<const double2*>(sv.EA + nrow + k);
+                const double2 ea = pea[t];
                 v = make_double2(acc[t][0] * elu_grad_from_out(ea.x), acc[t][1] * elu_grad_from_out(ea.y));
                 *reinterpret_cast<double2*>(sv.DE + nrow + k) = v;
             }

@@ -220,16 +220,17 @@ __global__ void __launch_bounds__(288, 2) wgrad_mma_kernel(const __grid_constant
 }
 
 // ------------------------------------------------------------------ thin tasks (K = d+1 or O = d)
-// dW = sum_nodes wide[node][w] * thin[node][t] with t < 17: 128 lanes over w (lane nW = a column of ones, which
-// yields the thin-side bias sum), 2 node slices, per-thread accumulators over t; HBM-bound (one pass over the
-// wide operand).
+// dW = sum_nodes wide[node][w] * thin[node][t], t < 17 (d + 1 or d).  One thread per (w, t mod 4) pair and node
+// slice, 8 independent loads of each operand in flight per thread (the kernel is a single HBM pass over the wide
+// operand: latency, not arithmetic, is what has to be hidden); slices are reduced in fixed order.
 constexpr int kThinMax = NMB_MAX_DIM + 1;
-constexpr int kThinSlices = 8;
+constexpr int kThinSlices = 4;
+constexpr int kThinU = 8;
 
 template <typename T>
-__global__ void __launch_bounds__(128 * kThinSlices) wgrad_thin_kernel(const __grid_constant__ WgArgs<T> args) {
+__global__ void __launch_bounds__(256 * kThinSlices) wgrad_thin_kernel(const __grid_constant__ WgArgs<T> args) {
     if (args.done_flag && *args.done_flag) return;
-    __shared__ T red[128 * (kThinMax + 1)];
+    __shared__ T red[3][256];
     const int item = blockIdx.x;
     int ti = 0;
     while (ti + 1 < args.n_tasks && item >= args.t[ti + 1].item0) ++ti;
@@ -242,46 +243,49 @@ __global__ void __launch_bounds__(128 * kThinSlices) wgrad_thin_kernel(const __g
     const T* Th = y_wide ? tk.A : tk.dY;
     const int ldW = y_wide ? tk.ldY : tk.ldA, w0 = y_wide ? tk.o0 : tk.k0, nW = y_wide ? tk.On : tk.Kn;
     const int ldT = y_wide ? tk.ldA : tk.ldY, t0 = y_wide ? tk.k0 : tk.o0, nT = y_wide ? tk.Kn : tk.On;
-    const int w = threadIdx.x & 127, q = threadIdx.x >> 7;
-    T acc[kThinMax];
+    const int w = threadIdx.x & 63, t4 = (threadIdx.x >> 6) & 3, q = threadIdx.x >> 8, pr = threadIdx.x & 255;
+    T* out = args.partials + (size_t)split * args.n_params;
+    for (int tg = 0; tg < nT; tg += 4) {
+        const int t = tg + t4;
+        const bool wok = w < nW, tok = t < nT;
+        T acc = T(0), wsum = T(0), tsum = T(0);
+        for (long long node = nb + q; node < ne; node += kThinSlices * kThinU) {
+            T wv[kThinU], tv[kThinU];
 #pragma unroll
-    for (int t = 0; t < kThinMax; ++t) acc[t] = T(0);
-    T wsum = T(0);
-#pragma unroll 4
-    for (long long node = nb + q; node < ne; node += kThinSlices) {
-        const T wv = w < nW ? Wd[(size_t)node * ldW + w0 + w] : (w == nW ? T(1) : T(0));
-        const T* th = Th + (size_t)node * ldT + t0;
+            for (int u = 0; u < kThinU; ++u) {
+                const long long nu = node + (long long)u * kThinSlices;
+                const bool ok = nu < ne;
+                wv[u] = (ok && wok) ? Wd[(size_t)nu * ldW + w0 + w] : T(0);
+                tv[u] = (ok && tok) ? __ldg(Th + (size_t)nu * ldT + t0 + t) : T(0);
+            }
 #pragma unroll
-        for (int t = 0; t < kThinMax; ++t)
-            if (t < nT) acc[t] = fma(wv, __ldg(th + t), acc[t]);
-        wsum += wv;
-    }
-    // fixed-order reduction over the node slices (deterministic)
-    for (int sl = 1; sl < kThinSlices; ++sl) {
-        if (q == sl) {
-#pragma unroll
-            for (int t = 0; t < kThinMax; ++t)
-                red[w * (kThinMax + 1) + t] = sl == 1 ? acc[t] : red[w * (kThinMax + 1) + t] + acc[t];
-            red[w * (kThinMax + 1) + kThinMax] = sl == 1 ? wsum : red[w * (kThinMax + 1) + kThinMax] + wsum;
-        }
-        __syncthreads();
-    }
-    if (q == 0 && w <= nW) {
-        T* out = args.partials + (size_t)split * args.n_params;
-        wsum += red[w * (kThinMax + 1) + kThinMax];
-#pragma unroll
-        for (int t = 0; t < kThinMax; ++t) {
-            if (t < nT) {
-                const T v = acc[t] + red[w * (kThinMax + 1) + t];
-                if (w < nW) {
-                    if (y_wide) out[tk.dst + (size_t)w * tk.ldK + t] = v;
-                    else out[tk.dst + (size_t)t * tk.ldK + w] = v;
-                } else if (!y_wide && tk.bias_dst >= 0) {
-                    out[tk.bias_dst + t] = v;
-                }
+            for (int u = 0; u < kThinU; ++u) {
+                acc = fma(wv[u], tv[u], acc);
+                wsum += wv[u];
+                tsum += tv[u];
             }
         }
-        if (y_wide && tk.bias_dst >= 0 && w < nW) out[tk.bias_dst + w] = wsum;
+        // fixed-order reduction over the node slices (deterministic)
+        T vals[3] = {acc, wsum, tsum};
+        for (int sl = 1; sl < kThinSlices; ++sl) {
+            if (q == sl) {
+#pragma unroll
+                for (int j = 0; j < 3; ++j) red[j][pr] = sl == 1 ? vals[j] : red[j][pr] + vals[j];
+            }
+            __syncthreads();
+        }
+        if (q == 0) {
+            acc += red[0][pr]; wsum += red[1][pr]; tsum += red[2][pr];
+            if (wok && tok) {
+                if (y_wide) out[tk.dst + (size_t)w * tk.ldK + t] = acc;
+                else out[tk.dst + (size_t)t * tk.ldK + w] = acc;
+            }
+            if (tk.bias_dst >= 0) {
+                if (y_wide && wok && t == 0) out[tk.bias_dst + w] = wsum;       // bias on the wide (dY) side
+                if (!y_wide && tok && w == 0) out[tk.bias_dst + t] = tsum;      // bias on the thin (dY) side
+            }
+        }
+        __syncthreads();
     }
 }
 
@@ -377,7 +381,7 @@ static int launch_wgrad(const nmb_ts_problem_t* p, const void* save, void* parti
         bool thin = true;      // every remaining task has one side <= d+1
         for (int i = 0; i < nt; ++i) thin = thin && (a.t[i].On <= kThinMax || a.t[i].Kn <= kThinMax);
         if (thin) {
-            wgrad_thin_kernel<T><<<item_small, 128 * kThinSlices, 0, st>>>(a);
+            wgrad_thin_kernel<T><<<item_small, 256 * kThinSlices, 0, st>>>(a);
         } else {
             const size_t smem = 4 * kNC * 64 * sizeof(T);
             NMB_CUDA(cudaFuncSetAttribute(wgrad_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

@@ -59,6 +59,52 @@ template <int WHICH> __global__ void __launch_bounds__(256) math_kernel(double* 
     out[blockIdx.x * blockDim.x + threadIdx.x] = r;
 }
 
+// DFMA and DMMA issued by different warps of the same SM sub-partitions: do they share one pipe?
+__global__ void __launch_bounds__(256) mixed_kernel(double* out, int iters) {
+    const double a0 = 1.0 + threadIdx.x * 1e-9, b0 = 0.999999;
+    double r = 0;
+    if ((threadIdx.x >> 5) & 4) {       // warps 4-7: one per sub-partition
+        double c[8];
+        for (int i = 0; i < 8; ++i) c[i] = i * 0.001;
+        for (int it = 0; it < iters * 8; ++it)
+#pragma unroll
+            for (int i = 0; i < 8; ++i) c[i] = fma(c[i], b0, a0);
+        for (int i = 0; i < 8; ++i) r += c[i];
+    } else {                            // warps 0-3
+        double c[8][2];
+        for (int i = 0; i < 8; ++i) c[i][0] = c[i][1] = i * 0.001;
+        for (int it = 0; it < iters; ++it)
+#pragma unroll
+            for (int i = 0; i < 8; ++i) dmma884(c[i], a0, b0);
+        for (int i = 0; i < 8; ++i) r += c[i][0] + c[i][1];
+    }
+    out[blockIdx.x * blockDim.x + threadIdx.x] = r;
+}
+
+static int run_mixed() {
+    int sms = 0;
+    CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0));
+    const int blocks = sms * 4, threads = 256, iters = 4096;
+    double* buf;
+    CK(cudaMalloc(&buf, sizeof(double) * blocks * threads));
+    cudaEvent_t e0, e1;
+    CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+    float best = 1e30f;
+    for (int rep = 0; rep < 4; ++rep) {
+        CK(cudaEventRecord(e0));
+        mixed_kernel<<<blocks, threads>>>(buf, iters);
+        CK(cudaEventRecord(e1));
+        CK(cudaEventSynchronize(e1));
+        float ms; CK(cudaEventElapsedTime(&ms, e0, e1));
+        if (rep && ms < best) best = ms;
+    }
+    // per block: 4 warps x iters x 8 DMMA x 256 FMA  +  4 warps x iters*8 x 8 DFMA x 32 FMA  (equal FMA counts)
+    const double fma = (double)blocks * 4.0 * iters * 8.0 * (256.0 + 8.0 * 32.0);
+    printf("{\"bench\": \"dfma_and_dmma_concurrent\", \"ms\": %.4f, \"tflops\": %.3f}\n", best, 2.0 * fma / (best * 1e-3) / 1e12);
+    cudaFree(buf);
+    return 0;
+}
+
 // shared-load cost: PAT 0 all lanes one address, 1 = 8 distinct (lane>>2), 2 = 4 distinct (lane&3) stride 32B,
 // 3 = all lanes distinct consecutive.  WIDTH 4/8/16 bytes.  Reports SM cycles per warp-instruction with 8 warps/SM.
 template <int WIDTH, int PAT> __global__ void __launch_bounds__(256) lds_kernel(double* out, long long* cyc, int iters) {
@@ -137,6 +183,7 @@ int main() {
     if (run_math<1>("dmma_m8n8k4", 256.0)) return 1;
     if (run_math<2>("dmma_m16n8k8", 1024.0)) return 1;
     if (run_math<3>("dmma_m16n8k16", 2048.0)) return 1;
+    if (run_mixed()) return 1;
     run_lds<16, 0>(); run_lds<16, 1>(); run_lds<16, 2>(); run_lds<16, 3>();
     run_lds<8, 0>(); run_lds<8, 1>(); run_lds<8, 2>(); run_lds<8, 3>();
     run_lds<4, 0>(); run_lds<4, 3>();
