@@ -59,20 +59,23 @@ NMB_HD double exp_reduce(double x, int& k) {
     const double kf = kd - magic;
     double r = fma(kf, -6.93147180369123816490e-01, x);
     r = fma(kf, -1.90821492927058770002e-10, r);
-    // expm1(r) = r + r^2 (1/2 + r/6 + ... + r^11/13!)
-    double q = 1.6059043836821613e-10;             // 1/13!
-    q = fma(q, r, 2.08767569878681e-09);           // 1/12!
-    q = fma(q, r, 2.505210838544172e-08);          // 1/11!
-    q = fma(q, r, 2.755731922398589e-07);          // 1/10!
-    q = fma(q, r, 2.7557319223985893e-06);         // 1/9!
-    q = fma(q, r, 2.48015873015873e-05);           // 1/8!
-    q = fma(q, r, 1.984126984126984e-04);          // 1/7!
-    q = fma(q, r, 1.388888888888889e-03);          // 1/6!
-    q = fma(q, r, 8.333333333333333e-03);          // 1/5!
-    q = fma(q, r, 4.1666666666666664e-02);         // 1/4!
-    q = fma(q, r, 1.6666666666666666e-01);         // 1/3!
-    q = fma(q, r, 0.5);
-    return fma(q * r, r, r);
+    // expm1(r) = r + r^2 q(r), q = sum_j r^j / (j+2)!  (j <= 11) as even(z) + r odd(z), z = r^2: two independent
+    // Horner chains of depth 5 instead of one of depth 11
+    const double z = r * r;
+    double qe = 2.08767569878681e-09;              // 1/12!
+    double qo = 1.6059043836821613e-10;            // 1/13!
+    qe = fma(qe, z, 2.755731922398589e-07);        // 1/10!
+    qo = fma(qo, z, 2.505210838544172e-08);        // 1/11!
+    qe = fma(qe, z, 2.48015873015873e-05);         // 1/8!
+    qo = fma(qo, z, 2.7557319223985893e-06);       // 1/9!
+    qe = fma(qe, z, 1.388888888888889e-03);        // 1/6!
+    qo = fma(qo, z, 1.984126984126984e-04);        // 1/7!
+    qe = fma(qe, z, 4.1666666666666664e-02);       // 1/4!
+    qo = fma(qo, z, 8.333333333333333e-03);        // 1/5!
+    qe = fma(qe, z, 0.5);                          // 1/2!
+    qo = fma(qo, z, 1.6666666666666666e-01);       // 1/3!
+    const double q = fma(qo, r, qe);
+    return fma(q, z, r);
 }
 
 NMB_HD double pow2i(int k) { return bits_f64((int64_t)(k + 1023) << 52); }

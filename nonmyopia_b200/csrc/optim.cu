@@ -47,8 +47,15 @@ __global__ void adamw_kernel(SegTab tb, int use_tab, nmb_adamw_t hp, T* __restri
         int seg = 0, ti = (int)i, nsp = 1;
         if (use_tab) { ti = transposed_index(tb, (int)i, seg); nsp = tb.splits[seg]; }
         if (nsp > 0) {
+            // split-K partials summed in split order (deterministic); up to 32 loads in flight per thread
             T g = T(0);
-            for (int q = 0; q < nsp; ++q) g += partials[(size_t)q * n + i];
+            for (int q0 = 0; q0 < nsp; q0 += 32) {
+                T pv[32];
+#pragma unroll
+                for (int u = 0; u < 32; ++u) pv[u] = q0 + u < nsp ? partials[(size_t)(q0 + u) * n + i] : T(0);
+#pragma unroll
+                for (int u = 0; u < 32; ++u) g += pv[u];
+            }
             const long long t = (state ? state->step : 0) + 1;
             const double bc1 = 1.0 - ::pow(hp.beta1, (double)t);
             const double bc2s = ::sqrt(1.0 - ::pow(hp.beta2, (double)t));

@@ -388,8 +388,8 @@ __device__ __forceinline__ void mma_policy_forward(const PolicyLayout& lay, cons
 }
 
 // ================================================================== backward step
-constexpr int kStagesBwd = 3;
-constexpr int kMaxRowsMmaBwd = 40;    // 7 row-major adjoint buffers + 3 weight stages in 227 KB
+constexpr int kStagesBwd = 5;          // 8 consumer warps drain a chunk in ~0.5 us: the ring must cover the L2 latency
+constexpr int kMaxRowsMmaBwd = 32;    // 7 row-major adjoint buffers (122 KB) + 5 weight stages (92 KB) in 227 KB
 
 struct MmaBwdSmem {
     double *X0, *X1, *X2, *X3, *X4, *X5, *GH, *GO, *GXY, *carry, *stage;

@@ -22,6 +22,7 @@ template <typename T> struct WgTask {
     int dst, ldK;                        // partial[dst + o*ldK + k]
     int bias_dst;                        // partial[bias_dst + o] or -1
     int item0, n_items;                  // work items of this task
+    int ybulk, abulk;                    // operand rows are 16-byte multiples at 16-byte aligned addresses (TMA-able)
 };
 
 template <typename T> struct WgArgs {
@@ -148,6 +149,11 @@ __global__ void __launch_bounds__(288, 2) wgrad_mma_kernel(const __grid_constant
         }
         fence_barrier_init();
     }
+    // thin operands (K = d+1 or O = d) fill only the first columns of their rows: the rest must read as zero
+    if (tk.On < 64 || tk.Kn < 64) {
+        for (int e = tid; e < kWgStages * kWgStageElems; e += blockDim.x) stage[e] = 0.0;
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
     __syncthreads();
     if (warp == 8) {
         // ---- producer: lane = node row of the chunk
@@ -162,14 +168,20 @@ __global__ void __launch_bounds__(288, 2) wgrad_mma_kernel(const __grid_constant
             if (lane >= valid) {      // ragged tail: zero rows
                 for (int c = 0; c < 64; ++c) { ys[c] = 0.0; as[c] = 0.0; }
             }
-            __syncwarp();
             const unsigned full = full0 + 8 * slot;
-            if (lane == 0) mbar_arrive_expect_tx(full, (ybytes + abytes) * (unsigned)valid);
+            // rows that are not 16-byte multiples (K = d+1) are copied by the lane itself
+            if (lane < valid) {
+                const long long node = n0 + lane;
+                if (!tk.ybulk) for (int c = 0; c < tk.On; ++c) ys[c] = tk.dY[(size_t)node * tk.ldY + tk.o0 + c];
+                if (!tk.abulk) for (int c = 0; c < tk.Kn; ++c) as[c] = tk.A[(size_t)node * tk.ldA + tk.k0 + c];
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive_expect_tx(full, ((tk.ybulk ? ybytes : 0u) + (tk.abulk ? abytes : 0u)) * (unsigned)valid);
             __syncwarp();
             if (lane < valid) {
                 const long long node = n0 + lane;
-                bulk_g2s(smem_u32(ys), tk.dY + (size_t)node * tk.ldY + tk.o0, ybytes, full);
-                bulk_g2s(smem_u32(as), tk.A + (size_t)node * tk.ldA + tk.k0, abytes, full);
+                if (tk.ybulk) bulk_g2s(smem_u32(ys), tk.dY + (size_t)node * tk.ldY + tk.o0, ybytes, full);
+                if (tk.abulk) bulk_g2s(smem_u32(as), tk.A + (size_t)node * tk.ldA + tk.k0, abytes, full);
             }
         }
         return;
@@ -204,6 +216,7 @@ __global__ void __launch_bounds__(288, 2) wgrad_mma_kernel(const __grid_constant
         if (lane == 0) mbar_arrive(empty0 + 8 * slot);
     }
     double* out = args.partials + (size_t)split * args.n_params;
+    const bool vec_ok = !(tk.ldK & 1) && !(tk.dst & 1) && !(args.n_params & 1);
 #pragma unroll
     for (int i = 0; i < 2; ++i) {
         const int o = o0 + 8 * i + fr;
@@ -211,83 +224,20 @@ __global__ void __launch_bounds__(288, 2) wgrad_mma_kernel(const __grid_constant
 #pragma unroll
             for (int t = 0; t < 4; ++t) {
                 const int k = k0 + 8 * t + 2 * fk;
-                if (k < tk.Kn)
-                    *reinterpret_cast<double2*>(out + tk.dst + (size_t)o * tk.ldK + k) = make_double2(acc[i][t][0], acc[i][t][1]);
+                double* pp = out + tk.dst + (size_t)o * tk.ldK + k;
+                if (vec_ok && k + 1 < tk.Kn) {
+                    *reinterpret_cast<double2*>(pp) = make_double2(acc[i][t][0], acc[i][t][1]);
+                } else {
+                    if (k < tk.Kn) pp[0] = acc[i][t][0];
+                    if (k + 1 < tk.Kn) pp[1] = acc[i][t][1];
+                }
             }
         }
     }
     if (tk.bias_dst >= 0 && tid < tk.On) out[tk.bias_dst + tid] = bacc;
 }
 
-// ------------------------------------------------------------------ thin tasks (K = d+1 or O = d)
-// dW = sum_nodes wide[node][w] * thin[node][t], t < 17 (d + 1 or d).  One thread per (w, t mod 4) pair and node
-// slice, 8 independent loads of each operand in flight per thread (the kernel is a single HBM pass over the wide
-// operand: latency, not arithmetic, is what has to be hidden); slices are reduced in fixed order.
-constexpr int kThinMax = NMB_MAX_DIM + 1;
-constexpr int kThinSlices = 4;
-constexpr int kThinU = 8;
-
-template <typename T>
-__global__ void __launch_bounds__(256 * kThinSlices) wgrad_thin_kernel(const __grid_constant__ WgArgs<T> args) {
-    if (args.done_flag && *args.done_flag) return;
-    __shared__ T red[3][256];
-    const int item = blockIdx.x;
-    int ti = 0;
-    while (ti + 1 < args.n_tasks && item >= args.t[ti + 1].item0) ++ti;
-    const WgTask<T>& tk = args.t[ti];
-    const int split = item - tk.item0;
-    const long long nb = tk.n_begin + (long long)split * args.chunk;
-    const long long ne = min(tk.n_end, nb + args.chunk);
-    const bool y_wide = tk.On >= tk.Kn;
-    const T* Wd = y_wide ? tk.dY : tk.A;
-    const T* Th = y_wide ? tk.A : tk.dY;
-    const int ldW = y_wide ? tk.ldY : tk.ldA, w0 = y_wide ? tk.o0 : tk.k0, nW = y_wide ? tk.On : tk.Kn;
-    const int ldT = y_wide ? tk.ldA : tk.ldY, t0 = y_wide ? tk.k0 : tk.o0, nT = y_wide ? tk.Kn : tk.On;
-    const int w = threadIdx.x & 63, t4 = (threadIdx.x >> 6) & 3, q = threadIdx.x >> 8, pr = threadIdx.x & 255;
-    T* out = args.partials + (size_t)split * args.n_params;
-    for (int tg = 0; tg < nT; tg += 4) {
-        const int t = tg + t4;
-        const bool wok = w < nW, tok = t < nT;
-        T acc = T(0), wsum = T(0), tsum = T(0);
-        for (long long node = nb + q; node < ne; node += kThinSlices * kThinU) {
-            T wv[kThinU], tv[kThinU];
-#pragma unroll
-            for (int u = 0; u < kThinU; ++u) {
-                const long long nu = node + (long long)u * kThinSlices;
-                const bool ok = nu < ne;
-                wv[u] = (ok && wok) ? Wd[(size_t)nu * ldW + w0 + w] : T(0);
-                tv[u] = (ok && tok) ? __ldg(Th + (size_t)nu * ldT + t0 + t) : T(0);
-            }
-#pragma unroll
-            for (int u = 0; u < kThinU; ++u) {
-                acc = fma(wv[u], tv[u], acc);
-                wsum += wv[u];
-                tsum += tv[u];
-            }
-        }
-        // fixed-order reduction over the node slices (deterministic)
-        T vals[3] = {acc, wsum, tsum};
-        for (int sl = 1; sl < kThinSlices; ++sl) {
-            if (q == sl) {
-#pragma unroll
-                for (int j = 0; j < 3; ++j) red[j][pr] = sl == 1 ? vals[j] : red[j][pr] + vals[j];
-            }
-            __syncthreads();
-        }
-        if (q == 0) {
-            acc += red[0][pr]; wsum += red[1][pr]; tsum += red[2][pr];
-            if (wok && tok) {
-                if (y_wide) out[tk.dst + (size_t)w * tk.ldK + t] = acc;
-                else out[tk.dst + (size_t)t * tk.ldK + w] = acc;
-            }
-            if (tk.bias_dst >= 0) {
-                if (y_wide && wok && t == 0) out[tk.bias_dst + w] = wsum;       // bias on the wide (dY) side
-                if (!y_wide && tok && w == 0) out[tk.bias_dst + t] = tsum;      // bias on the thin (dY) side
-            }
-        }
-        __syncthreads();
-    }
-}
+constexpr int kThinMax = NMB_MAX_DIM + 1;     // a "thin" operand side: K = d + 1 or O = d
 
 static void launch_wgrad_mma(const WgArgs<double>& am, int items, cudaStream_t st) {
     const size_t smem = (size_t)kWgStages * kWgStageElems * 8 + 2 * kWgStages * 8;
@@ -296,8 +246,8 @@ static void launch_wgrad_mma(const WgArgs<double>& am, int items, cudaStream_t s
 }
 static void launch_wgrad_mma(const WgArgs<float>&, int, cudaStream_t) {}
 
-// nodes per work item: a multiple of 32, at most 32 splits per segment, and - for the H x H tasks (7 over all
-// nodes, 3 over the design levels, 3 over the action level) - no more items than the 2 CTAs/SM that are resident
+// nodes per work item: a multiple of 32, at most 32 splits per segment, and - for the H x H tasks (8 over all
+// nodes, 4 over the design levels, 4 over the action level, thin ones included) - no more items than the 2 CTAs/SM that are resident
 static int wgrad_chunk(int L, long long N) {
     const long long nodes = (long long)(L + 1) * N;
     long long ch = (nodes + 31) / 32;
@@ -305,7 +255,7 @@ static int wgrad_chunk(int L, long long N) {
     if (ch < 64) ch = 64;
     const long long slots = 2LL * sm_count();
     auto items = [&](long long c) {
-        return 7 * ((nodes + c - 1) / c) + (L > 0 ? 3 * (((long long)L * N + c - 1) / c) : 0) + 3 * ((N + c - 1) / c);
+        return 8 * ((nodes + c - 1) / c) + (L > 0 ? 4 * (((long long)L * N + c - 1) / c) : 0) + 4 * ((N + c - 1) / c);
     };
     if (items(ch) > slots) {
         // the first chunk size that fits in one wave, unless it is a poor fit anyway (then keep 2 balanced waves)
@@ -341,7 +291,7 @@ static int launch_wgrad(const nmb_ts_problem_t* p, const void* save, void* parti
     auto add = [&](const T* dY, int ldY, int o0, int On, const T* A, int ldA, int k0, int Kn, long long nb,
                    long long ne, int wseg, int orow0, int kcol0, int bseg) {
         if (ne <= nb) return;
-        const bool big = use_mma && On == H && Kn == H;
+        const bool big = use_mma && (On == H || On <= kThinMax) && (Kn == H || Kn <= kThinMax);
         WgTask<T>& t = big ? am.t[ntm++] : a.t[nt++];
         int& item = big ? itemm : item_small;
         t.dY = dY; t.ldY = ldY; t.o0 = o0; t.On = On;
@@ -350,6 +300,8 @@ static int launch_wgrad(const nmb_ts_problem_t* p, const void* save, void* parti
         t.ldK = lay.K[wseg];
         t.dst = lay.off[wseg] + orow0 * t.ldK + kcol0;
         t.bias_dst = bseg >= 0 ? lay.off[bseg] + orow0 : -1;
+        t.ybulk = !(ldY & 1) && !(o0 & 1) && !(On & 1);
+        t.abulk = !(ldA & 1) && !(k0 & 1) && !(Kn & 1);
         t.item0 = item;
         t.n_items = (int)((ne - nb + a.chunk - 1) / a.chunk);
         item += t.n_items;
@@ -378,15 +330,9 @@ static int launch_wgrad(const nmb_ts_problem_t* p, const void* save, void* parti
     // bias rows of the gate blocks: offsets inside bih/bhh follow orow0 (handled by bias_dst above)
     if (itemm > 0) launch_wgrad_mma(am, itemm, st);
     if (item_small > 0) {
-        bool thin = true;      // every remaining task has one side <= d+1
-        for (int i = 0; i < nt; ++i) thin = thin && (a.t[i].On <= kThinMax || a.t[i].Kn <= kThinMax);
-        if (thin) {
-            wgrad_thin_kernel<T><<<item_small, 256 * kThinSlices, 0, st>>>(a);
-        } else {
-            const size_t smem = 4 * kNC * 64 * sizeof(T);
-            NMB_CUDA(cudaFuncSetAttribute(wgrad_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            wgrad_kernel<T><<<item_small, 256, smem, st>>>(a);
-        }
+        const size_t smem = 4 * kNC * 64 * sizeof(T);
+        NMB_CUDA(cudaFuncSetAttribute(wgrad_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        wgrad_kernel<T><<<item_small, 256, smem, st>>>(a);
     }
     NMB_LAUNCH_CHECK();
     return 0;

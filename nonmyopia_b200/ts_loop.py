@@ -82,8 +82,8 @@ class TSAMLoop:
             self._cand = self.state[56:72].view(torch.float64)
             self.grad = torch.zeros_like(self.theta)
             self._one_split = (C.c_int32 * 20)()
-        # rollout_fwd, objective, snapshot, rollout_bwd, wgrad (tensor-pipe + thin), adamw, advance (+ decide, reduce when sharded)
-        self.n_launches_per_iter = 8 if group is None else 10
+        # rollout_fwd, objective, snapshot, rollout_bwd, wgrad, adamw, advance (+ decide, reduce when sharded)
+        self.n_launches_per_iter = 7 if group is None else 9
 
     # ------------------------------------------------------------------ one iteration
     def _iteration(self, draws=None, mark=None) -> None:

@@ -105,6 +105,38 @@ static int run_mixed() {
     return 0;
 }
 
+// DMMA dependent-issue latency: 1 warp per SM sub-partition, NACC independent accumulator tiles
+template <int NACC> __global__ void __launch_bounds__(128) dmma_chain_kernel(double* out, long long* cyc, int iters) {
+    const double a0 = 1.0 + threadIdx.x * 1e-9, b0 = 0.999999;
+    double c[NACC][2];
+    for (int i = 0; i < NACC; ++i) c[i][0] = c[i][1] = i * 0.001;
+    const long long t0 = clock64();
+    for (int it = 0; it < iters; ++it)
+#pragma unroll
+        for (int i = 0; i < NACC; ++i) dmma884(c[i], a0, b0);
+    const long long t1 = clock64();
+    double r = 0;
+    for (int i = 0; i < NACC; ++i) r += c[i][0] + c[i][1];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = r;
+    if (threadIdx.x == 0) cyc[blockIdx.x] = t1 - t0;
+}
+template <int NACC> static int run_chain() {
+    int sms = 0;
+    CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0));
+    double* buf; long long* cyc;
+    CK(cudaMalloc(&buf, sizeof(double) * sms * 128));
+    CK(cudaMalloc(&cyc, sizeof(long long) * sms));
+    const int iters = 4096;
+    for (int rep = 0; rep < 2; ++rep) dmma_chain_kernel<NACC><<<sms, 128>>>(buf, cyc, iters);
+    CK(cudaDeviceSynchronize());
+    long long h[4];
+    CK(cudaMemcpy(h, cyc, sizeof(h), cudaMemcpyDeviceToHost));
+    printf("{\"bench\": \"dmma_chain\", \"independent_tiles\": %d, \"cycles_per_dmma\": %.2f}\n", NACC,
+           (double)h[0] / ((double)iters * NACC));
+    cudaFree(buf); cudaFree(cyc);
+    return 0;
+}
+
 // shared-load cost: PAT 0 all lanes one address, 1 = 8 distinct (lane>>2), 2 = 4 distinct (lane&3) stride 32B,
 // 3 = all lanes distinct consecutive.  WIDTH 4/8/16 bytes.  Reports SM cycles per warp-instruction with 8 warps/SM.
 template <int WIDTH, int PAT> __global__ void __launch_bounds__(256) lds_kernel(double* out, long long* cyc, int iters) {
@@ -184,6 +216,7 @@ int main() {
     if (run_math<2>("dmma_m16n8k8", 1024.0)) return 1;
     if (run_math<3>("dmma_m16n8k16", 2048.0)) return 1;
     if (run_mixed()) return 1;
+    run_chain<1>(); run_chain<2>(); run_chain<4>(); run_chain<8>();
     run_lds<16, 0>(); run_lds<16, 1>(); run_lds<16, 2>(); run_lds<16, 3>();
     run_lds<8, 0>(); run_lds<8, 1>(); run_lds<8, 2>(); run_lds<8, 3>();
     run_lds<4, 0>(); run_lds<4, 3>();
