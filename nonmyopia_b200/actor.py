@@ -26,6 +26,7 @@ import torch
 from torch import Tensor
 
 from . import _lib
+from . import sharding as sh
 from . import ts_engine as te
 from .acqfs import SobolQMCNormalSampler, qBOAcqf, qMultiStepHEntropySearch
 from .amortized_network import AmortizedNetwork
@@ -91,6 +92,8 @@ class Actor:
         # "device" (default): rotation angles / cost noise drawn in-kernel, CUDA-graph loop;
         # "host": drawn by the host generators in the reference's order (seed-stream parity)
         self.rng_mode = getattr(parms, "rng_mode", "device")
+        # restarts sharded over the ranks of this torch.distributed group (None: single GPU); SURVEY 8e
+        self.group = getattr(parms, "process_group", None)
 
     # ------------------------------------------------------------------ construct_acqf
     def construct_acqf(self, surr_model, buffer, **kwargs):
@@ -141,13 +144,14 @@ class Actor:
         if p.amortized:
             self._pretrain(buffer, prev_X, prev_y, nf)
             return
+        rank, world = sh.world_of(self.group)
+        lo, hi = sh.restart_range(p.n_restarts, rank, world)
         if bo_iter == 0 or not p.algo_ts:
             tree = self._random_tree(prev_X[0], nf, p.n_restarts)
-            self.maps = [_logit(torch.clamp(x.reshape(-1, d).to(device=dev, dtype=dt), min=0.01, max=0.99))
-                         .requires_grad_(True) for x in tree]
+            full = [torch.clamp(x.reshape(-1, d).to(device=dev, dtype=dt), min=0.01, max=0.99) for x in tree]
         else:
             # warm start: rotate the previous best trajectory about its first point (actor.py:294-379)
-            maps = [torch.sigmoid(x.detach()) for x in self.maps]
+            maps = [torch.sigmoid(sh.gather_level(x.detach(), p.n_restarts, self.group)) for x in self.maps]
             idx = prev_chosen_idx.long() if torch.is_tensor(prev_chosen_idx) else int(prev_chosen_idx)
             R = [torch.eye(d).to(prev_X)] + [generate_random_rotation_matrix(d).to(prev_X)
                                              for _ in range(p.n_restarts - 1)]
@@ -159,7 +163,10 @@ class Actor:
                 maps[lah - 1] = torch.clamp(rot, min=0.01, max=0.99).reshape(-1, d)
             a = generate_random_points_batch(maps[L - 1], p.cost_func_hypers["radius"], nf[-1] * p.n_actions)
             maps[L] = torch.clamp(a.to(device=dev, dtype=dt), min=0.01, max=0.99).reshape(-1, d)
-            self.maps = [_logit(x).requires_grad_(True) for x in maps]
+            full = maps
+        # every rank draws the full-size initialisation from the same host seed and keeps its restarts (8e)
+        self.maps = [_logit(sh.shard_level(x, p.n_restarts, lo, hi) if world > 1 else x).requires_grad_(True)
+                     for x in full]
         self._parameters = self.maps
 
     def _pretrain(self, buffer, prev_X, prev_y, nf):
@@ -207,12 +214,14 @@ class Actor:
         if embedder is not None:
             raise NotImplementedError("discrete environments are outside the B200 hot-path scope")
         p = self.parms
-        n_r = p.n_restarts
+        rank, world = sh.world_of(self.group)
+        lo, hi = sh.restart_range(p.n_restarts, rank, world)
+        n_r = hi - lo                                   # this rank's restarts (all of them on one GPU)
         prev_X = buffer["x"][iteration - 1:iteration].expand(n_r, -1)
         prev_y = buffer["y"][iteration - 1:iteration].expand(n_r, -1)
         prev_h = buffer["h"][iteration - 1:iteration].expand(n_r, -1)
         if p.amortized:
-            prev_h = prev_h + self.hidden_noise
+            prev_h = prev_h + self.hidden_noise[lo:hi]
         prev_cost = (float(buffer["cost"][p.n_initial_points:iteration].sum())
                      if iteration > p.n_initial_points else 0.0)
         is_hes = p.algo.startswith("HES")
@@ -229,6 +238,8 @@ class Actor:
         if is_hes:
             self.acqf.clean_dump_model()
         best_loss, best_cost, best_KL = res["best_loss"], res["best_cost"], res["best_KL"]
+        if world > 1:
+            return self._select_sharded(res, buffer, iteration, prev_cost, save_trajectory)
         idx = torch.argmin(best_loss + best_cost + best_KL)
         if save_trajectory:
             with open(p.save_dir + f"/trajectory_{iteration}.pkl", "wb") as fh:
@@ -243,19 +254,52 @@ class Actor:
         return {"all_losses": best_loss, "all_costs": best_cost, "loss": best_loss[idx], "cost": acqf_cost,
                 "next_X": next_X, "actions": actions, "hidden_state": hidden_state, "chosen_idx": idx}
 
+    def _select_sharded(self, res, buffer, iteration, prev_cost, save_trajectory):
+        """Final selection over ALL ranks' restarts: all-gather of the per-restart totals,
+        arg-min, the owner broadcasts the chosen restart's next_X / actions / hidden state.  Every rank
+        returns the same dictionary as the unsharded ``query``."""
+        p = self.parms
+        n_all, d = p.n_restarts, p.x_dim
+        total = res["best_loss"] + res["best_cost"] + res["best_KL"]
+        _, idx, owner, li = sh.select_best(total, n_all, self.group)
+        all_losses = sh.gather_restarts(res["best_loss"], n_all, self.group)
+        all_costs = sh.gather_restarts(res["best_cost"], n_all, self.group)
+        dev, dt = total.device, total.dtype
+        acts = res["best_actions"]
+        a_shape = (*acts.shape[:-3], *acts.shape[-2:])
+        bc = lambda t, shape: sh.broadcast_from_owner(t, shape, dt, dev, owner, self.group)
+        mine = sh.world_of(self.group)[0] == owner
+        next_X = bc(res["best_next_X"][0][li].reshape(1, -1) if mine else None, (1, d))
+        actions = bc(acts[..., li, :, :] if mine else None, a_shape)
+        hidden_state = None
+        if p.amortized:
+            hidden_state = bc(res["best_hidden_state"][0][li:li + 1] if mine else None, (1, p.hidden_dim))
+        idx_t = torch.tensor(idx, device=dev)
+        if save_trajectory:
+            tag = f"{iteration}.rank{sh.world_of(self.group)[0]}"
+            with open(p.save_dir + f"/trajectory_{tag}.pkl", "wb") as fh:
+                pickle.dump((res["saved_trajectory"], idx_t), fh)
+            with open(p.save_dir + f"/lossncost_{tag}.pkl", "wb") as fh:
+                pickle.dump((res["saved_loss"], res["saved_cost"]), fh)
+        acqf_cost = self.acqf.cost_function(prev_X=buffer["x"][iteration - 1:iteration], current_X=next_X,
+                                            previous_cost=prev_cost).detach()
+        return {"all_losses": all_losses, "all_costs": all_costs, "loss": all_losses[idx], "cost": acqf_cost,
+                "next_X": next_X, "actions": actions, "hidden_state": hidden_state, "chosen_idx": idx_t}
+
     def _query_amortized(self, prev_X, prev_y, prev_h, prev_cost, past_initial, save_trajectory):
         """HES-TS-AM: device-resident AdamW loop (one CUDA graph per iteration)."""
         p, acqf = self.parms, self.acqf
-        L, d, H, N = self.algo_lookahead_steps, p.x_dim, p.hidden_dim, p.n_restarts
+        L, d, H, N = self.algo_lookahead_steps, p.x_dim, p.hidden_dim, prev_X.shape[0]
         eng = acqf._ts_engine(acqf.f, d, H, N, p.torch_dtype)
         eng.seed = acqf.rng_seed
         theta0 = self.maps.flat_parameters().detach()
         record = bool(save_trajectory)
         loop = TSAMLoop(eng, theta0, prev_X, prev_y, prev_h, budget=float(p.budget), lr=p.acq_opt_lr,
                         past_initial=past_initial, prev_cost=prev_cost, max_iter=p.acq_opt_iter,
-                        record_history=record, record_trajectory=record)
+                        record_history=record, record_trajectory=record, n_global=p.n_restarts, group=self.group)
         if self.rng_mode == "host":
-            draws = _HostDraws(acqf, L, N, d, prev_X)
+            rank, world = sh.world_of(self.group)
+            draws = _HostDraws(acqf, L, p.n_restarts, d, prev_X, sh.restart_range(p.n_restarts, rank, world))
             st = loop.run(p.acq_opt_iter, draws_per_iter=draws)
         else:
             st = loop.run(p.acq_opt_iter)
@@ -283,41 +327,19 @@ class Actor:
         return out
 
     def _query_free(self, prev_X, prev_y, prev_h, prev_cost, past_initial, save_trajectory):
-        """Free-parameter algorithms: eager loop over ``acqf.forward`` + fused AdamW kernel."""
+        """Free-parameter algorithms: eager loop over ``acqf.forward`` + fused AdamW kernel
+        (``sharding.free_restart_loop`` restates actor.py:558-656; the parameters hold this rank's restarts)."""
         p, acqf = self.parms, self.acqf
         params = list(self._parameters)
         opt = _FlatAdamW(params, lr=p.acq_opt_lr)
-        best = dict(loss=torch.tensor([float("inf")], device=p.device), cost=torch.tensor([float("inf")],
-                    device=p.device), KL=0)
-        snap, stall = {}, 0
-        saved_trajectory, saved_loss, saved_cost = [], [], []
-        for ep in range(p.acq_opt_iter):
-            local_maps = [torch.sigmoid(x) for x in params]
-            if save_trajectory:
-                saved_trajectory.append([x.cpu().detach().tolist() for x in local_maps])
-            rd = acqf.forward(prev_X=prev_X, prev_y=prev_y, prev_hid_state=prev_h, maps=local_maps, embedder=None,
-                              prev_cost=prev_cost, enable_noise=False)
-            acqf_loss, acqf_cost = rd["acqf_loss"], rd["acqf_cost"]
-            if save_trajectory:
-                saved_loss.append(acqf_loss.tolist())
-                saved_cost.append(acqf_cost.tolist())
-            loss = acqf_loss + abs(p.budget - acqf_cost)
-            chosen = torch.argmin(loss)
-            if ep == 0 or bool(loss[chosen] < (best["loss"] + best["cost"]).min()):
-                best = dict(loss=acqf_loss.detach(), cost=acqf_cost.detach(), KL=0)
-                snap = dict(X=[x.detach() for x in rd["X"]], actions=rd["actions"].detach())
-                stall = 0
-            elif past_initial or ep >= 200:
-                stall += 1
-            grads = torch.autograd.grad(loss.mean(), params, allow_unused=True)
-            opt.step(grads)
-            if ep % 50 == 0:
-                print(f"Epoch {ep:05d}\tLoss {acqf_loss[chosen].item():.5f}\tCost: {acqf_cost[chosen].item():.5f}")
-            if stall > 50:
-                break
-        return dict(best_loss=best["loss"], best_cost=best["cost"], best_KL=0, best_next_X=snap["X"],
-                    best_actions=snap["actions"], best_hidden_state=None, saved_trajectory=saved_trajectory,
-                    saved_loss=saved_loss, saved_cost=saved_cost)
+
+        def objective(local_maps):
+            return acqf.forward(prev_X=prev_X, prev_y=prev_y, prev_hid_state=prev_h, maps=local_maps, embedder=None,
+                                prev_cost=prev_cost, enable_noise=False)
+
+        return sh.free_restart_loop(objective, params, opt.step, budget=p.budget, n_iter=p.acq_opt_iter,
+                                    past_initial=past_initial, n_global=p.n_restarts, group=self.group,
+                                    save_trajectory=save_trajectory)
 
 
 def _prior_free_sample(gp, x: Tensor) -> Tensor:
@@ -335,15 +357,20 @@ class _HostDraws:
     """Per-iteration draws in the reference's order: main rollout (action rotation, cost noise),
     then the frozen "original" rollout (every call rotated)."""
 
-    def __init__(self, acqf, L, N, d, like):
+    def __init__(self, acqf, L, N, d, like, own=None):
         self.args = (acqf, L, N, d, like)
+        self.own = own              # (lo, hi): this rank's restarts of the full-size draws (SURVEY 8e)
 
     def __len__(self):
         return 1 << 30
 
     def __getitem__(self, ep):
         acqf, L, N, d, like = self.args
-        return (*acqf._host_draws(L, N, d, like, False), *acqf._host_draws(L, N, d, like, True))
+        out = (*acqf._host_draws(L, N, d, like, False), *acqf._host_draws(L, N, d, like, True))
+        if self.own is not None and self.own != (0, N):
+            lo, hi = self.own
+            out = tuple(t[:, lo:hi].contiguous() for t in out)
+        return out
 
 
 class _FlatAdamW:

@@ -1,0 +1,185 @@
+"""Restart sharding over ranks: one process per GPU, rank ``g`` owns a block of the
+``n_restarts`` axis of every level tensor.  The data path has no collective; global semantics of the
+reference's loop (actor.py:558-656) are kept by
+
+* C3: one all-reduce(MIN) of two doubles per Adam iteration - ``min_r total`` and, for the snapshot,
+  ``min_r (loss + cost + KL)`` - so every rank takes the same snapshot / early-stop decision
+  (actor.py:622-639, 655);
+* the global mean of actor.py:641 (``loss.mean()`` over ALL restarts): the local backward is seeded with
+  ``1 / n_restarts_global``;
+* C1: a final all-gather of ``best_loss + best_cost + best_KL`` -> arg-min -> the owner broadcasts the
+  selected restart's ``next_X`` / ``actions`` / ``hidden_state`` (actor.py:662, 677-733).
+
+Everything here is backend-agnostic host logic over ``torch.distributed`` (NCCL on the GPUs; the
+world_size-2 ``gloo`` tests in tests/test_sharding_cpu.py drive it with the CPU oracle as the objective).
+"""
+from __future__ import annotations
+
+from typing import Callable, Dict, List, Optional, Sequence, Tuple
+
+import torch
+from torch import Tensor
+
+
+def _dist():
+    import torch.distributed as dist
+    return dist
+
+
+def world_of(group) -> Tuple[int, int]:
+    """(rank, world_size) of ``group``; (0, 1) when ``group`` is None (single GPU)."""
+    if group is None:
+        return 0, 1
+    dist = _dist()
+    return dist.get_rank(group), dist.get_world_size(group)
+
+
+def restart_range(n_restarts: int, rank: int, world: int) -> Tuple[int, int]:
+    """Contiguous block of restarts owned by ``rank``; ragged counts give the first
+    ``n_restarts % world`` ranks one extra restart."""
+    if not 0 <= rank < world:
+        raise ValueError(f"rank {rank} outside world of {world}")
+    if n_restarts < world:
+        raise ValueError(f"{n_restarts} restarts cannot be sharded over {world} ranks")
+    base, extra = divmod(n_restarts, world)
+    lo = rank * base + min(rank, extra)
+    return lo, lo + base + (1 if rank < extra else 0)
+
+
+def shard_level(t: Tensor, n_restarts: int, lo: int, hi: int) -> Tensor:
+    """Rows of restarts ``[lo, hi)`` of a flattened level tensor ``[cnt_s, ...]``.
+
+    The reference flattens ``[*nf_rev[:s], n_r, ...]`` (actor.py:240-247, acqfs.py:333-345): the restart
+    index is the FASTEST batch index, so a shard is a strided slice, not a contiguous block."""
+    if t.shape[0] % n_restarts:
+        raise ValueError(f"leading dim {t.shape[0]} is not a multiple of n_restarts={n_restarts}")
+    v = t.reshape(t.shape[0] // n_restarts, n_restarts, *t.shape[1:])
+    return v[:, lo:hi].reshape(-1, *t.shape[1:]).contiguous()
+
+
+def unshard_level(parts: Sequence[Tensor], counts: Sequence[int]) -> Tensor:
+    """Inverse of ``shard_level`` given every rank's shard (in rank order) and restart count."""
+    views = [p.reshape(p.shape[0] // c, c, *p.shape[1:]) for p, c in zip(parts, counts)]
+    full = torch.cat(views, dim=1)
+    return full.reshape(-1, *full.shape[2:])
+
+
+def allreduce_min(values: Tensor, group) -> Tensor:
+    """In-place MIN over ranks (no-op for ``group is None``); ``values`` holds a few doubles."""
+    if group is not None:
+        dist = _dist()
+        dist.all_reduce(values, op=dist.ReduceOp.MIN, group=group)
+    return values
+
+
+def allreduce_sum(values: Tensor, group) -> Tensor:
+    if group is not None:
+        dist = _dist()
+        dist.all_reduce(values, op=dist.ReduceOp.SUM, group=group)
+    return values
+
+
+def gather_restarts(local: Tensor, n_restarts: int, group) -> Tensor:
+    """All-gather a per-restart vector ``[n_local, ...]`` into ``[n_restarts, ...]`` (rank order = restart
+    order).  Ragged shards are padded to the largest shard for the collective."""
+    rank, world = world_of(group)
+    if world == 1:
+        return local
+    dist = _dist()
+    counts = [restart_range(n_restarts, r, world) for r in range(world)]
+    width = max(hi - lo for lo, hi in counts)
+    pad = local.new_zeros((width, *local.shape[1:]))
+    pad[:local.shape[0]] = local
+    out = [torch.empty_like(pad) for _ in range(world)]
+    dist.all_gather(out, pad, group=group)
+    return torch.cat([o[:hi - lo] for o, (lo, hi) in zip(out, counts)], dim=0)
+
+
+def gather_level(local: Tensor, n_restarts: int, group) -> Tensor:
+    """All ranks' shards of a flattened level tensor ``[cnt_s_local, ...]`` reassembled into the unsharded
+    ``[cnt_s, ...]`` layout (restart index fastest)."""
+    rank, world = world_of(group)
+    if world == 1:
+        return local
+    lo, hi = restart_range(n_restarts, rank, world)
+    n_loc = hi - lo
+    v = local.reshape(local.shape[0] // n_loc, n_loc, *local.shape[1:]).transpose(0, 1).contiguous()
+    full = gather_restarts(v, n_restarts, group)                  # [n_restarts, branches, ...]
+    return full.transpose(0, 1).reshape(-1, *local.shape[1:]).contiguous()
+
+
+def select_best(total_local: Tensor, n_restarts: int, group) -> Tuple[Tensor, int, int, int]:
+    """C1: all-gather the per-restart totals, arg-min (first minimum, like ``torch.argmin`` on the
+    unsharded vector).  Returns (all totals [n_restarts], global index, owner rank, index inside the owner)."""
+    rank, world = world_of(group)
+    totals = gather_restarts(total_local, n_restarts, group)
+    idx = int(torch.argmin(totals))
+    for r in range(world):
+        lo, hi = restart_range(n_restarts, r, world)
+        if lo <= idx < hi:
+            return totals, idx, r, idx - lo
+    raise AssertionError("unreachable")
+
+
+def broadcast_from_owner(t: Optional[Tensor], shape, dtype, device, owner: int, group) -> Tensor:
+    """The owner's tensor on every rank (``t`` is ignored on the other ranks)."""
+    rank, world = world_of(group)
+    if world == 1:
+        return t
+    dist = _dist()
+    buf = t.contiguous().clone() if rank == owner else torch.empty(shape, dtype=dtype, device=device)
+    dist.broadcast(buf, src=dist.get_global_rank(group, owner), group=group)
+    return buf
+
+
+def free_restart_loop(objective: Callable[[List[Tensor]], Dict], params: List[Tensor],
+                      opt_step: Callable[[Sequence[Optional[Tensor]]], None], *, budget: float, n_iter: int,
+                      past_initial: bool, n_global: Optional[int] = None, group=None, save_trajectory: bool = False,
+                      log: Optional[Callable[[str], None]] = print) -> Dict:
+    """The reference's AdamW loop for free-parameter algorithms (actor.py:558-656; HES-TS, HES-MC, qEI ... qKG)
+    over this rank's restarts.
+
+    ``objective(local_maps)`` evaluates ``acqf.forward`` on ``[sigmoid(p) for p in params]`` and returns the
+    reference's dict (``acqf_loss`` / ``acqf_cost`` per local restart, ``X``, ``actions``); ``opt_step(grads)``
+    applies AdamW (a ``None`` gradient leaves its tensor untouched, actor.py:641-648).  With a process group
+    the decision values are MIN-reduced and the backward is seeded with ``1 / n_global``."""
+    n_local = None
+    best = dict(loss=None, cost=None, KL=0)
+    best_min = float("inf")
+    snap, stall = {}, 0
+    saved_trajectory, saved_loss, saved_cost = [], [], []
+    n_done = 0
+    for ep in range(n_iter):
+        local_maps = [torch.sigmoid(x) for x in params]
+        if save_trajectory:
+            saved_trajectory.append([x.cpu().detach().tolist() for x in local_maps])
+        rd = objective(local_maps)
+        acqf_loss, acqf_cost = rd["acqf_loss"], rd["acqf_cost"]
+        if n_local is None:
+            n_local = acqf_loss.shape[0]
+            n_global = n_local if n_global is None else int(n_global)
+        if save_trajectory:
+            saved_loss.append(acqf_loss.tolist())
+            saved_cost.append(acqf_cost.tolist())
+        loss = acqf_loss + abs(budget - acqf_cost)
+        chosen = torch.argmin(loss)
+        cand = torch.stack([loss.detach()[chosen], (acqf_loss + acqf_cost).detach().min()])
+        cand = allreduce_min(cand, group).tolist()
+        if ep == 0 or cand[0] < best_min:
+            best = dict(loss=acqf_loss.detach(), cost=acqf_cost.detach(), KL=0)
+            best_min = cand[1]
+            snap = dict(X=[x.detach() for x in rd["X"]], actions=rd["actions"].detach())
+            stall = 0
+        elif past_initial or ep >= 200:
+            stall += 1
+        seed = loss.mean() if n_global == n_local else loss.sum() / n_global
+        grads = torch.autograd.grad(seed, params, allow_unused=True)
+        opt_step(grads)
+        n_done = ep + 1
+        if log is not None and ep % 50 == 0:
+            log(f"Epoch {ep:05d}\tLoss {acqf_loss[chosen].item():.5f}\tCost: {acqf_cost[chosen].item():.5f}")
+        if stall > 50:
+            break
+    return dict(best_loss=best["loss"], best_cost=best["cost"], best_KL=0, best_next_X=snap["X"],
+                best_actions=snap["actions"], best_hidden_state=None, saved_trajectory=saved_trajectory,
+                saved_loss=saved_loss, saved_cost=saved_cost, n_iter=n_done)
