@@ -255,7 +255,8 @@ def run_b200(args, rank, world, local_rank):
         barrier()
         ms_total = e0.elapsed_time(e1)
         # per-kernel timing of the same steps (eager launches, events on the launching stream)
-        kern = time_kernels(loop, stream, min(args.steps, 20)) if rank == 0 else {}
+        # (every rank runs them when sharded: the iteration holds the two all-reduces)
+        kern = time_kernels(loop, stream, min(args.steps, 20)) if (rank == 0 or world > 1) else {}
         # ---- e2e: the public class API with HOST buffers, copies inside the timed region
         e2e = run_e2e_loop(args, loop, prev_x, prev_y, prev_h, stream, barrier)
         e2e_api = run_e2e(args, gp, path, net, prev_x, prev_y, prev_h, budget, dev, stream, barrier)
@@ -286,7 +287,7 @@ def run_b200(args, rank, world, local_rank):
                                "MEASURED_PEAKS.json has no FP64 entry",
                 "per_kernel_ms": {k: round(v["ms"], 4) for k, v in kern.items()}}
     cpu = None
-    if not args.no_cpu_baseline:
+    if not args.no_cpu_baseline and world == 1:            # reported on rank 0 at N = 1 only
         cores = os.cpu_count() or 1
         r = cpu_oracle_rate(N, Lk, 12.0, cores)
         cpu = {"value": r["value"], "unit": UNIT, "cores": cores, "kind": "port", "sample": r["sample"]}

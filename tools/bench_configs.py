@@ -1,0 +1,247 @@
+#!/usr/bin/env python
+"""Secondary measurements for BASELINE.json configs[2], [3] and [4] (SURVEY 8d cfg 3-5); bench.py stays the
+headline (configs[1]).  One JSON line per case on stdout.
+
+    python tools/bench_configs.py mc     [--restarts 256] [--steps 10]   # cfg 3: Hartmann-6D HES-MC tree
+    python tools/bench_configs.py tf32                                     # cfg 4: Cosine8 FP64 vs FP32 variant
+    python tools/bench_configs.py sweep  [--max-restarts 8192]            # cfg 5: restarts x lookahead sweep
+
+Every case runs this repo's CUDA path only (no oracle, no CPU fallback); timing = CUDA events on the launching
+stream after warm-up.  Multi-GPU: launch under torchrun, every rank runs ``restarts / world`` restarts.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import math
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import torch
+
+F64 = torch.float64
+PEAKS = os.path.join(ROOT, "profiles", "pipe_peaks_r01.json")
+
+
+def fp64_peak():
+    try:
+        return float(json.load(open(PEAKS))["f64_fma_flops"])
+    except Exception:
+        return None
+
+
+def timed(fn, steps, warmup=3):
+    stream = torch.cuda.current_stream()
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(steps):
+        fn()
+    e1.record(stream)
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / steps
+
+
+def make_gp(env, dev, **hyp):
+    from nonmyopia_b200.gp import SurrogateGP
+    from nonmyopia_b200.synthetic import make_problem
+    prob = make_problem(env, seed=2, **hyp)
+    ls = torch.full((prob.d,), prob.lengthscale, dtype=F64)
+    gp = SurrogateGP(prob.train_X.to(dev), prob.train_Y.to(dev), kernel=prob.kernel, lengthscale=ls.to(dev),
+                     outputscale=prob.outputscale, noise=prob.noise, mean_const=prob.mean_const)
+    return prob, gp
+
+
+def cost_hypers(radius):
+    return dict(radius=radius, k=1.0, max_noise=1e-5, p_norm=2.0, discount=0.0, discount_threshold=-1.0)
+
+
+# ----------------------------------------------------------------------------- cfg 3: HES-MC tree
+def run_mc(args, rank, world):
+    """Hartmann-6D, n = 500, nf = [64, 4, 2] (reference actor.py:98-99), S_a = 64 leaf samples: one step = the
+    free-parameter Adam iteration of Actor.query (acqf.forward over the fantasy tree, autograd backward to every
+    design, fused AdamW)."""
+    from nonmyopia_b200 import acqfs, sharding as sh
+    from nonmyopia_b200.actor import _FlatAdamW, _logit, generate_random_points_batch
+    dev = torch.device("cuda", torch.cuda.current_device())
+    prob, gp = make_gp("Hartmann", dev, lengthscale=0.5)
+    d, n = prob.d, prob.train_X.shape[0]
+    nf = [int(v) for v in args.widths.split(",")]
+    L = len(nf)
+    lo, hi = sh.restart_range(args.restarts, rank, world)
+    n_r = hi - lo
+    torch.manual_seed(2)
+    acqf = acqfs.qMultiStepHEntropySearch(
+        model=gp, loss_function_class=acqfs.qLossFunctionTopK, loss_func_hypers=dict(dist_weight=1, dist_threshold=0.5),
+        cost_function_class=acqfs.qCostFunction, cost_func_hypers=cost_hypers(prob.radius), lookahead_steps=L,
+        n_actions=1, n_fantasy_at_design_pts=nf, n_fantasy_at_action_pts=64, enable_ts=False)
+    acqf.dump_model()
+    prev_X = prob.train_X[-1:].expand(n_r, -1).contiguous().to(dev)
+    prev_y = prob.train_Y[-1:].expand(n_r, -1).contiguous().to(dev)
+    prev_h = torch.zeros(n_r, 4, dtype=F64, device=dev)
+    levels, parent = [], prob.train_X[-1:].expand(n_r, -1)
+    for s in range(L + 1):
+        parent = generate_random_points_batch(parent, prob.radius, 1 if s == 0 else nf[s - 1])
+        parent = parent.reshape(-1, d) if s == 0 else parent
+        levels.append(parent.reshape(-1, d))
+    params = [_logit(torch.clamp(x.to(dev), 0.01, 0.99)).requires_grad_(True) for x in levels]
+    opt = _FlatAdamW(params, lr=1e-2)
+    budget = 2 * math.sqrt(d)
+
+    def step():
+        rd = acqf.forward(prev_X=prev_X, prev_y=prev_y, prev_hid_state=prev_h, maps=[torch.sigmoid(p) for p in params],
+                          prev_cost=0.0, enable_noise=False)
+        loss = rd["acqf_loss"] + abs(budget - rd["acqf_cost"])
+        opt.step(torch.autograd.grad(loss.sum() / args.restarts, params, allow_unused=True))
+
+    ms = timed(step, args.steps)
+    if world > 1:
+        import torch.distributed as dist
+        t = torch.tensor([ms], device=dev, dtype=F64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t)
+    per_restart = sum(math.prod(nf[:s]) for s in range(L + 1))
+    nodes = args.restarts * per_restart
+    # F_MC(d, n, s) ~ 2 n^2 + 2 n_s (3d + 12) + 8 n s per node at depth s
+    flops = args.restarts * sum(math.prod(nf[:s]) * (2 * n * n + 2 * (n + s) * (3 * d + 12) + 8 * n * s)
+                                for s in range(L + 1))
+    peak = fp64_peak()
+    out = dict(case="cfg3_hartmann_hes_mc", metric="hes_lookahead_node_posterior_evals_per_s_fwd_bwd",
+               value=nodes / (ms * 1e-3), unit="node evals/s", n_gpus=world, ms_per_step=ms, steps=args.steps,
+               dtype="f64", config=dict(workload=f"Hartmann-6D HES-MC tree nf={nf}, n={n} GP points, {args.restarts} restarts "
+                                        f"({n_r} per rank), S_a=64, FP64 (BASELINE configs[2])",
+                                        nodes_per_step=nodes, flops_per_step=flops),
+               roofline=dict(bound="fp64", achieved=flops / (ms * 1e-3) / 1e12, peak=peak and peak / 1e12, unit="TFLOP/s",
+                             frac=peak and flops / (ms * 1e-3) / peak))
+    if rank == 0:
+        print(json.dumps(out), flush=True)
+
+
+# ----------------------------------------------------------------------------- cfg 4: FP64 vs FP32 variant
+def run_tf32(args, rank, world):
+    """Cosine8 8-D, n = 200, HES-TS-AM: identical inputs and in-kernel draws through the FP64 and the FP32 kernels;
+    reports the relative deviations (north_star: 1e-3) and whether the arg-min restart agrees, plus both rates."""
+    from nonmyopia_b200 import ts_engine as te
+    from nonmyopia_b200.amortized_network import AmortizedNetwork
+    from nonmyopia_b200.gp import draw_thompson_path
+    from nonmyopia_b200.path import ThompsonPath
+    from nonmyopia_b200.ts_loop import TSAMLoop
+    dev = torch.device("cuda", torch.cuda.current_device())
+    prob, gp = make_gp("Cosine8", dev)
+    d, H = prob.d, 64
+    for L in (3, 20):
+        N = args.restarts
+        torch.manual_seed(2)
+        path64 = draw_thompson_path(gp, 1)
+        net = AmortizedNetwork(d + 1, d, H, 1, torch.tensor([[0.0, 1.0]] * d, dtype=F64)).double()
+        theta = net.flat_parameters().detach()
+        g = torch.Generator().manual_seed(7)
+        prev_h = torch.randn(N, H, generator=g).to(F64)
+        prev_x = prob.train_X[-1:].expand(N, -1).contiguous()
+        prev_y = prob.train_Y[-1:].expand(N, -1).contiguous()
+        res = {}
+        for dt in (torch.float64, torch.float32):
+            path = path64 if dt == F64 else ThompsonPath(
+                path64.W.to(dt), path64.w.to(dt), path64.v.to(dt), path64.train_X.to(dt), path64.lengthscale.to(dt),
+                kernel=path64.kernel, outputscale=path64.outputscale, mean_const=path64.mean_const)
+            eng = te.TSRollout(path, d, H, L, N, cost_hypers(prob.radius), dtype=dt, device=dev, seed=99)
+            loop = TSAMLoop(eng, theta, prev_x, prev_y, prev_h, budget=2 * math.sqrt(d), lr=1e-3, past_initial=False,
+                            max_iter=10**9, patience=-1)
+            loop.run(1, use_graph=False)
+            first = dict(loss=loop.main.loss.double().clone(), cost=loop.main.cost.double().clone(),
+                         A=loop.main.A.double().clone(), Y=loop.main.Y.double().clone())
+            loop.capture()
+            ms = timed(loop.graph.replay, args.steps * 5)
+            res[dt] = dict(first=first, ms=ms)
+        a, b = res[torch.float64]["first"], res[torch.float32]["first"]
+        rel = lambda k: float(((a[k] - b[k]).abs() / a[k].abs().clamp_min(1.0)).max())
+        tot64, tot32 = a["loss"] + (2 * math.sqrt(d) - a["cost"]).abs(), b["loss"] + (2 * math.sqrt(d) - b["cost"]).abs()
+        srt = torch.sort(tot64).values
+        out = dict(case=f"cfg4_cosine8_fp64_vs_fp32_L{L}", restarts=N, lookahead=L, n_train=prob.train_X.shape[0],
+                   rel_dev=dict(acqf_loss=rel("loss"), acqf_cost=rel("cost"), actions=rel("A"), path_values=rel("Y")),
+                   tolerance=1e-3, argmin_fp64=int(tot64.argmin()), argmin_fp32=int(tot32.argmin()),
+                   argmin_margin_fp64=float(srt[1] - srt[0]),
+                   ms_per_step=dict(f64=res[torch.float64]["ms"], f32=res[torch.float32]["ms"]),
+                   node_evals_per_s=dict(f64=N * (L + 1) / res[torch.float64]["ms"] * 1e3,
+                                         f32=N * (L + 1) / res[torch.float32]["ms"] * 1e3))
+        if rank == 0:
+            print(json.dumps(out), flush=True)
+
+
+# ----------------------------------------------------------------------------- cfg 5: sweep
+def run_sweep(args, rank, world):
+    """Alpine (n = 100) and SynGP (n = 25), HES-TS-AM, restarts 64 ... max x lookahead 1-4: graph-replayed
+    Adam iterations per case."""
+    from nonmyopia_b200 import ts_engine as te
+    from nonmyopia_b200.amortized_network import AmortizedNetwork
+    from nonmyopia_b200.gp import draw_thompson_path
+    from nonmyopia_b200.ts_loop import TSAMLoop
+    dev = torch.device("cuda", torch.cuda.current_device())
+    group = None
+    if world > 1:
+        import torch.distributed as dist
+        group = dist.group.WORLD
+    peak = fp64_peak()
+    for env in ("Alpine", "SynGP"):
+        prob, gp = make_gp(env, dev)
+        d, H, n = prob.d, 64, prob.train_X.shape[0]
+        torch.manual_seed(2)
+        path = draw_thompson_path(gp, 1)
+        net = AmortizedNetwork(d + 1, d, H, 1, torch.tensor([[0.0, 1.0]] * d, dtype=F64)).double()
+        theta = net.flat_parameters().detach()
+        n_r = 64
+        while n_r <= args.max_restarts:
+            for L in (1, 2, 3, 4):
+                N = n_r                                            # per rank (weak scaling)
+                g = torch.Generator().manual_seed(7 + rank)
+                prev_h = torch.randn(N, H, generator=g).to(F64)
+                prev_x = prob.train_X[-1:].expand(N, -1).contiguous()
+                prev_y = prob.train_Y[-1:].expand(N, -1).contiguous()
+                eng = te.TSRollout(path, d, H, L, N, cost_hypers(prob.radius), device=dev, seed=99 + rank)
+                loop = TSAMLoop(eng, theta, prev_x, prev_y, prev_h, budget=2 * math.sqrt(d), lr=1e-3,
+                                past_initial=False, n_global=N * world, max_iter=10**9, patience=-1, group=group)
+                loop.capture()
+                ms = timed(loop.graph.replay, args.steps * 5, warmup=5)
+                if world > 1:
+                    t = torch.tensor([ms], device=dev, dtype=F64)
+                    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                    ms = float(t)
+                nodes = N * world * (L + 1)
+                f_node = 2 * 1024 * d + 6 * 1024 + 2 * n * (3 * d + 12) + 3 * 2 * (10 * H * H + (2 * d + 1) * H)
+                out = dict(case="cfg5_sweep", env=env, n_train=n, restarts_per_gpu=N, n_gpus=world, lookahead=L,
+                           ms_per_step=ms, node_evals_per_s=nodes / ms * 1e3,
+                           fp64_frac=peak and nodes * f_node / (ms * 1e-3) / peak)
+                if rank == 0:
+                    print(json.dumps(out), flush=True)
+                del loop, eng
+            n_r *= 4 if n_r < 4096 else 2
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("case", choices=["mc", "tf32", "sweep"])
+    ap.add_argument("--restarts", type=int, default=None)
+    ap.add_argument("--widths", default="64,4,2")
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--max-restarts", type=int, default=8192)
+    args = ap.parse_args()
+    if args.restarts is None:
+        args.restarts = 256 if args.case == "mc" else 64
+    rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+    torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", 0)))
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", torch.cuda.current_device()))
+    {"mc": run_mc, "tf32": run_tf32, "sweep": run_sweep}[args.case](args, rank, world)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
