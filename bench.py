@@ -268,8 +268,7 @@ def run_b200(args, rank, world, local_rank):
     st = loop.read_state()
     assert st.step >= args.steps and not st.done, "timed steps did not run"
     if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
+        _finish(world)
         return
     value = nodes_per_step * world * args.steps / (ms_total * 1e-3)
     f_ts, f_net = algorithmic_flops_per_node(D, H, gp.n, path.W.shape[0])
@@ -317,8 +316,21 @@ def run_b200(args, rank, world, local_rank):
         "gpu_launches": loop.n_launches_per_iter * args.steps, "clocks": clk,
     }
     print(json.dumps(line), flush=True)
+    _finish(world)
+
+
+def _finish(world):
+    """End of a rank.  Sharded runs leave without tearing NCCL down: the communicator is referenced by the
+    captured per-iteration graph, and its teardown at interpreter exit was seen to hang after the result line
+    had been printed; the work is done and synchronised at this point."""
     if world > 1:
-        dist.destroy_process_group()
+        import torch.distributed as dist
+        torch.cuda.synchronize()
+        dist.barrier()
+        torch.cuda.synchronize()
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(0)
 
 
 def time_kernels(loop, stream, n_steps):

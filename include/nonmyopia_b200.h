@@ -264,11 +264,13 @@ int nmb_adamw_flat(int dtype, int64_t n, const nmb_adamw_t* hp, void* param, voi
 typedef struct nmb_gp {
     int32_t d, n, kernel_id;
     int32_t ldu;            /* row stride of U / gU (>= n, multiple of 4) */
+    int32_t ldl;            /* leading dimension of linv / linv_t: n rounded up to a multiple of 8 */
+    int32_t _pad;
     double amplitude, noise, mean_const;
     const void* train_x;    /* [n][d] */
     const void* inv_ls;     /* [d] */
-    const void* linv;       /* [n][n] inverse Cholesky root, row-major, lower triangular */
-    const void* linv_t;     /* [n][n] its transpose */
+    const void* linv;       /* [ldl][ldl] inverse Cholesky root, row-major, lower triangular, zero padded */
+    const void* linv_t;     /* [ldl][ldl] its transpose, zero padded */
     const void* alpha;      /* [n] (K + s2 I)^-1 (y - c) */
 } nmb_gp_t;
 

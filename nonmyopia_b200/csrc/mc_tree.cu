@@ -17,24 +17,28 @@
 //                slots are complete when its own level runs).
 //   gather_gu  : one warp per node: gU = 2 g_q u + sum_t g_dot_t u(z_t) + sum_desc g_dot u(desc),
 //                descendants visited in a fixed order.
-#include "policy_dev.cuh"
+#include "policy_mma.cuh"
 
 namespace nmb {
 
 template <typename T> struct GpDev {
-    int d, n, kernel_id, ldu;
+    int d, n, kernel_id, ldu, ldl;
     T amp, noise, mean_const;
     const T *train_x, *inv_ls, *linv, *linv_t, *alpha;
 };
 
 template <typename T> static GpDev<T> to_dev(const nmb_gp_t& g) {
     GpDev<T> o;
-    o.d = g.d; o.n = g.n; o.kernel_id = g.kernel_id; o.ldu = g.ldu;
+    o.d = g.d; o.n = g.n; o.kernel_id = g.kernel_id; o.ldu = g.ldu; o.ldl = g.ldl;
     o.amp = (T)g.amplitude; o.noise = (T)g.noise; o.mean_const = (T)g.mean_const;
     o.train_x = (const T*)g.train_x; o.inv_ls = (const T*)g.inv_ls; o.linv = (const T*)g.linv;
     o.linv_t = (const T*)g.linv_t; o.alpha = (const T*)g.alpha;
     return o;
 }
+
+}  // namespace nmb
+#include "whiten_mma.cuh"
+namespace nmb {
 
 extern __shared__ __align__(16) unsigned char mc_smem_raw[];
 
@@ -97,7 +101,7 @@ __global__ void __launch_bounds__(kNT, 1) whiten_fwd_kernel(GpDev<T> g, const T*
         T acc[2][4];
         zero_acc(acc);
         const int nc = min(kOB, n - cb);
-        gemm_block<T>(Kt, min(n, cb + kOB), g.linv_t, n, cb, nc, stage, tc, acc);
+        gemm_block<T>(Kt, min(n, cb + kOB), g.linv_t, g.ldl, cb, nc, stage, tc, acc);
 #pragma unroll
         for (int i = 0; i < 2; ++i) {
             const int r = tc.r0 + i;
@@ -165,7 +169,7 @@ __global__ void __launch_bounds__(kNT, 1) whiten_bwd_kernel(GpDev<T> g, const T*
         zero_acc(acc);
         const int nc = min(kOB, n - cb);
         // g_K[r][j] = sum_{i >= j} gU[r][i] Linv[i][j]: rows i >= cb of Linv, columns cb..cb+63
-        gemm_block<T>(Gt + (size_t)cb * kRS, n - cb, g.linv + (size_t)cb * n, n, cb, nc, stage, tc, acc);
+        gemm_block<T>(Gt + (size_t)cb * kRS, n - cb, g.linv + (size_t)cb * g.ldl, g.ldl, cb, nc, stage, tc, acc);
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
             const int c = cb + tc.c0 + j;
@@ -509,6 +513,8 @@ static int validate_gp(const nmb_gp_t* gp, int dtype, const char* who) {
     NMB_REQUIRE(gp->d >= 1 && gp->d <= NMB_MAX_DIM, NMB_ELIMIT, "%s: d=%d outside [1,%d]", who, gp->d, NMB_MAX_DIM);
     NMB_REQUIRE(gp->n >= 1 && gp->ldu >= gp->n, NMB_EINVAL, "%s: n=%d ldu=%d", who, gp->n, gp->ldu);
     NMB_REQUIRE(gp->kernel_id >= 0 && gp->kernel_id <= 3, NMB_EINVAL, "%s: kernel_id %d", who, gp->kernel_id);
+    NMB_REQUIRE(gp->ldl >= gp->n && gp->ldl % 8 == 0, NMB_EINVAL, "%s: ldl=%d must be a multiple of 8 and >= n=%d", who,
+                gp->ldl, gp->n);
     NMB_REQUIRE(gp->train_x && gp->inv_ls && gp->linv && gp->linv_t && gp->alpha, NMB_EINVAL, "%s: null gp array", who);
     return 0;
 }
@@ -520,6 +526,43 @@ static int validate_gp(const nmb_gp_t* gp, int dtype, const char* who) {
         else if ((d) <= 8) { CALL(8); }   \
         else { CALL(16); }                \
     } while (0)
+
+// FP64: tensor-pipe kernels (whiten_mma.cuh); rows per CTA / ring depth chosen so the tile fits shared memory
+template <int DM>
+static int launch_whiten_mma_d(const nmb_gp_t* gp, bool bwd, const double* pts, int64_t n_pts, double* U, double* m0,
+                               double* q, const double* gU, const double* g_m0, double* g_pts, cudaStream_t st) {
+    GpDev<double> g = to_dev<double>(*gp);
+    static const int cand[5][2] = {{32, 4}, {32, 3}, {24, 4}, {24, 3}, {16, 3}};
+    int R = 0, nst = 0;
+    size_t smem = 0;
+    for (int i = 0; i < 5 && !R; ++i) {
+        smem = wh_mma_bytes<DM>(gp->ldl, cand[i][0], cand[i][1]);
+        if (smem <= 227 * 1024) { R = cand[i][0]; nst = cand[i][1]; }
+    }
+    NMB_REQUIRE(R > 0, NMB_ELIMIT, "gp whiten: n=%d training points exceed shared memory", gp->n);
+    const unsigned grid = (unsigned)((n_pts + R - 1) / R), nthr = (unsigned)((R / 8) * 2 + 1) * 32;
+#define NMB_WHM(NST)                                                                                                  \
+    if (!bwd) {                                                                                                       \
+        NMB_CUDA(cudaFuncSetAttribute(whiten_fwd_mma_kernel<DM, NST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+        whiten_fwd_mma_kernel<DM, NST><<<grid, nthr, smem, st>>>(g, gp->ldl, R, pts, n_pts, U, m0, q);                 \
+    } else {                                                                                                          \
+        NMB_CUDA(cudaFuncSetAttribute(whiten_bwd_mma_kernel<DM, NST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+        whiten_bwd_mma_kernel<DM, NST><<<grid, nthr, smem, st>>>(g, gp->ldl, R, pts, n_pts, gU, g_m0, g_pts);          \
+    }
+    if (nst == 4) { NMB_WHM(4) } else { NMB_WHM(3) }
+#undef NMB_WHM
+    NMB_LAUNCH_CHECK();
+    return 0;
+}
+
+static int launch_whiten_mma(const nmb_gp_t* gp, bool bwd, const void* pts, int64_t n_pts, void* U, void* m0, void* q,
+                             const void* gU, const void* g_m0, void* g_pts, cudaStream_t st) {
+#define NMB_WD(DM) return launch_whiten_mma_d<DM>(gp, bwd, (const double*)pts, n_pts, (double*)U, (double*)m0, (double*)q, \
+                                                  (const double*)gU, (const double*)g_m0, (double*)g_pts, st)
+    NMB_MC_D(gp->d, NMB_WD);
+#undef NMB_WD
+    return 0;
+}
 
 template <typename T>
 static int launch_whiten(const nmb_gp_t* gp, bool bwd, const void* pts, int64_t n_pts, void* U, void* m0, void* q,
@@ -551,7 +594,7 @@ extern "C" int nmb_gp_whiten_fwd(const nmb_gp_t* gp, int dtype, const void* pts,
     NMB_REQUIRE(pts && U && m0 && q && n_pts >= 0, NMB_EINVAL, "nmb_gp_whiten_fwd: null argument");
     if (n_pts == 0) return 0;
     cudaStream_t st = (cudaStream_t)stream;
-    return dtype == NMB_F64 ? launch_whiten<double>(gp, false, pts, n_pts, U, m0, q, nullptr, nullptr, nullptr, st)
+    return dtype == NMB_F64 ? launch_whiten_mma(gp, false, pts, n_pts, U, m0, q, nullptr, nullptr, nullptr, st)
                             : launch_whiten<float>(gp, false, pts, n_pts, U, m0, q, nullptr, nullptr, nullptr, st);
 }
 
@@ -562,7 +605,7 @@ extern "C" int nmb_gp_whiten_bwd(const nmb_gp_t* gp, int dtype, const void* pts,
     NMB_REQUIRE(pts && gU && g_m0 && g_pts && n_pts >= 0, NMB_EINVAL, "nmb_gp_whiten_bwd: null argument");
     if (n_pts == 0) return 0;
     cudaStream_t st = (cudaStream_t)stream;
-    return dtype == NMB_F64 ? launch_whiten<double>(gp, true, pts, n_pts, nullptr, nullptr, nullptr, gU, g_m0, g_pts, st)
+    return dtype == NMB_F64 ? launch_whiten_mma(gp, true, pts, n_pts, nullptr, nullptr, nullptr, gU, g_m0, g_pts, st)
                             : launch_whiten<float>(gp, true, pts, n_pts, nullptr, nullptr, nullptr, gU, g_m0, g_pts, st);
 }
 

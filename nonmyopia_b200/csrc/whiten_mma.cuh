@@ -1,0 +1,252 @@
+// Shared-root whitening on the FP64 tensor pipe (DMMA m8n8k4), FP64 only.
+//
+//   forward : U[p][:]  = k(x_p, X_tr) L^-T        (A = kernel rows generated in shared memory, row-major;
+//                                                   B = L^-T streamed from L2, only rows k <= column block end)
+//   backward: g_K[p][:] = gU[p][:] L^-1            (A = the gU tile; B = L^-1, only rows i >= column block start),
+//             fused with g_x = sum_j (g_K[j] + g_m0 alpha_j) d k(x, X_j) / dx  in the accumulator epilogue.
+//
+// Same machinery as the policy GEMMs (policy_mma.cuh): a producer warp streams [32 k-rows][64 cols] chunks of the
+// triangular operand with cp.async.bulk into an mbarrier ring (row stride 72 doubles: conflict-free B fragments),
+// consumer warps own 8-row x 32-col accumulator tiles, A fragments come from a row-major tile with stride
+// KS = 4 mod 16 doubles (conflict free).  Replaces the DFMA 2x4 register-tile product (18 % of the FP64 peak at
+// n = 500: bound by the shared-memory data pipe, see the header of policy_mma.cuh).
+// The triangular operands are passed zero-padded, [ldl][ldl] with ldl = n rounded up to 8, so that every bulk copy
+// is 16-byte aligned and k extents are multiples of 4.
+// Reference: GPyTorch's exact prediction strategy behind model.posterior (acqfs.py:366, 414).
+#pragma once
+#include "policy_mma.cuh"
+
+namespace nmb {
+
+__host__ __device__ inline int wh_ks(int ldl) { return (ldl + 15) / 16 * 16 + 4; }
+
+template <int DMAX>
+inline size_t wh_mma_bytes(int ldl, int R, int nst) {
+    return ((size_t)nst * kStageElems + (size_t)R * wh_ks(ldl) + (size_t)R * DMAX + (size_t)2 * R * DMAX + 2 * nst) * 8;
+}
+
+struct WhSmem {
+    double *stage, *A, *xs, *red;
+    unsigned full0, empty0;
+    int KS;
+    template <int DMAX>
+    __device__ void carve(double* base, int ldl, int R, int nst) {
+        KS = wh_ks(ldl);
+        double* p = base;
+        stage = p; p += (size_t)nst * kStageElems;
+        A = p; p += (size_t)R * KS;
+        xs = p; p += R * DMAX;
+        red = p; p += 2 * R * DMAX;
+        full0 = smem_u32(p);
+        empty0 = full0 + 8 * nst;
+    }
+};
+
+// Producer warp: chunks of the triangular operand B [ldl][ldl] in consumption order.
+// forward (LOWER_ROWS = false): column block cb needs rows [0, cb + 64); backward: rows [cb, ldl).
+template <int NST, bool LOWER_ROWS>
+__device__ __forceinline__ void wh_producer(const double* __restrict__ B, int n, int ldl, const MmaRing& rg) {
+    const int lane = threadIdx.x & 31;
+    unsigned c = 0;
+    for (int cb = 0; cb < n; cb += kOB) {
+        const unsigned row_bytes = (unsigned)min(kOB, ldl - cb) * 8u;
+        const int k_lo = LOWER_ROWS ? cb : 0, k_hi = LOWER_ROWS ? ldl : min(cb + kOB, ldl);
+        for (int k0 = k_lo; k0 < k_hi; k0 += kKC, ++c) {
+            const unsigned slot = c % NST, fill = c / NST;
+            if (fill > 0) mbar_wait(rg.empty0 + 8 * slot, (fill - 1) & 1);
+            const int kn = min(kKC, k_hi - k0);
+            const unsigned full = rg.full0 + 8 * slot;
+            if (lane == 0) mbar_arrive_expect_tx(full, row_bytes * (unsigned)kn);
+            __syncwarp();
+            if (lane < kn)
+                bulk_g2s(smem_u32(rg.stage + (size_t)slot * kStageElems + lane * kSW), B + (size_t)(k0 + lane) * ldl + cb,
+                         row_bytes, full);
+        }
+    }
+}
+
+__device__ __forceinline__ void wh_init_barriers(const WhSmem& sm, int nst, int n_consumer_warps) {
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < nst; ++s) {
+            mbar_init(sm.full0 + 8 * s, 1);
+            mbar_init(sm.empty0 + 8 * s, n_consumer_warps);
+        }
+        fence_barrier_init();
+    }
+    __syncthreads();
+}
+
+// ------------------------------------------------------------------ forward
+template <int DMAX, int NST>
+__global__ void __launch_bounds__(288, 1) whiten_fwd_mma_kernel(GpDev<double> g, int ldl, int R,
+                                                                const double* __restrict__ pts, long long n_pts,
+                                                                double* __restrict__ U, double* __restrict__ m0,
+                                                                double* __restrict__ q) {
+    extern __shared__ __align__(16) unsigned char wh_smem_raw[];
+    const int n = g.n, d = g.d, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int ncw = (R >> 3) * 2, nthr = ncw * 32;
+    WhSmem sm;
+    sm.carve<DMAX>(reinterpret_cast<double*>(wh_smem_raw), ldl, R, NST);
+    wh_init_barriers(sm, NST, ncw);
+    const MmaRing ring{sm.stage, sm.full0, sm.empty0, sm.KS};
+    if (warp == ncw) {
+        wh_producer<NST, false>(g.linv_t, n, ldl, ring);
+        return;
+    }
+    const int KS = sm.KS;
+    const long long p0 = (long long)blockIdx.x * R;
+    const int nvalid = (int)min((long long)R, n_pts - p0);
+    for (int e = tid; e < R * DMAX; e += nthr) {
+        const int r = e / DMAX, k = e - r * DMAX;
+        sm.xs[e] = (r < nvalid && k < d) ? pts[(p0 + r) * d + k] * __ldg(g.inv_ls + k) : 0.0;
+    }
+    consumer_sync(nthr);
+    // ---- kernel rows: lane = training point (its scaled coordinates loaded once, reused for the warp's 4 query
+    //      rows = 4 independent sqrt/exp chains), conflict-free row-major stores
+    {
+        double ils[DMAX], macc[4] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll
+        for (int k = 0; k < DMAX; ++k) ils[k] = k < d ? __ldg(g.inv_ls + k) : 0.0;
+        for (int j = lane; j < KS; j += 32) {
+            double tj[DMAX], al = 0.0;
+            const bool live = j < n;
+#pragma unroll
+            for (int k = 0; k < DMAX; ++k) tj[k] = (live && k < d) ? __ldg(g.train_x + (size_t)j * d + k) * ils[k] : 0.0;
+            if (live) al = __ldg(g.alpha + j);
+#pragma unroll
+            for (int rr = 0; rr < 4; ++rr) {
+                const int r = warp + rr * ncw;
+                double r2 = 0.0;
+#pragma unroll
+                for (int k = 0; k < DMAX; ++k) {
+                    const double df = sm.xs[r * DMAX + k] - tj[k];
+                    r2 = fma(df, df, r2);
+                }
+                double kap, gc;
+                kernel_profile<double>(g.kernel_id, r2, kap, gc);
+                const double kv = (live && r < nvalid) ? g.amp * kap : 0.0;
+                macc[rr] = fma(kv, al, macc[rr]);
+                sm.A[(size_t)r * KS + j] = kv;
+            }
+        }
+#pragma unroll
+        for (int rr = 0; rr < 4; ++rr) {
+            const int r = warp + rr * ncw;
+            const double s = warp_sum(macc[rr]);
+            if (lane == 0 && r < nvalid) m0[p0 + r] = s;
+        }
+    }
+    consumer_sync(nthr);
+    // ---- U tile = K L^-T, 64 output columns at a time; only k < cb + 64 contributes
+    MmaWarp w;
+    w.init(warp, nthr, n);
+    const int row = w.row0 + w.fr;
+    double qacc = 0.0;
+    for (int cb = 0; cb < n; cb += kOB) {
+        double acc[4][2];
+        zero_acc4(acc);
+        w.active = cb + w.col0 < n;
+        mma_gemm<NST>(ring, w, sm.A, min(cb + kOB, ldl), acc);
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+            const int c = cb + w.col0 + 8 * t + 2 * w.fk;
+            if (c < n) {
+                const bool two = c + 1 < n;
+                qacc = fma(acc[t][0], acc[t][0], qacc);
+                if (two) qacc = fma(acc[t][1], acc[t][1], qacc);
+                if (row < nvalid) {
+                    double* up = U + (size_t)(p0 + row) * g.ldu + c;
+                    if (two) *reinterpret_cast<double2*>(up) = make_double2(acc[t][0], acc[t][1]);
+                    else *up = acc[t][0];
+                }
+            }
+        }
+    }
+    qacc += shfl_xor_(qacc, 1);
+    qacc += shfl_xor_(qacc, 2);
+    if (w.fk == 0) sm.red[(warp & 1) * R + row] = qacc;
+    consumer_sync(nthr);
+    if (tid < nvalid) q[p0 + tid] = sm.red[tid] + sm.red[R + tid];
+}
+
+// ------------------------------------------------------------------ backward
+template <int DMAX, int NST>
+__global__ void __launch_bounds__(288, 1) whiten_bwd_mma_kernel(GpDev<double> g, int ldl, int R,
+                                                                const double* __restrict__ pts, long long n_pts,
+                                                                const double* __restrict__ gU,
+                                                                const double* __restrict__ g_m0,
+                                                                double* __restrict__ g_pts) {
+    extern __shared__ __align__(16) unsigned char wh_smem_raw[];
+    const int n = g.n, d = g.d, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int ncw = (R >> 3) * 2, nthr = ncw * 32;
+    WhSmem sm;
+    sm.carve<DMAX>(reinterpret_cast<double*>(wh_smem_raw), ldl, R, NST);
+    wh_init_barriers(sm, NST, ncw);
+    const MmaRing ring{sm.stage, sm.full0, sm.empty0, sm.KS};
+    if (warp == ncw) {
+        wh_producer<NST, true>(g.linv, n, ldl, ring);
+        return;
+    }
+    const int KS = sm.KS;
+    const long long p0 = (long long)blockIdx.x * R;
+    const int nvalid = (int)min((long long)R, n_pts - p0);
+    for (int e = tid; e < R * DMAX; e += nthr) {
+        const int r = e / DMAX, k = e - r * DMAX;
+        sm.xs[e] = (r < nvalid && k < d) ? pts[(p0 + r) * d + k] * __ldg(g.inv_ls + k) : 0.0;
+    }
+    // gU tile: rows are contiguous in HBM and in the row-major A tile
+    for (int r = warp; r < R; r += ncw) {
+        const double* src = gU + (size_t)(p0 + r) * g.ldu;
+        for (int i = lane; i < KS; i += 32) sm.A[(size_t)r * KS + i] = (r < nvalid && i < n) ? src[i] : 0.0;
+    }
+    consumer_sync(nthr);
+    MmaWarp w;
+    w.init(warp, nthr, n);
+    const int row = w.row0 + w.fr;
+    const double gm = row < nvalid ? g_m0[p0 + row] : 0.0;
+    double xr[DMAX], gx[DMAX];
+#pragma unroll
+    for (int k = 0; k < DMAX; ++k) { xr[k] = sm.xs[row * DMAX + k]; gx[k] = 0.0; }
+    for (int cb = 0; cb < n; cb += kOB) {
+        double acc[4][2];
+        zero_acc4(acc);
+        w.active = cb + w.col0 < n;
+        // g_K[r][j] = sum_{i >= j} gU[r][i] Linv[i][j]: rows i >= cb of Linv, columns cb..cb+63
+        mma_gemm<NST>(ring, w, sm.A + cb, ldl - cb, acc);
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                const int c = cb + w.col0 + 8 * t + 2 * w.fk + e;
+                if (c < n) {
+                    const double al = __ldg(g.alpha + c);
+                    double sd[DMAX], r2 = 0.0;
+#pragma unroll
+                    for (int k = 0; k < DMAX; ++k) {
+                        sd[k] = k < d ? xr[k] - __ldg(g.train_x + (size_t)c * d + k) * __ldg(g.inv_ls + k) : 0.0;
+                        r2 = fma(sd[k], sd[k], r2);
+                    }
+                    double kap, gc;
+                    kernel_profile<double>(g.kernel_id, r2, kap, gc);
+                    const double coef = (acc[t][e] + gm * al) * g.amp * gc;
+#pragma unroll
+                    for (int k = 0; k < DMAX; ++k) gx[k] = fma(coef, sd[k], gx[k]);
+                }
+            }
+        }
+    }
+    // reduce over the 4 lanes of a fragment row and the 2 column warps that share the rows
+#pragma unroll
+    for (int k = 0; k < DMAX; ++k) { gx[k] += shfl_xor_(gx[k], 1); gx[k] += shfl_xor_(gx[k], 2); }
+    if (w.fk == 0) {
+#pragma unroll
+        for (int k = 0; k < DMAX; ++k) sm.red[((warp & 1) * R + row) * DMAX + k] = gx[k];
+    }
+    consumer_sync(nthr);
+    for (int e = tid; e < R * DMAX; e += nthr) {
+        const int r = e / DMAX, k = e - r * DMAX;
+        if (r < nvalid && k < d) g_pts[(p0 + r) * d + k] += (sm.red[e] + sm.red[R * DMAX + e]) * __ldg(g.inv_ls + k);
+    }
+}
+
+}  // namespace nmb

@@ -21,6 +21,7 @@ MAX_LEVELS = 16
 class GpStruct(C.Structure):
     """``nmb_gp_t``"""
     _fields_ = [("d", C.c_int32), ("n", C.c_int32), ("kernel_id", C.c_int32), ("ldu", C.c_int32),
+                ("ldl", C.c_int32), ("_pad", C.c_int32),
                 ("amplitude", C.c_double), ("noise", C.c_double), ("mean_const", C.c_double),
                 ("train_x", C.c_void_p), ("inv_ls", C.c_void_p), ("linv", C.c_void_p), ("linv_t", C.c_void_p),
                 ("alpha", C.c_void_p)]
@@ -42,11 +43,14 @@ class TreeState(C.Structure):
 def gp_struct(gp: SurrogateGP, dtype) -> tuple:
     """``nmb_gp_t`` + the tensors it points to (kept alive by the caller)."""
     n, d = gp.n, gp.d
+    ldl = (n + 7) // 8 * 8
+    # zero-padded [ldl][ldl] triangular operands: 16-byte aligned rows for the bulk copies of whiten_mma.cuh
+    linv = torch.zeros(ldl, ldl, dtype=dtype, device=gp.device)
+    linv[:n, :n] = gp.Linv.to(dtype)
     keep = dict(train_x=gp.train_X.to(dtype).contiguous(), inv_ls=(1.0 / gp.lengthscale).to(dtype).contiguous(),
-                linv=gp.Linv.to(dtype).contiguous(), linv_t=gp.Linv.T.to(dtype).contiguous(),
-                alpha=gp.alpha.to(dtype).contiguous())
+                linv=linv, linv_t=linv.T.contiguous(), alpha=gp.alpha.to(dtype).contiguous())
     ldu = (n + 3) // 4 * 4
-    st = GpStruct(d=d, n=n, kernel_id=_lib.KERNEL_IDS[gp.kernel], ldu=ldu, amplitude=gp.amplitude, noise=gp.noise,
+    st = GpStruct(d=d, n=n, kernel_id=_lib.KERNEL_IDS[gp.kernel], ldu=ldu, ldl=ldl, amplitude=gp.amplitude, noise=gp.noise,
                   mean_const=gp.mean_const, **{k: v.data_ptr() for k, v in keep.items()})
     return st, keep
 
