@@ -14,7 +14,9 @@ A node eval = one query point evaluated under the Thompson path, forward and bac
     python bench.py --impl reference [--gpus N] ...                  # CPU oracle on the host cores
 
 Multi-GPU (torchrun, one rank per GPU): every rank owns 64 restarts x 64 paths (weak scaling); the
-policy gradient is all-reduced (SUM) and the snapshot decision all-reduced (MIN) over NCCL.
+policy gradient is summed and the snapshot decision MIN-reduced over the ranks once per iteration - by this repo's
+own kernels over NVLink peer memory, fused with the AdamW update (--exchange peer, the default when the box maps
+peer memory), or by two NCCL all-reduces (--exchange nccl).
 """
 from __future__ import annotations
 
@@ -50,6 +52,8 @@ def parse_args():
     ap.add_argument("--restarts", type=int, default=N_RESTARTS)
     ap.add_argument("--paths", type=int, default=N_PATHS)
     ap.add_argument("--lookahead", type=int, default=L)
+    ap.add_argument("--exchange", default="auto", choices=["auto", "peer", "nccl"],
+                    help="N > 1: per-iteration gradient/decision exchange (own kernels over NVLink peer memory, or NCCL)")
     return ap.parse_args()
 
 
@@ -219,7 +223,7 @@ def run_b200(args, rank, world, local_rank):
     budget = 2 * math.sqrt(D)
     eng = te.TSRollout(path, D, H, Lk, N, cost_hypers(), device=dev, chains_per_path=n_r, seed=12345 + rank)
     loop = TSAMLoop(eng, theta0, prev_x, prev_y, prev_h, budget=budget, lr=1e-3, past_initial=False,
-                    n_global=N * world, max_iter=10**9, patience=-1, group=group)
+                    n_global=N * world, max_iter=10**9, patience=-1, group=group, exchange=args.exchange)
     stream = torch.cuda.Stream(device=dev)
     nodes_per_step = N * (Lk + 1)
 
@@ -298,6 +302,8 @@ def run_b200(args, rank, world, local_rank):
                                f"{Lk + 1} levels, n=50 GP points, M=1024 features, H=64, FP64 (BASELINE configs[1])",
                    "step": "one AdamW iteration of Actor.query: 2 rollouts fwd, objective, snapshot, rollout bwd, "
                            "weight gradients, AdamW", "launch_mode": mode,
+                   "exchange": {"none": "single GPU", "peer": "gradient SUM + decision MIN by own kernels over NVLink peer "
+                                "memory, fused with AdamW", "nccl": "two NCCL all-reduces per iteration"}[loop.exchange],
                    "l2": "no flush: the per-step working set (backward workspace "
                          f"{loop.main.save.numel() * 8 / 1e6:.0f} MB + partials) exceeds the 126 MB L2",
                    "nodes_per_step": nodes_per_step * world, "flops_per_node": {"thompson_path": f_ts, "policy_fwd": f_net,

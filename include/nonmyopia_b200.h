@@ -248,6 +248,37 @@ int nmb_adamw_flat(int dtype, int64_t n, const nmb_adamw_t* hp, void* param, voi
                    const void* grad, nmb_loop_state_t* state, int advance_state, void* stream);
 
 /* ------------------------------------------------------------------------
+ * Restart shards over NVLink peer memory (one process per GPU; SURVEY 8e C2 + C3): the per-iteration exchange of
+ * the sharded Actor.query loop - policy-gradient SUM and the MIN of the two snapshot-decision candidates
+ * (actor.py:622-639, 641-648) - written against peer-mapped buffers, fused with the AdamW update, instead of two
+ * NCCL all-reduces.  Every rank allocates nmb_peer_exchange_bytes(dtype, n) zero-initialised bytes in memory its
+ * peers can map (host side: torch.distributed._symmetric_memory), and passes all ranks' addresses of it.
+ * Call order per iteration, on every rank, same stream: nmb_peer_publish -> nmb_peer_wait_decide ->
+ * (nmb_snapshot_if_improved) -> nmb_peer_adamw_step.  CUDA-graph capturable; no-ops once state->done is set.
+ * ---------------------------------------------------------------------- */
+#define NMB_MAX_PEERS 16
+#define NMB_PEER_HEADER_BYTES 256
+#define NMB_PEER_TIMEOUT_STALL (-777)   /* state->stall after a peer failed to publish within ~2 s (loop stopped) */
+typedef struct nmb_peer_exchange {
+    int32_t rank, world;
+    int64_t n;                    /* gradient elements per rank (policy parameter count) */
+    void* base[NMB_MAX_PEERS];    /* base[r]: rank r's exchange buffer as mapped into THIS process */
+} nmb_peer_exchange_t;
+int64_t nmb_peer_exchange_bytes(int dtype, int64_t n);
+/* seg_splits_host == NULL: grad [n] is this rank's gradient; otherwise grad is the [splits][n] partials buffer of
+ * nmb_policy_wgrad and its seg_splits, reduced on the way out (d, H, n_actions give the parameter layout).
+ * Reads state->cand_total / cand_lck (nmb_ts_objective with defer_decision = 1). */
+int nmb_peer_publish(const nmb_peer_exchange_t* px, int dtype, const void* grad, int d, int H, int n_actions,
+                     const int32_t* seg_splits_host, const nmb_loop_state_t* state, void* stream);
+/* waits for every rank's publish, cand_* = MIN over ranks, then the decision of nmb_loop_decide */
+int nmb_peer_wait_decide(const nmb_peer_exchange_t* px, int dtype, nmb_loop_state_t* state, int past_initial,
+                         int patience, void* stream);
+/* theta <- AdamW(theta, sum over ranks of the published gradients); advances the loop state and the exchange epoch */
+int nmb_peer_adamw_step(const nmb_peer_exchange_t* px, int dtype, int d, int H, int n_actions, const nmb_adamw_t* hp,
+                        void* theta, void* theta_t, void* exp_avg, void* exp_avg_sq, nmb_loop_state_t* state,
+                        void* stream);
+
+/* ------------------------------------------------------------------------
  * Exact-GP posterior over a fantasy tree (HES-MC and the qEI/qPI/qSR/qUCB/qKG baselines):
  * replaces model.posterior -> sampler -> condition_on_observations per level and the leaf
  * posterior + sampler (reference acqfs.py:363-373, 413-415; BoTorch/GPyTorch arithmetic of

@@ -38,6 +38,22 @@ __global__ void transpose_kernel(SegTab tb, const T* __restrict__ theta, T* __re
 // torch.optim.AdamW (single-tensor path): p *= 1 - lr*wd; m.lerp_(g, 1-b1); v = b2 v + (1-b2) g^2;
 // denom = sqrt(v)/sqrt(1-b2^t) + eps; p -= (lr/(1-b1^t)) * m/denom
 template <typename T>
+__device__ __forceinline__ void adamw_apply(const nmb_adamw_t& hp, T g, long long t, long long i, int ti,
+                                            T* __restrict__ theta, T* __restrict__ theta_t, T* __restrict__ m,
+                                            T* __restrict__ v) {
+    const double bc1 = 1.0 - ::pow(hp.beta1, (double)t);
+    const double bc2s = ::sqrt(1.0 - ::pow(hp.beta2, (double)t));
+    T p = theta[i] * (T)(1.0 - hp.lr * hp.weight_decay);
+    T mi = m[i], vi = v[i];
+    mi = mi + (g - mi) * (T)(1.0 - hp.beta1);
+    vi = vi * (T)hp.beta2 + (T)(1.0 - hp.beta2) * g * g;
+    const T denom = Num<T>::sqrt(vi) / (T)bc2s + (T)hp.eps;
+    p = p - (T)(hp.lr / bc1) * (mi / denom);
+    theta[i] = p; m[i] = mi; v[i] = vi;
+    if (theta_t) theta_t[ti] = p;
+}
+
+template <typename T>
 __global__ void adamw_kernel(SegTab tb, int use_tab, nmb_adamw_t hp, T* __restrict__ theta, T* __restrict__ theta_t,
                              T* __restrict__ m, T* __restrict__ v, const T* __restrict__ partials, long long n,
                              nmb_loop_state_t* state, int advance) {
@@ -56,17 +72,7 @@ __global__ void adamw_kernel(SegTab tb, int use_tab, nmb_adamw_t hp, T* __restri
 #pragma unroll
                 for (int u = 0; u < 32; ++u) g += pv[u];
             }
-            const long long t = (state ? state->step : 0) + 1;
-            const double bc1 = 1.0 - ::pow(hp.beta1, (double)t);
-            const double bc2s = ::sqrt(1.0 - ::pow(hp.beta2, (double)t));
-            T p = theta[i] * (T)(1.0 - hp.lr * hp.weight_decay);
-            T mi = m[i], vi = v[i];
-            mi = mi + (g - mi) * (T)(1.0 - hp.beta1);
-            vi = vi * (T)hp.beta2 + (T)(1.0 - hp.beta2) * g * g;
-            const T denom = Num<T>::sqrt(vi) / (T)bc2s + (T)hp.eps;
-            p = p - (T)(hp.lr / bc1) * (mi / denom);
-            theta[i] = p; m[i] = mi; v[i] = vi;
-            if (theta_t) theta_t[ti] = p;
+            adamw_apply<T>(hp, g, (state ? state->step : 0) + 1, i, ti, theta, theta_t, m, v);
         }
     }
     (void)advance;
@@ -226,6 +232,156 @@ __global__ void decide_kernel(nmb_loop_state_t* state, int past_initial, int pat
     loop_decide(state, past_initial, patience);
 }
 
+
+// ------------------------------------------------------------------ restart shards over NVLink peer memory
+// One exchange per Adam iteration when the restarts are sharded (SURVEY 8e, C2 + C3), written against the ranks'
+// peer-mapped buffers instead of two NCCL all-reduces:
+//   publish   : this rank's policy gradient (split-K partials already reduced) and its two decision candidates go
+//               into slot[epoch & 1] of its own buffer; the last CTA to finish raises flag[rank] = epoch + 1 in
+//               EVERY rank's buffer (system-scope release).
+//   wait      : one warp spins (acquire) until all ranks' flags reached epoch + 1, MIN-reduces the candidates read
+//               from the peers and takes the snapshot / early-stop decision (identical on every rank).
+//   adamw     : every thread sums its gradient element over the ranks in rank order (bitwise identical everywhere,
+//               so the replicated weights never drift) and applies AdamW: the all-reduce is fused into the update.
+// Double-buffered slots: a rank can run at most one exchange ahead of the slowest one (it cannot pass `wait` of
+// epoch e + 1 before every rank has published e + 1, which each does after its own reads of epoch e).
+// Peer loads use ld.cv (never served from a stale L1 line; peer addresses bypass the local L2).
+struct PeerHdr {
+    unsigned long long flag[NMB_MAX_PEERS];   // flag[r]: last epoch + 1 published by rank r
+    unsigned long long epoch;                 // exchanges completed by this rank
+    unsigned int ticket;                      // CTA counter of publish
+    unsigned int pad;
+};
+static_assert(sizeof(PeerHdr) <= NMB_PEER_HEADER_BYTES, "peer header");
+
+struct PeerTab { unsigned char* base[NMB_MAX_PEERS]; int rank, world; long long n; long long slot_bytes, cand_off; };
+
+template <typename T> static PeerTab make_peertab(const nmb_peer_exchange_t* px) {
+    PeerTab t;
+    for (int r = 0; r < NMB_MAX_PEERS; ++r) t.base[r] = (unsigned char*)px->base[r];
+    t.rank = px->rank; t.world = px->world; t.n = px->n;
+    t.cand_off = (px->n * (long long)sizeof(T) + 15) / 16 * 16;
+    t.slot_bytes = t.cand_off + 16;
+    return t;
+}
+
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) peer_publish_kernel(PeerTab pt, SegTab tb, int use_tab, const T* __restrict__ grad,
+                                                            const nmb_loop_state_t* state) {
+    if (state->done) return;
+    PeerHdr* hdr = reinterpret_cast<PeerHdr*>(pt.base[pt.rank]);
+    const unsigned long long e = hdr->epoch;
+    unsigned char* slot = pt.base[pt.rank] + NMB_PEER_HEADER_BYTES + (e & 1) * pt.slot_bytes;
+    T* dst = reinterpret_cast<T*>(slot);
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < pt.n; i += (long long)gridDim.x * blockDim.x) {
+        int nsp = 1;
+        if (use_tab) { int seg; transposed_index(tb, (int)i, seg); nsp = tb.splits[seg]; }
+        // split-K partials of the weight-gradient kernel summed in split order (deterministic), 16 loads in flight
+        T g = T(0);
+        for (int q0 = 0; q0 < nsp; q0 += 16) {
+            T pv[16];
+#pragma unroll
+            for (int u = 0; u < 16; ++u) pv[u] = q0 + u < nsp ? grad[(size_t)(q0 + u) * pt.n + i] : T(0);
+#pragma unroll
+            for (int u = 0; u < 16; ++u) g += pv[u];
+        }
+        dst[i] = g;
+    }
+    __shared__ int last;
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) last = atomicAdd(&hdr->ticket, 1u) == gridDim.x - 1;
+    __syncthreads();
+    if (!last) return;
+    if (threadIdx.x == 0) {
+        hdr->ticket = 0;
+        double* cand = reinterpret_cast<double*>(slot + pt.cand_off);
+        cand[0] = state->cand_total;
+        cand[1] = state->cand_lck;
+        __threadfence_system();
+    }
+    __syncthreads();
+    if (threadIdx.x < pt.world) {
+        __threadfence_system();
+        st_release_sys(&reinterpret_cast<PeerHdr*>(pt.base[threadIdx.x])->flag[pt.rank], e + 1);
+    }
+}
+
+__global__ void __launch_bounds__(32) peer_wait_decide_kernel(PeerTab pt, nmb_loop_state_t* state, int past_initial,
+                                                              int patience) {
+    if (state->done) return;
+    const PeerHdr* hdr = reinterpret_cast<const PeerHdr*>(pt.base[pt.rank]);
+    const unsigned long long e = hdr->epoch;
+    const int lane = threadIdx.x;
+    double ct = INFINITY, cl = INFINITY;
+    bool timed_out = false;
+    if (lane < pt.world) {
+        // a rank that died must not hang this GPU: give up after ~4e9 cycles (about 2 s) and stop the loop
+        const long long t0 = clock64();
+        while (ld_acquire_sys(&hdr->flag[lane]) < e + 1) {
+            __nanosleep(40);
+            if (clock64() - t0 > 4000000000LL) { timed_out = true; break; }
+        }
+    }
+    if (__any_sync(0xffffffffu, timed_out)) {
+        if (lane == 0) { state->stall = NMB_PEER_TIMEOUT_STALL; state->done_next = 1; state->done = 1; }
+        return;
+    }
+    if (lane < pt.world) {
+        const double* cand = reinterpret_cast<const double*>(pt.base[lane] + NMB_PEER_HEADER_BYTES + (e & 1) * pt.slot_bytes +
+                                                             pt.cand_off);
+        ct = __ldcv(cand);
+        cl = __ldcv(cand + 1);
+    }
+    for (int m = 16; m > 0; m >>= 1) {
+        ct = fmin(ct, __shfl_xor_sync(0xffffffffu, ct, m));
+        cl = fmin(cl, __shfl_xor_sync(0xffffffffu, cl, m));
+    }
+    if (lane == 0) {
+        state->cand_total = ct;
+        state->cand_lck = cl;
+        loop_decide(state, past_initial, patience);
+    }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) peer_adamw_kernel(PeerTab pt, SegTab tb, nmb_adamw_t hp, T* __restrict__ theta,
+                                                         T* __restrict__ theta_t, T* __restrict__ m, T* __restrict__ v,
+                                                         const nmb_loop_state_t* state) {
+    if (state->done) return;
+    const unsigned long long e = reinterpret_cast<const PeerHdr*>(pt.base[pt.rank])->epoch;
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= pt.n) return;
+    const long long off = NMB_PEER_HEADER_BYTES + (long long)(e & 1) * pt.slot_bytes;
+    T pv[NMB_MAX_PEERS];
+#pragma unroll
+    for (int r = 0; r < NMB_MAX_PEERS; ++r)
+        pv[r] = r < pt.world ? __ldcv(reinterpret_cast<const T*>(pt.base[r] + off) + i) : T(0);
+    T g = T(0);
+#pragma unroll
+    for (int r = 0; r < NMB_MAX_PEERS; ++r) g += pv[r];
+    int seg;
+    const int ti = transposed_index(tb, (int)i, seg);
+    adamw_apply<T>(hp, g, state->step + 1, i, ti, theta, theta_t, m, v);
+}
+
+// end of a sharded iteration: the exchange epoch and the loop state advance together
+__global__ void peer_advance_kernel(PeerTab pt, nmb_loop_state_t* state) {
+    if (state->done) return;
+    reinterpret_cast<PeerHdr*>(pt.base[pt.rank])->epoch += 1;
+    state->step += 1;
+    state->done = state->done_next;
+}
+
 struct CopyList { const void* src[8]; void* dst[8]; long long n[8]; int count; };
 
 template <typename T>
@@ -349,6 +505,80 @@ extern "C" int nmb_adamw_flat(int dtype, int64_t n, const nmb_adamw_t* hp, void*
 extern "C" int nmb_loop_decide(nmb_loop_state_t* state, int past_initial, int patience, void* stream) {
     NMB_REQUIRE(state, NMB_EINVAL, "nmb_loop_decide: null state");
     decide_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(state, past_initial, patience);
+    NMB_LAUNCH_CHECK();
+    return 0;
+}
+
+static int validate_peers(const nmb_peer_exchange_t* px, const char* who) {
+    NMB_REQUIRE(px, NMB_EINVAL, "%s: null exchange", who);
+    NMB_REQUIRE(px->world >= 1 && px->world <= NMB_MAX_PEERS && px->rank >= 0 && px->rank < px->world, NMB_EINVAL,
+                "%s: rank %d / world %d (at most %d peers)", who, px->rank, px->world, NMB_MAX_PEERS);
+    NMB_REQUIRE(px->n >= 1, NMB_EINVAL, "%s: n=%lld", who, (long long)px->n);
+    for (int r = 0; r < px->world; ++r) NMB_REQUIRE(px->base[r], NMB_EINVAL, "%s: peer %d buffer is null", who, r);
+    return 0;
+}
+
+extern "C" int64_t nmb_peer_exchange_bytes(int dtype, int64_t n) {
+    const int64_t esz = dtype == NMB_F32 ? 4 : 8;
+    return NMB_PEER_HEADER_BYTES + 2 * ((n * esz + 15) / 16 * 16 + 16);
+}
+
+extern "C" int nmb_peer_publish(const nmb_peer_exchange_t* px, int dtype, const void* grad, int d, int H, int n_actions,
+                                const int32_t* seg_splits_host, const nmb_loop_state_t* state, void* stream) {
+    int rc = validate_peers(px, "nmb_peer_publish");
+    if (rc) return rc;
+    NMB_REQUIRE(grad && state, NMB_EINVAL, "nmb_peer_publish: null argument");
+    SegTab tb;
+    memset(&tb, 0, sizeof(tb));
+    const int use_tab = seg_splits_host != nullptr;
+    if (use_tab) {
+        tb = make_segtab(d, H, n_actions, seg_splits_host);
+        NMB_REQUIRE(tb.off[S_COUNT] == px->n, NMB_EINVAL, "nmb_peer_publish: exchange holds %lld elements, policy has %d",
+                    (long long)px->n, tb.off[S_COUNT]);
+    }
+    const unsigned grid = (unsigned)std::min<long long>((px->n + 255) / 256, 2LL * sm_count());
+    cudaStream_t st = (cudaStream_t)stream;
+    if (dtype == NMB_F64) peer_publish_kernel<double><<<grid, 256, 0, st>>>(make_peertab<double>(px), tb, use_tab, (const double*)grad, state);
+    else if (dtype == NMB_F32) peer_publish_kernel<float><<<grid, 256, 0, st>>>(make_peertab<float>(px), tb, use_tab, (const float*)grad, state);
+    else { set_error("nmb_peer_publish: dtype %d", dtype); return NMB_EINVAL; }
+    NMB_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int nmb_peer_wait_decide(const nmb_peer_exchange_t* px, int dtype, nmb_loop_state_t* state, int past_initial,
+                                    int patience, void* stream) {
+    int rc = validate_peers(px, "nmb_peer_wait_decide");
+    if (rc) return rc;
+    NMB_REQUIRE(state && (dtype == NMB_F64 || dtype == NMB_F32), NMB_EINVAL, "nmb_peer_wait_decide: bad argument");
+    const PeerTab pt = dtype == NMB_F64 ? make_peertab<double>(px) : make_peertab<float>(px);
+    peer_wait_decide_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(pt, state, past_initial, patience);
+    NMB_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int nmb_peer_adamw_step(const nmb_peer_exchange_t* px, int dtype, int d, int H, int n_actions,
+                                   const nmb_adamw_t* hp, void* theta, void* theta_t, void* exp_avg, void* exp_avg_sq,
+                                   nmb_loop_state_t* state, void* stream) {
+    int rc = validate_peers(px, "nmb_peer_adamw_step");
+    if (rc) return rc;
+    NMB_REQUIRE(hp && theta && exp_avg && exp_avg_sq && state, NMB_EINVAL, "nmb_peer_adamw_step: null argument");
+    SegTab tb = make_segtab(d, H, n_actions, nullptr);
+    NMB_REQUIRE(tb.off[S_COUNT] == px->n, NMB_EINVAL, "nmb_peer_adamw_step: exchange holds %lld elements, policy has %d",
+                (long long)px->n, tb.off[S_COUNT]);
+    cudaStream_t st = (cudaStream_t)stream;
+    const unsigned grid = (unsigned)((px->n + 255) / 256);
+    PeerTab pt;
+    if (dtype == NMB_F64) {
+        pt = make_peertab<double>(px);
+        peer_adamw_kernel<double><<<grid, 256, 0, st>>>(pt, tb, *hp, (double*)theta, (double*)theta_t, (double*)exp_avg,
+                                                         (double*)exp_avg_sq, state);
+    } else if (dtype == NMB_F32) {
+        pt = make_peertab<float>(px);
+        peer_adamw_kernel<float><<<grid, 256, 0, st>>>(pt, tb, *hp, (float*)theta, (float*)theta_t, (float*)exp_avg,
+                                                        (float*)exp_avg_sq, state);
+    } else { set_error("nmb_peer_adamw_step: dtype %d", dtype); return NMB_EINVAL; }
+    NMB_LAUNCH_CHECK();
+    peer_advance_kernel<<<1, 1, 0, st>>>(pt, state);
     NMB_LAUNCH_CHECK();
     return 0;
 }

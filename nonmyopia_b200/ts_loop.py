@@ -36,7 +36,7 @@ class TSAMLoop:
                  budget: float, lr: float, past_initial: bool, prev_cost: float = 0.0, n_global: Optional[int] = None,
                  max_iter: int = 500, record_history: bool = False, record_trajectory: bool = False,
                  patience: int = 50, betas=(0.9, 0.999), eps: float = 1e-8,
-                 weight_decay: float = 1e-2, group=None):
+                 weight_decay: float = 1e-2, group=None, exchange: str = "auto"):
         self.eng = eng
         d, H, L, N = eng.d, eng.H, eng.L, eng.N
         dt, dev = eng.dtype, eng.device
@@ -76,13 +76,29 @@ class TSAMLoop:
         self.graph = None
         # process group over which the restarts are sharded (None: single GPU)
         self.group = group
+        self.px, self.exchange = None, "none"
         if group is not None:
             import torch.distributed as dist
+            from .peer import PeerExchange
             self._dist = dist
             self._cand = self.state[56:72].view(torch.float64)
             self.grad = torch.zeros_like(self.theta)
             self._one_split = (C.c_int32 * 20)()
-        # rollout_fwd, objective, snapshot, rollout_bwd, wgrad, adamw, advance (+ decide, reduce when sharded)
+            # per-iteration exchange (gradient SUM + decision MIN): own kernels over NVLink peer memory, fused with
+            # the AdamW update ("peer"), or two NCCL all-reduces ("nccl"); "auto" falls back to NCCL with the reason
+            if exchange not in ("auto", "peer", "nccl"):
+                raise ValueError(f"exchange={exchange!r}")
+            self.exchange, self.exchange_note = "nccl", None
+            if exchange != "nccl":
+                self.px, why = PeerExchange.try_get(group, self.theta.numel(), dt, dev)
+                if self.px is not None:
+                    self.exchange = "peer"
+                elif exchange == "peer":
+                    raise _lib.NmbError(f"peer exchange unavailable: {why}")
+                else:
+                    self.exchange_note = why
+        # rollout_fwd, objective, snapshot, rollout_bwd, wgrad, adamw, advance; sharded: + decide, reduce (NCCL) or
+        # + publish, wait/decide (peer memory; the advance is the exchange's own)
         self.n_launches_per_iter = 7 if group is None else 9
 
     # ------------------------------------------------------------------ one iteration
@@ -107,6 +123,8 @@ class TSAMLoop:
             _lib.ptr(self.total), _lib.ptr(self.g_loss), _lib.ptr(self.g_cost), _lib.ptr(self.g_X),
             _lib.ptr(self.g_A), _lib.ptr(self.hist_loss), _lib.ptr(self.hist_cost), _lib.ptr(self.hist_X),
             C.c_int64(self.max_iter), int(self.group is not None), state_p, st), "nmb_ts_objective")
+        if self.px is not None:
+            return self._finish_iteration_peer(rm, state_p, st, mark)
         if self.group is not None:
             # restarts sharded over ranks: one MIN all-reduce of (min total, min loss+cost+KL) keeps the
             # snapshot / early-stop decision identical on every rank
@@ -136,9 +154,33 @@ class TSAMLoop:
                    "nmb_policy_adamw_step")
         mark("adamw")
 
+    def _finish_iteration_peer(self, rm, state_p, st, mark) -> None:
+        """Rest of a sharded iteration with the exchange over NVLink peer memory: the decision needs the other
+        ranks' minima and the update their gradients, so both wait for ONE rendezvous after the local backward."""
+        eng, lib = self.eng, self.eng.lib
+        px = self.px.byref()
+        mark("objective+snapshot")
+        eng.backward(self.prob, rm, self.g_loss, self.g_cost, self.g_X, self.g_A)
+        mark("ts_rollout_bwd")
+        partials = eng.weight_grad_partials(self.prob, self.main)
+        mark("policy_wgrad")
+        _lib.check(lib.nmb_peer_publish(px, eng.dt, _lib.ptr(partials), eng.d, eng.H, 1, eng.seg_splits, state_p, st),
+                   "nmb_peer_publish")
+        _lib.check(lib.nmb_peer_wait_decide(px, eng.dt, state_p, int(self.past_initial), self.patience, st),
+                   "nmb_peer_wait_decide")
+        _lib.check(lib.nmb_snapshot_if_improved(eng.dt, 6, self._src, self._dst, self._cnt, state_p, st),
+                   "nmb_snapshot_if_improved")
+        _lib.check(lib.nmb_peer_adamw_step(px, eng.dt, eng.d, eng.H, 1, C.byref(self.hp), _lib.ptr(self.theta),
+                                           _lib.ptr(self.theta_t), _lib.ptr(self.m), _lib.ptr(self.v), state_p, st),
+                   "nmb_peer_adamw_step")
+        mark("adamw")
+
     def read_state(self) -> te.LoopState:
         raw = self.state[:C.sizeof(te.LoopState)].cpu().numpy().tobytes()
-        return te.LoopState.from_buffer_copy(raw)
+        st = te.LoopState.from_buffer_copy(raw)
+        if st.stall == -777:
+            raise _lib.NmbError("peer exchange timed out: a rank did not publish within ~2 s (loop stopped)")
+        return st
 
     def capture(self) -> None:
         """Capture one iteration in a CUDA graph (after a dry pass that sets kernel attributes)."""

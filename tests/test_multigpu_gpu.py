@@ -39,7 +39,7 @@ def _entry(rank, fn, store, tmp, *args):
 
 
 # ----------------------------------------------------------------------------- HES-TS-AM (device loop)
-def _ts_am_worker(rank, group, tmp):
+def _ts_am_worker(rank, group, tmp, exchange):
     from nonmyopia_b200 import sharding as sh, ts_engine as te
     from nonmyopia_b200.ts_loop import TSAMLoop
     from tests.test_path_gpu import _product_path
@@ -49,7 +49,9 @@ def _ts_am_worker(rank, group, tmp):
     lo, hi = sh.restart_range(N, rank, 2)
     eng = te.TSRollout(_product_path(fx), d, Hh, L, hi - lo, fx["cost"])
     loop = TSAMLoop(eng, te.flatten_params(fx["policy"]), fx["prev_X"][lo:hi], fx["prev_y"][lo:hi], fx["prev_h"][lo:hi],
-                    budget=fx["budget"], lr=fx["lr"], past_initial=False, max_iter=fx["n_iter"], n_global=N, group=group)
+                    budget=fx["budget"], lr=fx["lr"], past_initial=False, max_iter=fx["n_iter"], n_global=N, group=group,
+                    exchange=exchange)
+    assert loop.exchange == exchange
     draws = []
     for dr in fx["draws"]:
         full = (*pack_draws(dr["main_rot"], dr["main_noise"], L, N), *pack_draws(dr["orig_rot"], dr["orig_noise"], L, N))
@@ -70,12 +72,14 @@ def _ts_am_worker(rank, group, tmp):
         assert H.rel_err(final[k], ref, atol=1e-3) < 1e-8, k
 
 
-def test_ts_am_loop_sharded_matches_reference_golden():
+@pytest.mark.parametrize("exchange", ["nccl", "peer"])
+def test_ts_am_loop_sharded_matches_reference_golden(exchange):
+    """exchange = "peer": gradient SUM / decision MIN through the nmb_peer_* kernels over NVLink peer memory."""
     _need_two()
-    _spawn(_ts_am_worker)
+    _spawn(_ts_am_worker, exchange)
 
 
-def _graph_worker(rank, group, tmp):
+def _graph_worker(rank, group, tmp, exchange):
     """Default mode: collectives captured in the per-iteration CUDA graph; the replicated policy must stay
     bit-identical on both ranks and the loop state must advance in lock step."""
     import torch.distributed as dist
@@ -87,7 +91,8 @@ def _graph_worker(rank, group, tmp):
     lo, hi = sh.restart_range(N, rank, 2)
     eng = te.TSRollout(_product_path(fx), d, Hh, L, hi - lo, fx["cost"], seed=77 + rank)
     loop = TSAMLoop(eng, te.flatten_params(fx["policy"]), fx["prev_X"][lo:hi], fx["prev_y"][lo:hi], fx["prev_h"][lo:hi],
-                    budget=fx["budget"], lr=1e-3, past_initial=True, max_iter=64, n_global=N, group=group)
+                    budget=fx["budget"], lr=1e-3, past_initial=True, max_iter=64, n_global=N, group=group,
+                    exchange=exchange)
     st = loop.run(32, poll_every=8)
     assert st.step == 32
     both = [torch.empty_like(loop.theta) for _ in range(2)]
@@ -100,9 +105,10 @@ def _graph_worker(rank, group, tmp):
     assert torch.equal(other[0], other[1])
 
 
-def test_ts_am_graph_loop_two_ranks_lockstep():
+@pytest.mark.parametrize("exchange", ["nccl", "peer"])
+def test_ts_am_graph_loop_two_ranks_lockstep(exchange):
     _need_two()
-    _spawn(_graph_worker)
+    _spawn(_graph_worker, exchange)
 
 
 # ----------------------------------------------------------------------------- free parameters through Actor
