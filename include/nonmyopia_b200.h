@@ -303,6 +303,10 @@ typedef struct nmb_gp {
     const void* linv;       /* [ldl][ldl] inverse Cholesky root, row-major, lower triangular, zero padded */
     const void* linv_t;     /* [ldl][ldl] its transpose, zero padded */
     const void* alpha;      /* [n] (K + s2 I)^-1 (y - c) */
+    /* FP64 tensor-pipe kernels: the same two matrices tiled by 64-column blocks, [ceil(ldl/64)][ldl][72]
+     * (tile[b][k][c] = M[k][64 b + c] for c < 64 and 64 b + c < ldl, else 0): one bulk copy per operand chunk */
+    const void* linv_tiles;
+    const void* linv_t_tiles;
 } nmb_gp_t;
 
 typedef struct nmb_tree {

@@ -17,6 +17,7 @@
 //                slots are complete when its own level runs).
 //   gather_gu  : one warp per node: gU = 2 g_q u + sum_t g_dot_t u(z_t) + sum_desc g_dot u(desc),
 //                descendants visited in a fixed order.
+#include <algorithm>
 #include "policy_mma.cuh"
 
 namespace nmb {
@@ -24,7 +25,7 @@ namespace nmb {
 template <typename T> struct GpDev {
     int d, n, kernel_id, ldu, ldl;
     T amp, noise, mean_const;
-    const T *train_x, *inv_ls, *linv, *linv_t, *alpha;
+    const T *train_x, *inv_ls, *linv, *linv_t, *alpha, *linv_tiles, *linv_t_tiles;
 };
 
 template <typename T> static GpDev<T> to_dev(const nmb_gp_t& g) {
@@ -33,6 +34,7 @@ template <typename T> static GpDev<T> to_dev(const nmb_gp_t& g) {
     o.amp = (T)g.amplitude; o.noise = (T)g.noise; o.mean_const = (T)g.mean_const;
     o.train_x = (const T*)g.train_x; o.inv_ls = (const T*)g.inv_ls; o.linv = (const T*)g.linv;
     o.linv_t = (const T*)g.linv_t; o.alpha = (const T*)g.alpha;
+    o.linv_tiles = (const T*)g.linv_tiles; o.linv_t_tiles = (const T*)g.linv_t_tiles;
     return o;
 }
 
@@ -404,44 +406,117 @@ __global__ void __launch_bounds__(128) level_bwd_kernel(GpDev<T> g, const __grid
     }
 }
 
-// ------------------------------------------------------------------ gU gather: warp per node
+// ------------------------------------------------------------------ gU gather
+// gU[x] = 2 Gq[x] u(x) + sum_{t < s} Gdot[x][t] u(z_t) + sum_{y below x} Gdot[y][s] u(y), descendants in a fixed order.
+// Pure streaming of n-vectors: (1 + s + #descendants) reads per node.  Two things matter:
+//  * work is issued restart-major (all nodes of one restart's tree, ~MBs, by neighbouring warps at the same time), so
+//    a vector read by its s ancestors and by itself is served from L2 after the first touch instead of HBM;
+//  * a node with hundreds of descendants (the root of a [64,4,2] tree has 832) gets a whole CTA: the warps split the
+//    descendant list, partial sums meet in shared memory in warp order (deterministic).
+// Descendants are visited four at a time so that 16 independent loads per lane are in flight.
+template <typename T> struct DescIter {
+    const TreeDev& tr;
+    int s;
+    long long i;
+    __device__ DescIter(const TreeDev& t, int s_, long long i_) : tr(t), s(s_), i(i_) {}
+    __device__ long long count() const {
+        long long c = 0;
+        for (int s2 = s + 1; s2 < tr.n_levels; ++s2) c += tr.cnt[s2] / tr.cnt[s];
+        return c;
+    }
+    // e-th descendant in (level, then sibling) order -> global node index
+    __device__ long long node(long long e) const {
+        for (int s2 = s + 1; s2 < tr.n_levels; ++s2) {
+            const long long c = tr.cnt[s2] / tr.cnt[s];
+            if (e < c) return tr.off[s2] + i + e * tr.cnt[s];
+            e -= c;
+        }
+        return -1;
+    }
+};
+
 template <typename T>
-__global__ void __launch_bounds__(256) gather_gu_kernel(GpDev<T> g, const __grid_constant__ TreeDev tr, StateDev<T> st) {
-    const int lane = threadIdx.x & 31;
-    const long long warp0 = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
+__device__ __forceinline__ void gather_desc(const GpDev<T>& g, const TreeDev& tr, const StateDev<T>& st, int s, long long i,
+                                            long long e0, long long e1, long long estep, int k0, int lane, T (&a)[4]) {
+    const DescIter<T> it(tr, s, i);
     const int NL = tr.n_levels;
-    const long long total = tr.off[NL];
-    // heavy (root-side) nodes first: node order is already level 0, 1, ...
-    for (long long node = warp0; node < total; node += nwarps) {
-        int s = 0;
-        while (node >= tr.off[s + 1]) ++s;
-        const long long i = node - tr.off[s];
+    for (long long e = e0; e < e1; e += 4 * estep) {
+        T gd[4], v[4][4];
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+            const long long eb = e + b * estep;
+            const long long dn = eb < e1 ? it.node(eb) : -1;
+            gd[b] = dn >= 0 ? st.Gdot[(size_t)dn * NL + s] : T(0);
+            const T* uy = st.U + (size_t)(dn >= 0 ? dn : 0) * g.ldu;
+#pragma unroll
+            for (int u = 0; u < 4; ++u) { const int k = k0 + lane + 32 * u; v[b][u] = (dn >= 0 && k < g.n) ? uy[k] : T(0); }
+        }
+#pragma unroll
+        for (int b = 0; b < 4; ++b)
+#pragma unroll
+            for (int u = 0; u < 4; ++u) a[u] = fma(gd[b], v[b][u], a[u]);
+    }
+}
+
+// restart-major work order over the levels [s_lo, s_hi): item -> (level, index inside the level)
+__device__ __forceinline__ void restart_major(const TreeDev& tr, int s_lo, int s_hi, long long item, int& s, long long& i) {
+    const long long n_r = tr.cnt[0];
+    long long per = 0;
+    for (int l = s_lo; l < s_hi; ++l) per += tr.cnt[l] / n_r;
+    const long long r = item / per;
+    long long m = item - r * per;
+    s = s_lo;
+    while (m >= tr.cnt[s] / n_r) { m -= tr.cnt[s] / n_r; ++s; }
+    i = m * n_r + r;
+}
+
+template <typename T, bool CTA_PER_NODE>
+__global__ void __launch_bounds__(256) gather_gu_kernel(GpDev<T> g, const __grid_constant__ TreeDev tr, StateDev<T> st, int s_lo,
+                                                        int s_hi, long long n_items) {
+    __shared__ T part[8][128];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int NL = tr.n_levels;
+    const long long unit0 = CTA_PER_NODE ? blockIdx.x : (((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+    const long long nunits = CTA_PER_NODE ? gridDim.x : (((long long)gridDim.x * blockDim.x) >> 5);
+    for (long long item = unit0; item < n_items; item += nunits) {
+        int s;
+        long long i;
+        restart_major(tr, s_lo, s_hi, item, s, i);
+        const long long node = tr.off[s] + i;
         const T* ux = st.U + (size_t)node * g.ldu;
         T* out = st.gU + (size_t)node * g.ldu;
         const T gq2 = T(2) * st.Gq[node];
-        for (int k0 = lane; k0 < g.n; k0 += 32 * 4) {
-            // 4 strided elements per lane per pass keeps the descendant loop's loads independent
-            T a[4];
+        const long long D = DescIter<T>(tr, s, i).count();
+        for (int k0 = 0; k0 < g.n; k0 += 128) {
+            T a[4] = {T(0), T(0), T(0), T(0)};
+            if (CTA_PER_NODE) {
+                gather_desc<T>(g, tr, st, s, i, warp, D, 8, k0, lane, a);
 #pragma unroll
-            for (int u = 0; u < 4; ++u) { const int k = k0 + 32 * u; a[u] = k < g.n ? gq2 * ux[k] : T(0); }
-            for (int t = 0; t < s; ++t) {
-                const T gd = st.Gdot[(size_t)node * NL + t];
-                const T* uz = st.U + (size_t)(tr.off[t] + i % tr.cnt[t]) * g.ldu;
+                for (int u = 0; u < 4; ++u) part[warp][lane + 32 * u] = a[u];
+                __syncthreads();
+                if (threadIdx.x < 128 && k0 + threadIdx.x < g.n) {
+                    const int k = k0 + threadIdx.x;
+                    T v = gq2 * ux[k];
+                    for (int t = 0; t < s; ++t)
+                        v = fma(st.Gdot[(size_t)node * NL + t], st.U[(size_t)(tr.off[t] + i % tr.cnt[t]) * g.ldu + k], v);
 #pragma unroll
-                for (int u = 0; u < 4; ++u) { const int k = k0 + 32 * u; if (k < g.n) a[u] = fma(gd, uz[k], a[u]); }
-            }
-            for (int s2 = s + 1; s2 < NL; ++s2) {
-                for (long long y = i; y < tr.cnt[s2]; y += tr.cnt[s]) {
-                    const long long dn = tr.off[s2] + y;
-                    const T gd = st.Gdot[(size_t)dn * NL + s];
-                    const T* uy = st.U + (size_t)dn * g.ldu;
-#pragma unroll
-                    for (int u = 0; u < 4; ++u) { const int k = k0 + 32 * u; if (k < g.n) a[u] = fma(gd, uy[k], a[u]); }
+                    for (int w = 0; w < 8; ++w) v += part[w][threadIdx.x];
+                    out[k] = v;
                 }
-            }
+                __syncthreads();
+            } else {
 #pragma unroll
-            for (int u = 0; u < 4; ++u) { const int k = k0 + 32 * u; if (k < g.n) out[k] = a[u]; }
+                for (int u = 0; u < 4; ++u) { const int k = k0 + lane + 32 * u; a[u] = k < g.n ? gq2 * ux[k] : T(0); }
+                for (int t = 0; t < s; ++t) {
+                    const T gd = st.Gdot[(size_t)node * NL + t];
+                    const T* uz = st.U + (size_t)(tr.off[t] + i % tr.cnt[t]) * g.ldu;
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) { const int k = k0 + lane + 32 * u; if (k < g.n) a[u] = fma(gd, uz[k], a[u]); }
+                }
+                gather_desc<T>(g, tr, st, s, i, 0, D, 1, k0, lane, a);
+#pragma unroll
+                for (int u = 0; u < 4; ++u) { const int k = k0 + lane + 32 * u; if (k < g.n) out[k] = a[u]; }
+            }
         }
     }
 }
@@ -531,6 +606,7 @@ static int validate_gp(const nmb_gp_t* gp, int dtype, const char* who) {
 template <int DM>
 static int launch_whiten_mma_d(const nmb_gp_t* gp, bool bwd, const double* pts, int64_t n_pts, double* U, double* m0,
                                double* q, const double* gU, const double* g_m0, double* g_pts, cudaStream_t st) {
+    NMB_REQUIRE(gp->linv_tiles && gp->linv_t_tiles, NMB_EINVAL, "gp whiten (FP64): linv_tiles / linv_t_tiles are null");
     GpDev<double> g = to_dev<double>(*gp);
     static const int cand[5][2] = {{32, 4}, {32, 3}, {24, 4}, {24, 3}, {16, 3}};
     int R = 0, nst = 0;
@@ -677,9 +753,28 @@ extern "C" int nmb_mc_gather_gu(const nmb_gp_t* gp, const nmb_tree_t* tree, cons
     if (rc) return rc;
     NMB_REQUIRE(st && st->U && st->gU && st->Gq && st->Gdot, NMB_EINVAL, "nmb_mc_gather_gu: null array");
     cudaStream_t s = (cudaStream_t)stream;
-    const unsigned grid = warp_grid(tr.off[tr.n_levels]);
-    if (dtype == NMB_F64) gather_gu_kernel<double><<<grid, 256, 0, s>>>(to_dev<double>(*gp), tr, to_dev<double>(*st));
-    else gather_gu_kernel<float><<<grid, 256, 0, s>>>(to_dev<float>(*gp), tr, to_dev<float>(*st));
+    // levels whose nodes have >= 64 descendants get a CTA per node, the rest a warp per node
+    int s_heavy = 0;
+    while (s_heavy < tr.n_levels) {
+        long long desc = 0;
+        for (int s2 = s_heavy + 1; s2 < tr.n_levels; ++s2) desc += tr.cnt[s2] / tr.cnt[s_heavy];
+        if (desc < 64) break;
+        ++s_heavy;
+    }
+    const long long n_heavy = tr.off[s_heavy], n_light = tr.off[tr.n_levels] - n_heavy;
+#define NMB_GG(T)                                                                                                       \
+    do {                                                                                                                \
+        if (n_heavy > 0) {                                                                                              \
+            const unsigned grid = (unsigned)std::min<long long>(n_heavy, 16LL * sm_count());                            \
+            gather_gu_kernel<T, true><<<grid, 256, 0, s>>>(to_dev<T>(*gp), tr, to_dev<T>(*st), 0, s_heavy, n_heavy);    \
+        }                                                                                                               \
+        if (n_light > 0)                                                                                                \
+            gather_gu_kernel<T, false><<<warp_grid(n_light), 256, 0, s>>>(to_dev<T>(*gp), tr, to_dev<T>(*st), s_heavy,  \
+                                                                         tr.n_levels, n_light);                         \
+    } while (0)
+    if (dtype == NMB_F64) NMB_GG(double);
+    else NMB_GG(float);
+#undef NMB_GG
     NMB_LAUNCH_CHECK();
     return 0;
 }

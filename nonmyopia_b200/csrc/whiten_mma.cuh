@@ -10,8 +10,8 @@
 // consumer warps own 8-row x 32-col accumulator tiles, A fragments come from a row-major tile with stride
 // KS = 4 mod 16 doubles (conflict free).  Replaces the DFMA 2x4 register-tile product (18 % of the FP64 peak at
 // n = 500: bound by the shared-memory data pipe, see the header of policy_mma.cuh).
-// The triangular operands are passed zero-padded, [ldl][ldl] with ldl = n rounded up to 8, so that every bulk copy
-// is 16-byte aligned and k extents are multiples of 4.
+// The triangular operands are passed zero-padded to ldl = n rounded up to 8 (k extents are multiples of 4) and
+// pre-tiled by 64-column blocks, [ceil(ldl/64)][ldl][72], so that a chunk is one contiguous, 16-byte aligned bulk copy.
 // Reference: GPyTorch's exact prediction strategy behind model.posterior (acqfs.py:366, 414).
 #pragma once
 #include "policy_mma.cuh"
@@ -42,25 +42,25 @@ struct WhSmem {
     }
 };
 
-// Producer warp: chunks of the triangular operand B [ldl][ldl] in consumption order.
+// Producer warp: chunks of the triangular operand in consumption order.  The operand is pre-tiled on the host,
+// Bt[column block][k][kSW] (64 columns + 8 pad = the stage row stride), so a [kn k-rows][kSW] chunk is ONE contiguous
+// bulk copy that lands in the stage layout as is (32 per-row copies of 512 B left the consumers waiting on the
+// copy engine: 18 % of the samples on the full-barrier wait).
 // forward (LOWER_ROWS = false): column block cb needs rows [0, cb + 64); backward: rows [cb, ldl).
 template <int NST, bool LOWER_ROWS>
-__device__ __forceinline__ void wh_producer(const double* __restrict__ B, int n, int ldl, const MmaRing& rg) {
-    const int lane = threadIdx.x & 31;
+__device__ __forceinline__ void wh_producer(const double* __restrict__ Bt, int n, int ldl, const MmaRing& rg) {
+    if ((threadIdx.x & 31) != 0) return;
     unsigned c = 0;
     for (int cb = 0; cb < n; cb += kOB) {
-        const unsigned row_bytes = (unsigned)min(kOB, ldl - cb) * 8u;
+        const double* tile = Bt + (size_t)(cb / kOB) * ldl * kSW;
         const int k_lo = LOWER_ROWS ? cb : 0, k_hi = LOWER_ROWS ? ldl : min(cb + kOB, ldl);
         for (int k0 = k_lo; k0 < k_hi; k0 += kKC, ++c) {
             const unsigned slot = c % NST, fill = c / NST;
             if (fill > 0) mbar_wait(rg.empty0 + 8 * slot, (fill - 1) & 1);
-            const int kn = min(kKC, k_hi - k0);
+            const unsigned bytes = (unsigned)min(kKC, k_hi - k0) * kSW * 8u;
             const unsigned full = rg.full0 + 8 * slot;
-            if (lane == 0) mbar_arrive_expect_tx(full, row_bytes * (unsigned)kn);
-            __syncwarp();
-            if (lane < kn)
-                bulk_g2s(smem_u32(rg.stage + (size_t)slot * kStageElems + lane * kSW), B + (size_t)(k0 + lane) * ldl + cb,
-                         row_bytes, full);
+            mbar_arrive_expect_tx(full, bytes);
+            bulk_g2s(smem_u32(rg.stage + (size_t)slot * kStageElems), tile + (size_t)k0 * kSW, bytes, full);
         }
     }
 }
@@ -90,7 +90,7 @@ __global__ void __launch_bounds__(288, 1) whiten_fwd_mma_kernel(GpDev<double> g,
     wh_init_barriers(sm, NST, ncw);
     const MmaRing ring{sm.stage, sm.full0, sm.empty0, sm.KS};
     if (warp == ncw) {
-        wh_producer<NST, false>(g.linv_t, n, ldl, ring);
+        wh_producer<NST, false>(g.linv_t_tiles, n, ldl, ring);
         return;
     }
     const int KS = sm.KS;
@@ -184,7 +184,7 @@ __global__ void __launch_bounds__(288, 1) whiten_bwd_mma_kernel(GpDev<double> g,
     wh_init_barriers(sm, NST, ncw);
     const MmaRing ring{sm.stage, sm.full0, sm.empty0, sm.KS};
     if (warp == ncw) {
-        wh_producer<NST, true>(g.linv, n, ldl, ring);
+        wh_producer<NST, true>(g.linv_tiles, n, ldl, ring);
         return;
     }
     const int KS = sm.KS;

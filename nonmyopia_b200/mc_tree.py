@@ -24,7 +24,7 @@ class GpStruct(C.Structure):
                 ("ldl", C.c_int32), ("_pad", C.c_int32),
                 ("amplitude", C.c_double), ("noise", C.c_double), ("mean_const", C.c_double),
                 ("train_x", C.c_void_p), ("inv_ls", C.c_void_p), ("linv", C.c_void_p), ("linv_t", C.c_void_p),
-                ("alpha", C.c_void_p)]
+                ("alpha", C.c_void_p), ("linv_tiles", C.c_void_p), ("linv_t_tiles", C.c_void_p)]
 
 
 class TreeStruct(C.Structure):
@@ -40,6 +40,18 @@ class TreeState(C.Structure):
     _fields_ = [(n, C.c_void_p) for n in _names]
 
 
+def _col_tiles(M: Tensor, width: int = 64, stride: int = 72) -> Tensor:
+    """[ldl][ldl] -> [ceil(ldl/width)][ldl][stride]: 64-column blocks padded to the 72-double row stride of the
+    shared-memory stage, so one contiguous bulk copy moves a whole operand chunk (csrc/whiten_mma.cuh)."""
+    ldl = M.shape[0]
+    nb = (ldl + width - 1) // width
+    out = torch.zeros(nb, ldl, stride, dtype=M.dtype, device=M.device)
+    for b in range(nb):
+        w = min(width, ldl - b * width)
+        out[b, :, :w] = M[:, b * width:b * width + w]
+    return out
+
+
 def gp_struct(gp: SurrogateGP, dtype) -> tuple:
     """``nmb_gp_t`` + the tensors it points to (kept alive by the caller)."""
     n, d = gp.n, gp.d
@@ -49,6 +61,7 @@ def gp_struct(gp: SurrogateGP, dtype) -> tuple:
     linv[:n, :n] = gp.Linv.to(dtype)
     keep = dict(train_x=gp.train_X.to(dtype).contiguous(), inv_ls=(1.0 / gp.lengthscale).to(dtype).contiguous(),
                 linv=linv, linv_t=linv.T.contiguous(), alpha=gp.alpha.to(dtype).contiguous())
+    keep["linv_tiles"], keep["linv_t_tiles"] = _col_tiles(keep["linv"]), _col_tiles(keep["linv_t"])
     ldu = (n + 3) // 4 * 4
     st = GpStruct(d=d, n=n, kernel_id=_lib.KERNEL_IDS[gp.kernel], ldu=ldu, ldl=ldl, amplitude=gp.amplitude, noise=gp.noise,
                   mean_const=gp.mean_const, **{k: v.data_ptr() for k, v in keep.items()})
