@@ -100,7 +100,10 @@ def run_mc(args, rank, world):
         loss = rd["acqf_loss"] + abs(budget - rd["acqf_cost"])
         opt.step(torch.autograd.grad(loss.sum() / args.restarts, params, allow_unused=True))
 
-    ms = timed(step, args.steps)
+    mode = "eager"
+    # 8 warm-up iterations: the first ones grow the caching allocator (2 x 853 MB workspaces) and load modules
+    ms = timed(step, args.steps, warmup=8)
+    print(f"rank {rank}: {ms:.3f} ms/step ({mode})", file=sys.stderr, flush=True)
     if world > 1:
         import torch.distributed as dist
         t = torch.tensor([ms], device=dev, dtype=F64)
@@ -113,7 +116,7 @@ def run_mc(args, rank, world):
                                 for s in range(L + 1))
     peak = fp64_peak()
     out = dict(case="cfg3_hartmann_hes_mc", metric="hes_lookahead_node_posterior_evals_per_s_fwd_bwd",
-               value=nodes / (ms * 1e-3), unit="node evals/s", n_gpus=world, ms_per_step=ms, steps=args.steps,
+               value=nodes / (ms * 1e-3), unit="node evals/s", n_gpus=world, ms_per_step=ms, steps=args.steps, launch_mode=mode,
                dtype="f64", config=dict(workload=f"Hartmann-6D HES-MC tree nf={nf}, n={n} GP points, {args.restarts} restarts "
                                         f"({n_r} per rank), S_a=64, FP64 (BASELINE configs[2])",
                                         nodes_per_step=nodes, flops_per_step=flops),
@@ -228,7 +231,7 @@ def main():
     ap.add_argument("case", choices=["mc", "tf32", "sweep"])
     ap.add_argument("--restarts", type=int, default=None)
     ap.add_argument("--widths", default="64,4,2")
-    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--max-restarts", type=int, default=8192)
     args = ap.parse_args()
     if args.restarts is None:
