@@ -248,6 +248,17 @@ int nmb_adamw_flat(int dtype, int64_t n, const nmb_adamw_t* hp, void* param, voi
                    const void* grad, nmb_loop_state_t* state, int advance_state, void* stream);
 
 /* ------------------------------------------------------------------------
+ * Cholesky root of the training covariance and its explicit inverse: the caches behind SingleTaskGP.posterior that
+ * GPyTorch builds once per model (psd_safe_cholesky of K + s2 I and the inverse root it multiplies by; reached from
+ * reference acqfs.py:258-266, 364-373).  `batch` row-major matrices, one CTA each (one warp for n <= 32):
+ * A [n][lda] is overwritten by L (lower, strict upper triangle zeroed), Linv (may be NULL) receives L^-1.
+ * info[b] follows LAPACK potrf: 0, or k > 0 when the leading minor of order k is not positive definite (the caller
+ * applies GPyTorch's jitter rule and retries on a fresh copy).  n <= 800 (GPyTorch's max_cholesky_size).
+ * ---------------------------------------------------------------------- */
+int nmb_cholesky_root(int dtype, int n, int batch, void* A, int64_t lda, int64_t stride_a, void* Linv, int64_t ldi,
+                      int64_t stride_i, int32_t* info, void* stream);
+
+/* ------------------------------------------------------------------------
  * Restart shards over NVLink peer memory (one process per GPU; SURVEY 8e C2 + C3): the per-iteration exchange of
  * the sharded Actor.query loop - policy-gradient SUM and the MIN of the two snapshot-decision candidates
  * (actor.py:622-639, 641-648) - written against peer-mapped buffers, fused with the AdamW update, instead of two

@@ -13,8 +13,8 @@ max_cholesky_size) and keeps the caches the kernels stream:
 * ``alpha`` mean cache ``(K + s2 I)^-1 (y - c)``
 * ``beta``  whitened targets ``L^-1 (y - c)`` (``mu(x) = c + u(x) . beta`` with ``u = L^-1 k``)
 
-The once-per-BO-step factorisation uses ``torch.linalg`` on the device (cuSOLVER); it is
-outside the optimisation loop.
+The once-per-BO-step factorisation and the inverse root are one launch of the ``nmb_cholesky_root``
+kernel (csrc/chol.cu: one CTA per matrix, blocked, panel in shared memory).
 """
 from __future__ import annotations
 
@@ -50,11 +50,26 @@ def kernel_matrix(x1: Tensor, x2: Tensor, kernel: str, lengthscale: Tensor, outp
     return K
 
 
-def _psd_safe_cholesky(A: Tensor) -> Tensor:
-    """GPyTorch's jitter rule (linear_operator psd_safe_cholesky)."""
-    L, info = torch.linalg.cholesky_ex(A)
+def cholesky_root(A: Tensor, inverse: bool = True):
+    """Lower Cholesky factor (and its explicit inverse) of ``A [..., n, n]`` by the ``nmb_cholesky_root`` kernel.
+    Returns ``(L, Linv or None, info [batch] int32)``; ``A`` is not modified."""
+    n = A.shape[-1]
+    L = A.detach().reshape(-1, n, n).clone().contiguous()
+    batch = L.shape[0]
+    Linv = torch.empty_like(L) if inverse else None
+    info = torch.zeros(batch, dtype=torch.int32, device=A.device)
+    _lib.check(_lib.lib().nmb_cholesky_root(
+        _lib.dtype_code(A.dtype), n, batch, _lib.ptr(L), C.c_int64(n), C.c_int64(n * n), _lib.ptr(Linv), C.c_int64(n),
+        C.c_int64(n * n), C.c_void_p(info.data_ptr()), _lib.stream_ptr()), "nmb_cholesky_root")
+    return L.reshape(A.shape), (Linv.reshape(A.shape) if inverse else None), info
+
+
+def _psd_safe_cholesky(A: Tensor):
+    """GPyTorch's jitter rule (linear_operator psd_safe_cholesky) around ``nmb_cholesky_root``.
+    Returns ``(L, L^-1)``."""
+    L, Linv, info = cholesky_root(A)
     if not bool(info.any()):
-        return L
+        return L, Linv
     jitter = 1e-6 if A.dtype == torch.float32 else 1e-8
     prev = 0.0
     Ap = A.clone()
@@ -62,9 +77,9 @@ def _psd_safe_cholesky(A: Tensor) -> Tensor:
         new = jitter * 10**i
         Ap.diagonal().add_(new - prev)
         prev = new
-        L, info = torch.linalg.cholesky_ex(Ap)
+        L, Linv, info = cholesky_root(Ap)
         if not bool(info.any()):
-            return L
+            return L, Linv
     raise RuntimeError("Matrix not positive definite after repeatedly adding jitter")
 
 
@@ -88,13 +103,11 @@ class SurrogateGP:
         self.noise = float(noise)
         self.mean_const = float(mean_const)
         Khat = kernel_matrix(self.train_X, self.train_X, kernel, self.lengthscale, self.outputscale, self.noise)
-        self.L = _psd_safe_cholesky(Khat)
+        self.L, self.Linv = _psd_safe_cholesky(Khat)
         resid = (self.train_Y - self.mean_const).unsqueeze(-1)
-        self.alpha = torch.cholesky_solve(resid, self.L).squeeze(-1).contiguous()
-        eye = torch.eye(n, dtype=dtype, device=dev)
-        self.Linv = torch.linalg.solve_triangular(self.L, eye, upper=False).contiguous()
         # GPyTorch multiplies by the explicit inverse root (k R, R = L^-T): whiten the same way
         self.beta = (self.Linv @ resid).squeeze(-1).contiguous()
+        self.alpha = (self.Linv.T @ self.beta.unsqueeze(-1)).squeeze(-1).contiguous()
 
     # ---- views
     @property
@@ -185,7 +198,7 @@ def draw_thompson_path(gp: SurrogateGP, n_paths: int = 1, num_features: int = 10
     phi = scale * torch.cat([z.sin(), z.cos()], dim=-1)                  # [n, M]
     prior_at_train = gp.mean_const + (phi @ w.T).T                       # [S, n]
     resid = gp.train_Y.unsqueeze(0) - (prior_at_train + eps)
-    v = torch.cholesky_solve(resid.T.contiguous(), gp.L).T.contiguous()  # [S, n]
+    v = ((resid @ gp.Linv.T) @ gp.Linv).contiguous()                      # [S, n] = (K + s2 I)^-1 resid, row-wise
     ls = gp.lengthscale if gp.ard else gp.lengthscale[:1]
     return ThompsonPath(W, w, v, gp.train_X, ls, kernel=gp.kernel, outputscale=gp.outputscale,
                         mean_const=gp.mean_const)
