@@ -295,7 +295,12 @@ __global__ void __launch_bounds__(256) level_fwd_kernel(GpDev<T> g, const __grid
     const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
     const int NL = tr.n_levels;
     const bool leaf = (s == NL - 1);
-    for (long long i = warp0; i < tr.cnt[s]; i += nwarps) {
+    // restart-major order inside the level: the nodes of one restart's subtree run on neighbouring warps, so the
+    // ancestors' n-vectors (shared by up to hundreds of nodes) are L2 hits; the s dots are accumulated together
+    // from one pass over the node's own vector (independent load streams instead of s dependent reductions).
+    const long long n_r = tr.cnt[0], per = tr.cnt[s] / n_r;
+    for (long long item = warp0; item < tr.cnt[s]; item += nwarps) {
+        const long long i = (item % per) * n_r + item / per;
         const long long node = tr.off[s] + i;
         const T* ux = st.U + (size_t)node * g.ldu;
         T w[NMB_MAX_LEVELS];
@@ -307,12 +312,23 @@ __global__ void __launch_bounds__(256) level_fwd_kernel(GpDev<T> g, const __grid
             const T zb = ((const T*)tr.base[s - 1])[i / tr.cnt[s - 1]];
             bown = tr.obs_noise ? zb : st.sig[par] * zb / st.cst[par];
         }
+        T dots[NMB_MAX_LEVELS];
+        for (int t0 = 0; t0 < s; t0 += 4) {
+            T d4[4] = {T(0), T(0), T(0), T(0)};
+            const T* uz[4];
+#pragma unroll
+            for (int b = 0; b < 4; ++b) uz[b] = st.U + (size_t)(tr.off[min(t0 + b, s - 1)] + i % tr.cnt[min(t0 + b, s - 1)]) * g.ldu;
+            for (int k = lane; k < g.n; k += 32) {
+                const T x = ux[k];
+#pragma unroll
+                for (int b = 0; b < 4; ++b) d4[b] = fma(x, uz[b][k], d4[b]);
+            }
+#pragma unroll
+            for (int b = 0; b < 4; ++b) if (t0 + b < s) dots[t0 + b] = warp_sum(d4[b]);
+        }
         for (int t = 0; t < s; ++t) {
             const long long anc = tr.off[t] + i % tr.cnt[t];
-            const T* uz = st.U + (size_t)anc * g.ldu;
-            T dot = T(0);
-            for (int k = lane; k < g.n; k += 32) dot = fma(ux[k], uz[k], dot);
-            dot = warp_sum(dot);
+            const T dot = dots[t];
             T ga[DMAX];
             const T kx = kern_pair<T, DMAX>(g, st.pts + node * g.d, st.pts + anc * g.d, ga);
             T acc = kx - dot;
@@ -612,7 +628,7 @@ static int launch_whiten_mma_d(const nmb_gp_t* gp, bool bwd, const double* pts, 
     int R = 0, nst = 0;
     size_t smem = 0;
     for (int i = 0; i < 5 && !R; ++i) {
-        smem = wh_mma_bytes<DM>(gp->ldl, cand[i][0], cand[i][1]);
+        smem = wh_mma_bytes<DM>(gp->ldl, cand[i][0], cand[i][1], bwd);
         if (smem <= 227 * 1024) { R = cand[i][0]; nst = cand[i][1]; }
     }
     NMB_REQUIRE(R > 0, NMB_ELIMIT, "gp whiten: n=%d training points exceed shared memory", gp->n);

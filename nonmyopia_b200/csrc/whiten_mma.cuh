@@ -20,23 +20,28 @@ namespace nmb {
 
 __host__ __device__ inline int wh_ks(int ldl) { return (ldl + 15) / 16 * 16 + 4; }
 
+// per consumer warp (backward only): its 32 training points of the current column block, scaled, + their alpha
+template <int DMAX> __host__ __device__ constexpr int wh_tp_elems() { return 32 * (DMAX + 1); }
+
 template <int DMAX>
-inline size_t wh_mma_bytes(int ldl, int R, int nst) {
-    return ((size_t)nst * kStageElems + (size_t)R * wh_ks(ldl) + (size_t)R * DMAX + (size_t)2 * R * DMAX + 2 * nst) * 8;
+inline size_t wh_mma_bytes(int ldl, int R, int nst, bool bwd) {
+    const size_t tp = bwd ? (size_t)(R / 8) * 2 * wh_tp_elems<DMAX>() : 0;
+    return ((size_t)nst * kStageElems + (size_t)R * wh_ks(ldl) + (size_t)R * DMAX + (size_t)2 * R * DMAX + tp + 2 * nst) * 8;
 }
 
 struct WhSmem {
-    double *stage, *A, *xs, *red;
+    double *stage, *A, *xs, *red, *tp;
     unsigned full0, empty0;
     int KS;
     template <int DMAX>
-    __device__ void carve(double* base, int ldl, int R, int nst) {
+    __device__ void carve(double* base, int ldl, int R, int nst, bool bwd = false) {
         KS = wh_ks(ldl);
         double* p = base;
         stage = p; p += (size_t)nst * kStageElems;
         A = p; p += (size_t)R * KS;
         xs = p; p += R * DMAX;
         red = p; p += 2 * R * DMAX;
+        tp = p; p += bwd ? (R / 8) * 2 * wh_tp_elems<DMAX>() : 0;
         full0 = smem_u32(p);
         empty0 = full0 + 8 * nst;
     }
@@ -180,7 +185,7 @@ __global__ void __launch_bounds__(288, 1) whiten_bwd_mma_kernel(GpDev<double> g,
     const int n = g.n, d = g.d, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int ncw = (R >> 3) * 2, nthr = ncw * 32;
     WhSmem sm;
-    sm.carve<DMAX>(reinterpret_cast<double*>(wh_smem_raw), ldl, R, NST);
+    sm.carve<DMAX>(reinterpret_cast<double*>(wh_smem_raw), ldl, R, NST, true);
     wh_init_barriers(sm, NST, ncw);
     const MmaRing ring{sm.stage, sm.full0, sm.empty0, sm.KS};
     if (warp == ncw) {
@@ -207,23 +212,39 @@ __global__ void __launch_bounds__(288, 1) whiten_bwd_mma_kernel(GpDev<double> g,
     double xr[DMAX], gx[DMAX];
 #pragma unroll
     for (int k = 0; k < DMAX; ++k) { xr[k] = sm.xs[row * DMAX + k]; gx[k] = 0.0; }
+    double ils[DMAX];
+#pragma unroll
+    for (int k = 0; k < DMAX; ++k) ils[k] = k < d ? __ldg(g.inv_ls + k) : 0.0;
+    double* tp = sm.tp + (size_t)warp * wh_tp_elems<DMAX>();
     for (int cb = 0; cb < n; cb += kOB) {
         double acc[4][2];
         zero_acc4(acc);
         w.active = cb + w.col0 < n;
+        // this warp's 32 training points of the block (one per lane), fetched under the GEMM and parked in shared
+        // memory for the epilogue (per-column global loads inside the epilogue were 19 % of the stall samples)
+        const int cpt = cb + w.col0 + lane;
+        double tjr[DMAX], alr = 0.0;
+#pragma unroll
+        for (int k = 0; k < DMAX; ++k) tjr[k] = (cpt < n && k < d) ? __ldg(g.train_x + (size_t)cpt * d + k) * ils[k] : 0.0;
+        if (cpt < n) alr = __ldg(g.alpha + cpt);
         // g_K[r][j] = sum_{i >= j} gU[r][i] Linv[i][j]: rows i >= cb of Linv, columns cb..cb+63
         mma_gemm<NST>(ring, w, sm.A + cb, ldl - cb, acc);
+        __syncwarp();
+#pragma unroll
+        for (int k = 0; k < DMAX; ++k) tp[lane * DMAX + k] = tjr[k];
+        tp[32 * DMAX + lane] = alr;
+        __syncwarp();
 #pragma unroll
         for (int t = 0; t < 4; ++t) {
 #pragma unroll
             for (int e = 0; e < 2; ++e) {
-                const int c = cb + w.col0 + 8 * t + 2 * w.fk + e;
-                if (c < n) {
-                    const double al = __ldg(g.alpha + c);
+                const int cl = 8 * t + 2 * w.fk + e;
+                if (cb + w.col0 + cl < n) {
+                    const double al = tp[32 * DMAX + cl];
                     double sd[DMAX], r2 = 0.0;
 #pragma unroll
                     for (int k = 0; k < DMAX; ++k) {
-                        sd[k] = k < d ? xr[k] - __ldg(g.train_x + (size_t)c * d + k) * __ldg(g.inv_ls + k) : 0.0;
+                        sd[k] = xr[k] - tp[cl * DMAX + k];
                         r2 = fma(sd[k], sd[k], r2);
                     }
                     double kap, gc;

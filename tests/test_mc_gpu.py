@@ -52,8 +52,10 @@ def test_whiten_matches_oracle():
     assert H.rel_err(m0, m0_ref, atol=1e-3) < 1e-8
     assert H.rel_err(q, (u_ref * u_ref).sum(-1), atol=1e-3) < 1e-8
     gx = torch.zeros(P, d, dtype=F64, device="cuda")
-    _lib.check(lib.nmb_gp_whiten_bwd(C.byref(g), 0, _lib.ptr(xc), C.c_int64(P), _lib.ptr(gU.cuda()), _lib.ptr(gm.cuda()),
+    gUc, gmc = gU.cuda(), gm.cuda()            # held: a temporary's block could be reused before the kernel runs
+    _lib.check(lib.nmb_gp_whiten_bwd(C.byref(g), 0, _lib.ptr(xc), C.c_int64(P), _lib.ptr(gUc), _lib.ptr(gmc),
                                      _lib.ptr(gx), _lib.stream_ptr()))
+    torch.cuda.synchronize()
     assert H.rel_err(gx, gx_ref, atol=1e-2) < 1e-8
 
 
