@@ -54,7 +54,10 @@ __device__ __forceinline__ void bulk_g2s(unsigned dst, const void* src, unsigned
 }
 __device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
 // barrier over the consumer warps only (id 1); the producer warp never joins it
-__device__ __forceinline__ void consumer_sync(int nthr) { asm volatile("bar.sync 1, %0;" ::"r"(nthr) : "memory"); }
+// (id 1 by default; the forward rollout runs two row groups per CTA on ids 1 and 2)
+__device__ __forceinline__ void consumer_sync(int nthr, int bar = 1) {
+    asm volatile("bar.sync %1, %0;" ::"r"(nthr), "r"(bar) : "memory");
+}
 
 __device__ __forceinline__ void dmma884(double (&c)[2], double a, double b) {
     asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
@@ -87,6 +90,24 @@ struct MmaSmem {
         OUT = p; p += d * rows;
         cost_acc = p; p += rows;
         full0 = smem_u32(p);
+        empty0 = full0 + 8 * kStages;
+    }
+    // Row group [row_off, row_off + rows_g) of a CTA of rows_total rows: the groups' buffers lie one after the other
+    // behind the shared weight ring, the mbarriers behind the last group (same footprint as carve(rows_total)).
+    __device__ void carve_group(double* base, int d, int H, int rows_total, int row_off, int rows_g) {
+        rows = rows_g;
+        KS = H + 4;
+        const int per_row = 4 * KS + 2 * d + 2;
+        stage = base;
+        double* p = base + kStages * kStageElems + (size_t)row_off * per_row;
+        B0 = p; p += rows * KS;
+        B1 = p; p += rows * KS;
+        HA = p; p += rows * KS;
+        HB = p; p += rows * KS;
+        IN = p; p += (d + 1) * rows;
+        OUT = p; p += d * rows;
+        cost_acc = p;
+        full0 = smem_u32(base + kStages * kStageElems + (size_t)rows_total * per_row);
         empty0 = full0 + 8 * kStages;
     }
     static size_t bytes(int d, int H, int rows) {
@@ -179,6 +200,7 @@ __device__ __forceinline__ void mma_producer(const PolicyLayout& lay, const doub
 // Consumer-side state of one warp
 struct MmaWarp {
     int lane, row0, col0, nthr;
+    int tid, bar;          // thread index inside the consumer group and the group's named barrier
     bool active;           // this warp's 32 columns intersect [0, H)
     unsigned chunk;        // running chunk counter (same order as the producer)
     int fr, fk;            // fragment coordinates: lane >> 2, lane & 3
@@ -189,6 +211,8 @@ struct MmaWarp {
         nthr = nthr_;
         active = col0 < H;
         chunk = 0;
+        tid = threadIdx.x;
+        bar = 1;
         fr = lane >> 2;
         fk = lane & 3;
     }
@@ -236,7 +260,7 @@ __device__ __forceinline__ void mma_policy_forward(const PolicyLayout& lay, cons
                                                    const SaveAreas<double>* save, long long node0, int nvalid,
                                                    double* __restrict__ hs_out) {
     const int d = lay.d, H = lay.H, rows = sm.rows, KS = sm.KS;
-    const int tid = threadIdx.x, nthr = w.nthr;
+    const int tid = w.tid, nthr = w.nthr;
     const MmaRing ring = sm.ring();
     // ---- embedding (K = d+1): B0 = elu(We [x;y] + be)
     {
@@ -257,7 +281,7 @@ __device__ __forceinline__ void mma_policy_forward(const PolicyLayout& lay, cons
             }
         }
     }
-    consumer_sync(nthr);
+    consumer_sync(nthr, w.bar);
     const int row = w.row0 + w.fr;
     const bool rv = row < nvalid;
     const size_t nrow = (size_t)(node0 + row) * H;
@@ -275,7 +299,7 @@ __device__ __forceinline__ void mma_policy_forward(const PolicyLayout& lay, cons
             if (save && rv) *reinterpret_cast<double2*>(save->P + nrow + o) = v;
         }
     }
-    consumer_sync(nthr);
+    consumer_sync(nthr, w.bar);
     // ---- GRU cell (gates r, z, n of the same (row, col) stay in registers)
     {
         double rg[4][2], zg[4][2], gh[4][2];
@@ -328,7 +352,7 @@ __device__ __forceinline__ void mma_policy_forward(const PolicyLayout& lay, cons
             }
         }
     }
-    consumer_sync(nthr);
+    consumer_sync(nthr, w.bar);
     // ---- post MLP layer 0: B0 = u1 = elu(W0 [p; h'] + b0)
     const int sB0 = head_a ? S_AB0 : S_XB0, sB3 = head_a ? S_AB3 : S_XB3;
     const int sW6 = head_a ? S_AW6 : S_XW6, sB6 = head_a ? S_AB6 : S_XB6;
@@ -345,7 +369,7 @@ __device__ __forceinline__ void mma_policy_forward(const PolicyLayout& lay, cons
             if (save && rv) *reinterpret_cast<double2*>(save->U1 + nrow + o) = v;
         }
     }
-    consumer_sync(nthr);
+    consumer_sync(nthr, w.bar);
     // ---- layer 3: u2 = elu(W3 u1 + b3) -> hprev buffer (dead)
     zero_acc4(acc);
     mma_gemm<kStages>(ring, w, sm.B0, H, acc);
@@ -359,7 +383,7 @@ __device__ __forceinline__ void mma_policy_forward(const PolicyLayout& lay, cons
             if (save && rv) *reinterpret_cast<double2*>(save->U2 + nrow + o) = v;
         }
     }
-    consumer_sync(nthr);
+    consumer_sync(nthr, w.bar);
     // ---- output layer (O = d): out = sigmoid(W6 u2 + b6); 4 threads per output, 2 interleaved chains each
     {
         const double* Wt = theta_t + lay.off[sW6];       // [H][d]
@@ -384,7 +408,7 @@ __device__ __forceinline__ void mma_policy_forward(const PolicyLayout& lay, cons
             }
         }
     }
-    consumer_sync(nthr);
+    consumer_sync(nthr, w.bar);
 }
 
 // ================================================================== backward step

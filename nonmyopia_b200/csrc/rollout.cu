@@ -207,34 +207,43 @@ __global__ void __launch_bounds__(kNT, 1) ts_rollout_fwd_kernel(ProblemDev<T> pb
 // rows (multiple of 8, <= 56) chains per CTA; rows/4 consumer warps + 1 producer warp (policy_mma.cuh).
 template <int DMAX>
 __global__ void __launch_bounds__(kMaxRowsMma * 8 + 32, 1)
-    ts_rollout_fwd_mma_kernel(ProblemDev<double> pb, RolloutDev<double> ro0, RolloutDev<double> ro1, int rows) {
+    ts_rollout_fwd_mma_kernel(ProblemDev<double> pb, RolloutDev<double> ro0, RolloutDev<double> ro1, int rows_cta) {
     using T = double;
     if (pb.done_flag && *pb.done_flag) return;
     const RolloutDev<T>& ro = blockIdx.y == 0 ? ro0 : ro1;
     const int d = pb.d, H = pb.H, L = pb.L;
     const long long N = pb.N;
-    const long long chain0 = (long long)blockIdx.x * rows;
-    const int nvalid = (int)min((long long)rows, N - chain0);
-    const int tid = threadIdx.x;
-    const int ncw = rows >> 2, nthr = ncw * 32;
+    const int ncw_all = rows_cta >> 2, nthr_all = ncw_all * 32;
     const long long step = pb.step_ptr ? *pb.step_ptr : 0;
+    // Two independent row groups per CTA (e.g. 56 rows = 32 + 24) walk the same layer sequence on their own named
+    // barrier and shared-memory buffers but consume ONE weight ring: they drift apart by up to the ring depth, so one
+    // group's GEMM fills the FP64 pipe while the other sits in an activation epilogue, a barrier or the path phase.
+    const int rowsA = ((rows_cta >> 3) + 1) / 2 * 8;
+    const int grp = (int)threadIdx.x >= rowsA * 8 ? 1 : 0;
+    const int rows = grp ? rows_cta - rowsA : rowsA;               // rows, threads, first chain of THIS group
+    const int tid = (int)threadIdx.x - (grp ? rowsA * 8 : 0);
+    const int nthr = rows * 8;
+    const long long chain0 = (long long)blockIdx.x * rows_cta + (grp ? rowsA : 0);
+    const int nvalid = (int)max(0LL, min((long long)rows, N - chain0));
 
     MmaSmem sm;
-    sm.carve(reinterpret_cast<T*>(nmb_smem_raw), d, H, rows);
-    if (tid == 0) {
+    sm.carve_group(reinterpret_cast<T*>(nmb_smem_raw), d, H, rows_cta, grp ? rowsA : 0, rows);
+    if (threadIdx.x == 0) {
         for (int s = 0; s < kStages; ++s) {
             mbar_init(sm.full0 + 8 * s, 1);
-            mbar_init(sm.empty0 + 8 * s, ncw);
+            mbar_init(sm.empty0 + 8 * s, ncw_all);
         }
         fence_barrier_init();
     }
     __syncthreads();
-    if (tid >= nthr) {      // producer warp
+    if ((int)threadIdx.x >= nthr_all) {      // producer warp
         mma_producer<kStages, false>(pb.lay, ro.theta_t, L, sm.ring());
         return;
     }
     MmaWarp w;
     w.init(tid >> 5, nthr, H);
+    w.tid = tid;
+    w.bar = 1 + grp;
     const int KS = sm.KS;
 
     // ---- load the tile's inputs
@@ -251,7 +260,7 @@ __global__ void __launch_bounds__(kMaxRowsMma * 8 + 32, 1)
         if (ro.has_save && r < nvalid) ro.sv.HS[(chain0 + r) * H + k] = v;
     }
     if (tid < rows) sm.cost_acc[tid] = T(0);
-    consumer_sync(nthr);
+    consumer_sync(nthr, w.bar);
 
     const SaveAreas<T>* sv = ro.has_save ? &ro.sv : nullptr;
     for (int l = 0; l <= L; ++l) {
@@ -301,7 +310,7 @@ __global__ void __launch_bounds__(kMaxRowsMma * 8 + 32, 1)
             for (int k = 0; k < DMAX; ++k) gp[k] = group_sum(gp[k], 8);
         }
         const T yv = yp + pb.path.mean_const;
-        consumer_sync(nthr);     // every thread has read sm.IN / sm.OUT of this step
+        consumer_sync(nthr, w.bar);     // every thread has read sm.IN / sm.OUT of this step
         if (live && lane == 0) {
             T dir[DMAX];
             const T dist = move_dist<T, DMAX>(pb.cost, d, pt, xin, dir);
@@ -332,7 +341,7 @@ __global__ void __launch_bounds__(kMaxRowsMma * 8 + 32, 1)
             for (int k = 0; k < DMAX; ++k) if (k < d) sm.IN[k * rows + r] = pt[k];
             sm.IN[d * rows + r] = yv;
         }
-        consumer_sync(nthr);
+        consumer_sync(nthr, w.bar);
     }
 }
 
