@@ -285,7 +285,9 @@ def run_b200(args, rank, world, local_rank):
         flops = kern[dom]["flops"]
         ach = flops / (kern[dom]["ms"] * 1e-3) / 1e12
         roof = {"bound": "fp64", "kernel": dom, "achieved": ach, "peak": fp64_peak, "unit": "TFLOP/s",
-                "frac": ach / fp64_peak, "traffic": None,
+                "frac": ach / fp64_peak, "traffic": ncu_dram_traffic(dom),
+                "traffic_note": "DRAM read + write bytes per launch from profiles/ncu_full_r01_rollout_wgrad.csv (the backward "
+                                "workspace, not algorithmic bytes: the kernel is FP64-pipe bound)",
                 "peak_source": "own-measured FP64 DFMA peak on this pool's B200 (profiles/pipe_peaks_r01.json); "
                                "MEASURED_PEAKS.json has no FP64 entry",
                 "per_kernel_ms": {k: round(v["ms"], 4) for k, v in kern.items()}}
@@ -323,6 +325,24 @@ def run_b200(args, rank, world, local_rank):
     }
     print(json.dumps(line), flush=True)
     _finish(world)
+
+
+def ncu_dram_traffic(kernel_substr):
+    """DRAM bytes per launch (read + write) of the named kernel from the committed `ncu --set full` capture
+    (profiles/ncu_full_r01_rollout_wgrad.csv, raw page); None when the file or the kernel is missing."""
+    import csv
+    path = os.path.join(ROOT, "profiles", "ncu_full_r01_rollout_wgrad.csv")
+    scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    try:
+        rows = list(csv.reader(open(path)))
+        hdr, units = rows[0], rows[1]
+        kn, ir, iw = hdr.index("Kernel Name"), hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
+        for r in rows[2:]:
+            if kernel_substr in r[kn]:
+                return float(r[ir]) * scale[units[ir]] + float(r[iw]) * scale[units[iw]]
+    except Exception:
+        pass
+    return None
 
 
 def _finish(world):

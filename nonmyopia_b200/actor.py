@@ -176,17 +176,19 @@ class Actor:
         L, d, n = self.algo_lookahead_steps, p.x_dim, p.n_restarts
         dev, dt = p.device, p.torch_dtype
         prev_h = buffer["h"][-1:].clone().expand(n, -1)
-        opt = torch.optim.AdamW(self._parameters, lr=0.01)
+        opt = torch.optim.AdamW(self._parameters, lr=0.01, capturable=True)
         tree = self._random_tree(prev_X[0:1], nf, n)
         target = torch.stack([torch.clamp(x.to(device=dev, dtype=dt).reshape(-1, d), min=0.01, max=0.99)
                               for x in tree], dim=0).detach()
         self.hidden_noise = torch.randn(n, p.hidden_dim).to(target[-1])
         prev_h = prev_h + self.hidden_noise
         gp = self.acqf.gp()
-        stall, best = 0, float("inf")
-        for ep in range(300):
-            outs, h = [], prev_h
-            x, y = prev_X[0].expand(n, d), prev_y[0].expand(n, p.y_dim)
+        x0, y0 = prev_X[0].expand(n, d), prev_y[0].expand(n, p.y_dim)
+
+        def epoch():
+            """One imitation epoch, device work only: rollout of the network on draws of the surrogate, L1 loss to
+            the random ball designs, backward, AdamW."""
+            outs, h, x, y = [], prev_h, x0, y0
             for j in range(L):
                 x, h = self.maps(x, y, h, return_actions=False, enable_noise=False)
                 outs.append(x)
@@ -194,17 +196,53 @@ class Actor:
             a, h = self.maps(x, y, h, return_actions=True, enable_noise=False)
             outs.append(a)
             loss = torch.mean(abs(target - torch.stack(outs, dim=0)))
-            if ep % 10 == 0:
-                print("Loss:", loss.item())
-            if loss < best:
-                best, stall = loss, 0
-            else:
-                stall += 1
             loss.backward()
             opt.step()
-            opt.zero_grad()
+            return loss.detach()
+
+        # The epoch is ~300 small launches: after three eager epochs (they count) it is captured once and replayed
+        # as a CUDA graph; the host reads the loss every epoch for the reference's early-stop rule (actor.py:200-216).
+        graph, static_loss, side = None, None, torch.cuda.Stream(device=target.device)
+        stall, best = 0, float("inf")
+        for ep in range(300):
+            if graph is None and ep == 3 and self.rng_mode != "host":
+                try:
+                    opt.zero_grad(set_to_none=True)
+                    torch.cuda.synchronize()
+                    g = torch.cuda.CUDAGraph()
+                    with torch.cuda.graph(g, stream=side):
+                        static_loss = epoch()
+                    graph = g
+                    graph.replay()              # capture only records: this replay is epoch 3
+                    loss = static_loss
+                except Exception as e:          # capture unsupported for some op: keep the eager epochs
+                    print("pre-training runs eagerly (graph capture failed: %s)" % type(e).__name__)
+                    torch.cuda.synchronize()
+                    graph, static_loss = False, None
+                    opt.zero_grad(set_to_none=True)
+                    loss = epoch()
+            elif graph:
+                graph.replay()
+                loss = static_loss
+            elif ep < 3 and self.rng_mode != "host":
+                side.wait_stream(torch.cuda.current_stream())
+                with torch.cuda.stream(side):
+                    opt.zero_grad(set_to_none=True)
+                    loss = epoch()
+                torch.cuda.current_stream().wait_stream(side)
+            else:
+                opt.zero_grad(set_to_none=True)
+                loss = epoch()
+            loss_v = float(loss)
+            if ep % 10 == 0:
+                print("Loss:", loss_v)
+            if loss_v < best:
+                best, stall = loss_v, 0
+            else:
+                stall += 1
             if stall >= 50:
                 break
+        torch.cuda.current_stream().wait_stream(side)
 
     # ------------------------------------------------------------------ query
     def query(self, buffer, iteration: int, embedder=None, f_posterior=None, save_trajectory=True):
