@@ -314,8 +314,9 @@ def run_b200(args, rank, world, local_rank):
         "e2e": {"value": nodes_per_step * world * e2e["steps"] / (e2e_ms * 1e-3), "unit": UNIT,
                 "h2d_bytes_per_step": e2e["h2d"], "d2h_bytes_per_step": e2e["d2h"], "ms_per_step": e2e_ms / e2e["steps"],
                 "api": "TSAMLoop.step_host - the per-iteration engine of Actor.query (HES-TS-AM): per-step H2D of "
-                       "prev_X/prev_y/prev_hid_state from pinned memory, one iteration (same launches as `value`), "
-                       "D2H of the per-restart loss/cost, stream synchronise",
+                       "prev_X/prev_y/prev_hid_state from pinned memory (each step's copy is issued on a side stream "
+                       "during the previous step's kernels, two input-buffer sets), one iteration (same launches as "
+                       "`value`), D2H of the per-restart loss/cost, stream synchronise",
                 "class_api_eager": {
                     "value": nodes_per_step * world * e2e_api["steps"] / (api_ms * 1e-3), "unit": UNIT,
                     "ms_per_step": api_ms / e2e_api["steps"],
@@ -395,13 +396,14 @@ def run_e2e_loop(args, loop, prev_x, prev_y, prev_h, stream, barrier):
     hx, hy, hh = prev_x.pin_memory(), prev_y.pin_memory(), prev_h.pin_memory()
     N = hx.shape[0]
     out_host = torch.empty(2, N, dtype=torch.float64).pin_memory()
+    nxt = (hx, hy, hh)                      # inputs of the following step: copied under this step's kernels
     for _ in range(3):
-        loop.step_host(hx, hy, hh, out_host)
+        loop.step_host(hx, hy, hh, out_host, next_inputs=nxt)
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(stream)
     for _ in range(args.steps):
-        loop.step_host(hx, hy, hh, out_host)
+        loop.step_host(hx, hy, hh, out_host, next_inputs=nxt)
     e1.record(stream)
     barrier()
     assert torch.isfinite(out_host).all()

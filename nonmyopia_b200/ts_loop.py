@@ -58,6 +58,8 @@ class TSAMLoop:
         self.prev = (prev_x.to(dev, dt).contiguous(), prev_y.reshape(-1).to(dev, dt).contiguous(),
                      prev_h.to(dev, dt).contiguous())
         self.prob = eng.problem(*self.prev, prev_cost=prev_cost)
+        self._prev_cost = prev_cost
+        self._alt = None          # second input buffer set + graph (step_host with prefetch)
         self.main = te.RolloutBuffers(d, H, L, N, dt, dev, with_save=True)
         self.orig = te.RolloutBuffers(d, H, L, N, dt, dev, with_save=False)
         z = lambda *s: torch.zeros(*s, dtype=dt, device=dev)
@@ -220,23 +222,65 @@ class TSAMLoop:
                 break
         return self.read_state()
 
-    def step_host(self, host_x: Tensor, host_y: Tensor, host_h: Tensor, host_out: Tensor) -> None:
+    def _enable_alt_inputs(self) -> None:
+        """Second set of input buffers with its own captured graph, so the host can copy the NEXT step's inputs
+        (side stream) while this step computes."""
+        if self._alt is not None:
+            return
+        if self.graph is None:
+            self.capture()
+        prev2 = tuple(torch.empty_like(t) for t in self.prev)
+        prob2 = self.eng.problem(*prev2, prev_cost=self._prev_cost)
+        self.eng._keep = self.prev                      # the engine keeps the primary set alive; prev2 is kept here
+        prob1, self.prob = self.prob, prob2
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            self._iteration()
+        self.prob = prob1
+        self._alt = dict(prev=prev2, prob=prob2, graph=g, side=torch.cuda.Stream(device=self.state.device),
+                         ready=torch.cuda.Event(), which=0, staged=False)
+
+    def step_host(self, host_x: Tensor, host_y: Tensor, host_h: Tensor, host_out: Tensor, next_inputs=None) -> None:
         """One Adam iteration driven from HOST buffers (the reference reads loss / cost on the host every
         iteration, actor.py:580-581,618-619): pinned ``prev_X / prev_y / prev_hid_state`` -> HBM, one graph
         replay (or eager launch sequence), this iteration's per-restart loss and cost -> pinned ``host_out[2, N]``,
         then a stream synchronise.  The graph reads the inputs through fixed device buffers, so the copies
-        land in place."""
-        px, py, ph = self.prev
-        px.copy_(host_x.view_as(px), non_blocking=True)
-        py.copy_(host_y.view_as(py), non_blocking=True)
-        ph.copy_(host_h.view_as(ph), non_blocking=True)
+        land in place.  ``next_inputs = (host_x, host_y, host_h)`` of the FOLLOWING call may be passed: they are copied
+        on a side stream into the other input-buffer set while this iteration runs (every step's copy still happens,
+        it just no longer sits in front of the kernels)."""
+        main = torch.cuda.current_stream()
+        alt = self._alt
+        if next_inputs is not None and alt is None and self.graph is not None:
+            self._enable_alt_inputs()
+            alt = self._alt
+        if alt is not None and alt["staged"]:
+            main.wait_event(alt["ready"])               # this step's inputs were prefetched into set `which`
+            which = alt["which"]
+        else:
+            which = alt["which"] if alt is not None else 0
+            px, py, ph = self.prev if which == 0 else alt["prev"]
+            px.copy_(host_x.view_as(px), non_blocking=True)
+            py.copy_(host_y.view_as(py), non_blocking=True)
+            ph.copy_(host_h.view_as(ph), non_blocking=True)
         if self.graph is not None:
-            self.graph.replay()
+            (self.graph if which == 0 else alt["graph"]).replay()
         else:
             self._iteration()
+        if alt is not None:
+            alt["staged"] = False
+            if next_inputs is not None:
+                # the other set was last read by the previous call, which ended with a synchronise
+                nx, ny, nh = next_inputs
+                dx, dy, dh = alt["prev"] if which == 0 else self.prev
+                with torch.cuda.stream(alt["side"]):
+                    dx.copy_(nx.view_as(dx), non_blocking=True)
+                    dy.copy_(ny.view_as(dy), non_blocking=True)
+                    dh.copy_(nh.view_as(dh), non_blocking=True)
+                    alt["ready"].record(alt["side"])
+                alt["which"], alt["staged"] = 1 - which, True
         host_out[0].copy_(self.main.loss, non_blocking=True)
         host_out[1].copy_(self.main.cost, non_blocking=True)
-        torch.cuda.current_stream().synchronize()
+        main.synchronize()
 
     # ------------------------------------------------------------------ results (actor.py:661-733)
     def result(self):
