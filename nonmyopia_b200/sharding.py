@@ -135,51 +135,88 @@ def broadcast_from_owner(t: Optional[Tensor], shape, dtype, device, owner: int, 
 def free_restart_loop(objective: Callable[[List[Tensor]], Dict], params: List[Tensor],
                       opt_step: Callable[[Sequence[Optional[Tensor]]], None], *, budget: float, n_iter: int,
                       past_initial: bool, n_global: Optional[int] = None, group=None, save_trajectory: bool = False,
-                      log: Optional[Callable[[str], None]] = print) -> Dict:
+                      log: Optional[Callable[[str], None]] = print, use_graph: bool = False) -> Dict:
     """The reference's AdamW loop for free-parameter algorithms (actor.py:558-656; HES-TS, HES-MC, qEI ... qKG)
     over this rank's restarts.
 
     ``objective(local_maps)`` evaluates ``acqf.forward`` on ``[sigmoid(p) for p in params]`` and returns the
     reference's dict (``acqf_loss`` / ``acqf_cost`` per local restart, ``X``, ``actions``); ``opt_step(grads)``
     applies AdamW (a ``None`` gradient leaves its tensor untouched, actor.py:641-648).  With a process group
-    the decision values are MIN-reduced and the backward is seeded with ``1 / n_global``."""
-    n_local = None
+    the decision values are MIN-reduced and the backward is seeded with ``1 / n_global``.
+
+    ``use_graph`` (CUDA only): after two eager iterations the device work of one iteration - sigmoid, objective,
+    backward, AdamW, the two decision minima - is captured once and replayed as a CUDA graph; the host still reads
+    the minima every iteration for the reference's snapshot / early-stop rule (one synchronisation per iteration
+    instead of ~100 eager launches).  Requires an objective without per-call host randomness."""
     best = dict(loss=None, cost=None, KL=0)
     best_min = float("inf")
     snap, stall = {}, 0
     saved_trajectory, saved_loss, saved_cost = [], [], []
     n_done = 0
-    for ep in range(n_iter):
+    keep = (lambda t: t.detach().clone()) if use_graph else (lambda t: t.detach())
+
+    def iteration():
         local_maps = [torch.sigmoid(x) for x in params]
-        if save_trajectory:
-            saved_trajectory.append([x.cpu().detach().tolist() for x in local_maps])
         rd = objective(local_maps)
         acqf_loss, acqf_cost = rd["acqf_loss"], rd["acqf_cost"]
-        if n_local is None:
-            n_local = acqf_loss.shape[0]
-            n_global = n_local if n_global is None else int(n_global)
+        loss = acqf_loss + abs(budget - acqf_cost)
+        cand = torch.stack([loss.detach().min(), (acqf_loss + acqf_cost).detach().min()])
+        n_loc = acqf_loss.shape[0]
+        n_glob = n_loc if n_global is None else int(n_global)
+        seed = loss.mean() if n_glob == n_loc else loss.sum() / n_glob
+        opt_step(torch.autograd.grad(seed, params, allow_unused=True))
+        return local_maps, rd, cand
+
+    graph, static, side, warm = None, None, None, 2
+    if use_graph:
+        side = torch.cuda.Stream(device=params[0].device)
+    for ep in range(n_iter):
+        if use_graph and ep >= warm and graph is not False:
+            if graph is None:
+                try:
+                    torch.cuda.synchronize()
+                    g = torch.cuda.CUDAGraph()
+                    with torch.cuda.graph(g, stream=side):
+                        static = iteration()
+                    graph = g
+                except Exception as e:          # an op of this objective cannot be captured: stay eager
+                    if log is not None:
+                        log(f"free-parameter loop runs eagerly (graph capture failed: {type(e).__name__})")
+                    torch.cuda.synchronize()
+                    graph, keep = False, (lambda t: t.detach())
+            if graph:
+                graph.replay()
+                local_maps, rd, cand = static
+            else:
+                local_maps, rd, cand = iteration()
+        elif use_graph:
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                local_maps, rd, cand = iteration()
+            torch.cuda.current_stream().wait_stream(side)
+        else:
+            local_maps, rd, cand = iteration()
+        acqf_loss, acqf_cost = rd["acqf_loss"], rd["acqf_cost"]
         if save_trajectory:
+            saved_trajectory.append([x.cpu().detach().tolist() for x in local_maps])
             saved_loss.append(acqf_loss.tolist())
             saved_cost.append(acqf_cost.tolist())
-        loss = acqf_loss + abs(budget - acqf_cost)
-        chosen = torch.argmin(loss)
-        cand = torch.stack([loss.detach()[chosen], (acqf_loss + acqf_cost).detach().min()])
-        cand = allreduce_min(cand, group).tolist()
+        cand = allreduce_min(cand.clone() if group is not None else cand, group).tolist()
         if ep == 0 or cand[0] < best_min:
-            best = dict(loss=acqf_loss.detach(), cost=acqf_cost.detach(), KL=0)
+            best = dict(loss=keep(acqf_loss), cost=keep(acqf_cost), KL=0)
             best_min = cand[1]
-            snap = dict(X=[x.detach() for x in rd["X"]], actions=rd["actions"].detach())
+            snap = dict(X=[keep(x) for x in rd["X"]], actions=keep(rd["actions"]))
             stall = 0
         elif past_initial or ep >= 200:
             stall += 1
-        seed = loss.mean() if n_global == n_local else loss.sum() / n_global
-        grads = torch.autograd.grad(seed, params, allow_unused=True)
-        opt_step(grads)
         n_done = ep + 1
         if log is not None and ep % 50 == 0:
+            chosen = torch.argmin(acqf_loss + abs(budget - acqf_cost))
             log(f"Epoch {ep:05d}\tLoss {acqf_loss[chosen].item():.5f}\tCost: {acqf_cost[chosen].item():.5f}")
         if stall > 50:
             break
+    if use_graph:
+        torch.cuda.current_stream().wait_stream(side)
     return dict(best_loss=best["loss"], best_cost=best["cost"], best_KL=0, best_next_X=snap["X"],
                 best_actions=snap["actions"], best_hidden_state=None, saved_trajectory=saved_trajectory,
                 saved_loss=saved_loss, saved_cost=saved_cost, n_iter=n_done)

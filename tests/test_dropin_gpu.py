@@ -190,3 +190,38 @@ def test_actor_query_device_rng_runs_and_stops():
     assert out["next_X"].shape == (1, fx["d"]) and bool(((out["next_X"] > 0) & (out["next_X"] < 1)).all())
     assert out["hidden_state"].shape == (1, fx["H"])
     assert torch.isfinite(out["all_losses"]).all()
+
+
+@pytest.mark.parametrize("name", ["ts_free_ackley_L2", "mc_ackley_L1", "mc_hartmann_L3"])
+def test_free_loop_graph_replay_equals_eager(name):
+    """sharding.free_restart_loop: the iteration replayed as one CUDA graph gives bit-identical parameters, snapshots
+    and iteration count to the eager launch sequence (cost noise off: the graph draws its own device numbers)."""
+    from nonmyopia_b200 import acqfs, sharding as sh
+    from nonmyopia_b200.actor import _FlatAdamW
+    fx = H.load(name)
+    ts = fx["kind"] == "ts_free"
+    L, N, d = fx["L"], fx["n_r"], fx["d"]
+    fx = dict(fx, cost=dict(fx["cost"], max_noise=0.0))
+    torch.manual_seed(3)
+    acqf = make_acqf(fx, [1] * L if ts else list(fx["nf"]), ts, n_samples=fx.get("S_a", 64))
+    acqf.dump_model(f=_product_path(fx) if ts else None)
+    prev_X, prev_y = fx["prev_X"].cuda(), fx["prev_y"].cuda()
+    prev_h = torch.zeros(N, 4, dtype=F64, device="cuda")
+    outs = []
+    for use_graph in (False, True):
+        params = [l.clone().cuda().requires_grad_(True) for l in fx["logits"]]
+        opt = _FlatAdamW(params, lr=1e-2)
+        objective = lambda maps: acqf.forward(prev_X=prev_X, prev_y=prev_y, prev_hid_state=prev_h, maps=maps,
+                                              prev_cost=0.0, enable_noise=False)
+        res = sh.free_restart_loop(objective, params, opt.step, budget=fx["budget"], n_iter=25, past_initial=True,
+                                   log=None, use_graph=use_graph)
+        outs.append((params, res))
+    (pa, ra), (pb, rb) = outs
+    assert ra["n_iter"] == rb["n_iter"] == 25
+    # multi-level MC trees accumulate ancestor adjoints with FP64 atomics (order varies run to run): 1e-7 there,
+    # bitwise otherwise
+    same = (lambda a, b: torch.equal(a, b)) if (ts or L == 1) else (lambda a, b: H.scaled_err(a, b) < 1e-7)
+    for a, b in zip(pa, pb):
+        assert same(a, b)
+    assert same(ra["best_loss"], rb["best_loss"]) and same(ra["best_cost"], rb["best_cost"])
+    assert same(ra["best_actions"], rb["best_actions"])
