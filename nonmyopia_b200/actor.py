@@ -375,9 +375,9 @@ class Actor:
             return acqf.forward(prev_X=prev_X, prev_y=prev_y, prev_hid_state=prev_h, maps=local_maps, embedder=None,
                                 prev_cost=prev_cost, enable_noise=False)
 
-        # HES objectives draw their cost noise on the device (graph-safe): replay the iteration as one CUDA graph;
-        # the BoTorch-style baselines keep per-call host state (qKG scramble) and stay eager
-        use_graph = isinstance(acqf, qMultiStepHEntropySearch) and self.rng_mode != "host" and params[0].is_cuda
+        # every objective draws its cost noise on the device (graph-safe generator): replay the iteration as one
+        # CUDA graph; "host" RNG mode keeps the eager launch sequence (draws in the reference's host order)
+        use_graph = self.rng_mode != "host" and params[0].is_cuda
         return sh.free_restart_loop(objective, params, opt.step, budget=p.budget, n_iter=p.acq_opt_iter,
                                     past_initial=past_initial, n_global=p.n_restarts, group=self.group,
                                     save_trajectory=save_trajectory, use_graph=use_graph)

@@ -17,8 +17,14 @@ from __future__ import annotations
 
 from typing import Callable, Dict, List, Optional, Sequence, Tuple
 
+import warnings
+
 import torch
 from torch import Tensor
+
+# the graph-replayed loop runs its backward on the capture stream while the leaves were created on the caller's
+# stream; the streams are ordered explicitly (wait_stream), so autograd's generic hint does not apply
+warnings.filterwarnings("ignore", message="The AccumulateGrad node's stream does not match")
 
 
 def _dist():

@@ -127,3 +127,35 @@ def test_baselines_match_reference_golden():
         for gd, gr in zip(grads, g["grads"]):
             scale = max(float(gr.abs().max()), 1e-6)
             assert float((gd.cpu() - gr).abs().max()) / scale < 1e-7, algo
+
+
+@pytest.mark.parametrize("algo", ["qEI", "qUCB", "qKG"])
+def test_baseline_loop_graph_replay_equals_eager(algo):
+    """The free-parameter loop over a BoTorch-style baseline, replayed as a CUDA graph, equals the eager loop
+    (cost noise off; q = 1 trees have no atomics: bitwise; qKG's one-level tree: 1e-9)."""
+    from nonmyopia_b200 import acqfs, sharding as sh
+    from nonmyopia_b200.actor import _FlatAdamW
+    fx = H.load("baselines_ackley")
+    if algo not in fx["algos"]:
+        pytest.skip(f"{algo} not in the fixture")
+    g = fx["algos"][algo]
+    gp = product_gp(fx["gp"])
+    smp = acqfs.SobolQMCNormalSampler(64, seed=0)
+    smp.base_samples = g["base"].clone()
+    acqf = acqfs.qBOAcqf(name=algo, model=gp, lookahead_steps=1 if algo == "qKG" else 0, n_actions=1,
+                         n_fantasy_at_design_pts=[64], loss_function_class=acqfs.qLossFunctionTopK,
+                         loss_func_hypers=dict(dist_weight=1, dist_threshold=0.5), cost_function_class=acqfs.qCostFunction,
+                         cost_func_hypers=dict(fx["cost"], max_noise=0.0), sampler=smp, best_f=fx["best_f"])
+    prev_X = g["prev_X"].cuda()
+    outs = []
+    for use_graph in (False, True):
+        params = [torch.logit(m.clone().clamp(0.01, 0.99)).cuda().requires_grad_(True) for m in g["maps"]]
+        opt = _FlatAdamW(params, lr=1e-2)
+        res = sh.free_restart_loop(lambda maps: acqf.forward(prev_X, None, maps), params, opt.step, budget=fx.get("budget", 2.0),
+                                   n_iter=20, past_initial=True, log=None, use_graph=use_graph)
+        outs.append((params, res))
+    (pa, ra), (pb, rb) = outs
+    assert ra["n_iter"] == rb["n_iter"] == 20
+    for a, b in zip(pa, pb):
+        assert H.scaled_err(a, b) < 1e-9
+    assert H.scaled_err(ra["best_loss"], rb["best_loss"]) < 1e-9
