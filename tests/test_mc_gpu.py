@@ -159,3 +159,44 @@ def test_baseline_loop_graph_replay_equals_eager(algo):
     for a, b in zip(pa, pb):
         assert H.scaled_err(a, b) < 1e-9
     assert H.scaled_err(ra["best_loss"], rb["best_loss"]) < 1e-9
+
+
+@pytest.mark.parametrize("n,d,kernel", [(333, 3, "rbf"), (700, 6, "matern52"), (800, 8, "matern32"), (97, 12, "matern52")])
+def test_whiten_large_n_vs_oracle(n, d, kernel):
+    """Shared-root whitening at training-set sizes where the kernels fall back to 24 / 16-row tiles and 3-stage rings
+    (n up to GPyTorch's max_cholesky_size = 800), odd n (padding to ldl), d > 8: values and gradient vs the oracle."""
+    import ctypes as C
+    from nonmyopia_b200 import _lib
+    from nonmyopia_b200.gp import SurrogateGP
+    from nonmyopia_b200.mc_tree import gp_struct
+    from oracle import gp_math
+    gen = torch.Generator().manual_seed(n)
+    X = torch.rand(n, d, dtype=F64, generator=gen)
+    Y = torch.randn(n, 1, dtype=F64, generator=gen)
+    ls = torch.full((1, d), 0.4, dtype=F64)
+    ref = gp_math.DenseGP.fit_caches(X, Y, kind=kernel, lengthscale=ls, outputscale=1.3, noise=1e-2, mean_const=0.1)
+    gp = SurrogateGP(X, Y, kernel=kernel, lengthscale=ls.reshape(-1), outputscale=1.3, noise=1e-2, mean_const=0.1)
+    g, keep = gp_struct(gp, F64)
+    P = 101
+    x = torch.rand(P, d, dtype=F64, generator=gen)
+    xr = x.clone().requires_grad_(True)
+    k = gp_math.kernel_matrix(xr, ref.train_X, ref.kind, ref.lengthscale, ref.outputscale)
+    u_ref, m0_ref = k @ ref.R, k @ ref.alpha
+    gU = torch.randn(P, g.ldu, dtype=F64, generator=gen)
+    gm = torch.randn(P, dtype=F64, generator=gen)
+    (gx_ref,) = torch.autograd.grad((u_ref * gU[:, :n]).sum() + (m0_ref * gm).sum(), xr)
+    xc, gUc, gmc = x.cuda(), gU.cuda(), gm.cuda()
+    U = torch.zeros(P, g.ldu, dtype=F64, device="cuda")
+    m0, q = torch.zeros(P, dtype=F64, device="cuda"), torch.zeros(P, dtype=F64, device="cuda")
+    gx = torch.zeros(P, d, dtype=F64, device="cuda")
+    lib = _lib.lib()
+    _lib.check(lib.nmb_gp_whiten_fwd(C.byref(g), 0, _lib.ptr(xc), C.c_int64(P), _lib.ptr(U), _lib.ptr(m0), _lib.ptr(q),
+                                     _lib.stream_ptr()))
+    _lib.check(lib.nmb_gp_whiten_bwd(C.byref(g), 0, _lib.ptr(xc), C.c_int64(P), _lib.ptr(gUc), _lib.ptr(gmc), _lib.ptr(gx),
+                                     _lib.stream_ptr()))
+    torch.cuda.synchronize()
+    # conditioning of K + s2 I at these sizes: 1e-7 of the largest entry
+    assert H.scaled_err(U[:, :n], u_ref) < 1e-7
+    assert H.scaled_err(m0, m0_ref) < 1e-7
+    assert H.scaled_err(q, (u_ref * u_ref).sum(-1)) < 1e-7
+    assert float((gx.cpu() - gx_ref).abs().max()) / float(gx_ref.abs().max()) < 1e-7
