@@ -225,3 +225,50 @@ def test_free_loop_graph_replay_equals_eager(name):
         assert same(a, b)
     assert same(ra["best_loss"], rb["best_loss"]) and same(ra["best_cost"], rb["best_cost"])
     assert same(ra["best_actions"], rb["best_actions"])
+
+
+@pytest.mark.parametrize("name", ["ts_free_ackley_L2", "mc_ackley_L1", "mc_hartmann_L3"])
+def test_free_query_loop_matches_oracle_loop(name):
+    """Free-parameter Actor.query loop (graph replay) vs the oracle's restatement of actor.py:489-662 on the same
+    logits, base samples and (zero) cost noise: snapshot decisions, AdamW trajectory, best values, arg-min."""
+    from nonmyopia_b200 import sharding as sh
+    from nonmyopia_b200.actor import _FlatAdamW
+    from oracle import hes_oracle as ho
+    from tests.test_mc_gpu import _samplers
+    fx = H.load(name)
+    ts = fx["kind"] == "ts_free"
+    L, N, d = fx["L"], fx["n_r"], fx["d"]
+    n_iter = 30
+    fx0 = dict(fx, cost=dict(fx["cost"], max_noise=0.0))
+    nf = [1] * L if ts else list(fx["nf"])
+    # ---- oracle loop on the CPU
+    spec = ho.HESSpec(lookahead=L, nf=nf, cost=H.cost_spec(fx0["cost"]), enable_ts=ts)
+    zero = lambda: ho.HESDraws(cost_noise=[torch.zeros(*nf[:s][::-1], N, 1, 1, dtype=F64) for s in range(L + 1)])
+    ref_params = [l.clone() for l in fx["logits"]]
+    ref = ho.query_loop(spec, fx["prev_X"], fx["prev_y"], None, ref_params, budget=fx["budget"], lr=1e-2, n_iter=n_iter,
+                        past_initial=True, path=H.oracle_path(fx) if ts else None, gp=None if ts else H.dense_gp(fx["gp"]),
+                        design_base=fx.get("design_base"), action_base=fx.get("action_base"),
+                        draws_per_iter=[(zero(), None) for _ in range(n_iter)])
+    # ---- product loop
+    if ts:
+        acqf = make_acqf(fx0, nf, True)
+        acqf.dump_model(f=_product_path(fx))
+    else:
+        ds, a = _samplers(fx)
+        acqf = make_acqf(fx0, nf, False, n_samples=fx["S_a"], design_samplers=ds, action_sampler=a)
+        acqf.dump_model()
+    prev_X, prev_y = fx["prev_X"].cuda(), fx["prev_y"].cuda()
+    prev_h = torch.zeros(N, 4, dtype=F64, device="cuda")
+    params = [l.clone().cuda().requires_grad_(True) for l in fx["logits"]]
+    opt = _FlatAdamW(params, lr=1e-2)
+    res = sh.free_restart_loop(lambda maps: acqf.forward(prev_X=prev_X, prev_y=prev_y, prev_hid_state=prev_h, maps=maps,
+                                                         prev_cost=0.0, enable_noise=False),
+                               params, opt.step, budget=fx["budget"], n_iter=n_iter, past_initial=True, log=None,
+                               use_graph=True)
+    assert res["n_iter"] == ref["n_iter"]
+    for a_, b_ in zip(params, ref_params):
+        assert H.scaled_err(a_, b_) < 1e-7
+    assert H.rel_err(res["best_loss"], ref["best_loss"], atol=1e-2) < 1e-7
+    assert H.rel_err(res["best_cost"], ref["best_cost"], atol=1e-3) < 1e-7
+    tot = res["best_loss"] + res["best_cost"]
+    assert int(torch.argmin(tot)) == int(ref["idx"])
