@@ -16,6 +16,7 @@ import json
 import math
 import os
 import sys
+import time
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 if ROOT not in sys.path:
@@ -94,15 +95,34 @@ def run_mc(args, rank, world):
     opt = _FlatAdamW(params, lr=1e-2)
     budget = 2 * math.sqrt(d)
 
-    def step():
-        rd = acqf.forward(prev_X=prev_X, prev_y=prev_y, prev_hid_state=prev_h, maps=[torch.sigmoid(p) for p in params],
-                          prev_cost=0.0, enable_noise=False)
-        loss = rd["acqf_loss"] + abs(budget - rd["acqf_cost"])
-        opt.step(torch.autograd.grad(loss.sum() / args.restarts, params, allow_unused=True))
+    def objective(maps):
+        return acqf.forward(prev_X=prev_X, prev_y=prev_y, prev_hid_state=prev_h, maps=maps, prev_cost=0.0, enable_noise=False)
 
-    mode = "eager"
-    # 8 warm-up iterations: the first ones grow the caching allocator (2 x 853 MB workspaces) and load modules
-    ms = timed(step, args.steps, warmup=8)
+    group = None
+    if world > 1:
+        import torch.distributed as dist
+        group = dist.group.WORLD
+
+    def run(n_iter):
+        """The product loop (sharding.free_restart_loop = Actor._query_free): graph-replayed iteration, two decision
+        minima read on the host every iteration (MIN-reduced over the ranks when sharded)."""
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        sh.free_restart_loop(objective, params, opt.step, budget=budget, n_iter=n_iter, past_initial=False,
+                             n_global=args.restarts, group=group, log=None, use_graph=not args.eager)
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1)
+
+    mode = "eager" if args.eager else "cuda-graph"
+    run(10)                                   # allocator growth, module loading
+    # every call re-captures its graph and regrows the private pool: difference of the best long and short calls
+    shorts = [run(10) for _ in range(2)]
+    longs = [run(10 + args.steps) for _ in range(3)]
+    ms = (min(longs) - min(shorts)) / args.steps     # device time per iteration (events on the launching stream)
+    print(f"rank {rank}: run(10) {[round(v, 1) for v in shorts]} ms, run({10 + args.steps}) {[round(v, 1) for v in longs]} ms",
+          file=sys.stderr, flush=True)
     print(f"rank {rank}: {ms:.3f} ms/step ({mode})", file=sys.stderr, flush=True)
     if world > 1:
         import torch.distributed as dist
@@ -233,6 +253,7 @@ def main():
     ap.add_argument("--widths", default="64,4,2")
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--max-restarts", type=int, default=8192)
+    ap.add_argument("--eager", action="store_true", help="mc: eager launch sequence instead of the graph replay")
     args = ap.parse_args()
     if args.restarts is None:
         args.restarts = 256 if args.case == "mc" else 64
