@@ -105,3 +105,42 @@ def test_rollout_fp32_variant_tolerance():
     assert H.rel_err(buf.loss, g["acqf_loss"], atol=1.0) < 1e-3
     assert H.rel_err(buf.cost, g["acqf_cost"], atol=1.0) < 1e-3
     assert H.rel_err(buf.A, g["actions"].reshape(fx["n_r"], fx["d"]), atol=1.0) < 1e-3
+
+
+@pytest.mark.parametrize("d,Hd,n_r,L,kernel", [(3, 16, 9, 2, "rbf"), (3, 24, 40, 2, "matern52"), (5, 64, 65, 1, "matern32"),
+                                               (6, 32, 17, 3, "matern12"), (12, 64, 33, 2, "matern52")])
+def test_rollout_other_dims_vs_oracle(d, Hd, n_r, L, kernel):
+    """Input dimensions beyond the fixtures' 2 and 8 (odd d takes the non-tensor-pipe backward; d > 8 the 16-wide
+    template), all four kernels, hidden sizes that are not 64: a synthetic GP + Thompson path built by the oracle
+    (d = 1 is not a valid input of the reference either: its rotation draws a coordinate PAIR)."""
+    from oracle import gp_math, hes_oracle as ho
+    from nonmyopia_b200 import ts_engine as te
+    gen = torch.Generator().manual_seed(100 * d + Hd)
+    n = 23
+    X = torch.rand(n, d, dtype=torch.float64, generator=gen)
+    Y = torch.randn(n, 1, dtype=torch.float64, generator=gen)
+    ls = torch.full((1, d), 0.35, dtype=torch.float64)
+    gp = gp_math.DenseGP.fit_caches(X, Y, kind=kernel, lengthscale=ls, outputscale=1.2, noise=1e-2, mean_const=0.05)
+    path = gp_math.draw_matheron_path(gp, Y, 1, generator=gen)
+    P = ho.init_policy_params(d, Hd, generator=gen)
+    cost = dict(radius=0.1, k=1.0, max_noise=1e-5, p_norm=2.0, discount=0.0, discount_threshold=-1.0)
+    fx = dict(d=d, H=Hd, L=L, n_r=n_r, policy=P, cost=cost, budget=2.0,
+              gp=dict(train_X=X, train_Y=Y, kernel=kernel, lengthscale=0.35, outputscale=1.2, noise=1e-2, mean_const=0.05, ard=True),
+              path=dict(W=path.W, w=path.w, v=path.v),
+              prev_X=X[-1:].expand(n_r, -1).clone(), prev_y=Y[-1:].expand(n_r, -1).clone(),
+              prev_h=torch.randn(n_r, Hd, dtype=torch.float64, generator=gen))
+    spec = ho.HESSpec(L, [1] * L, 1, H.cost_spec(cost), enable_ts=True)
+    Pq = {k: v.clone().requires_grad_(True) for k, v in P.items()}
+    torch.manual_seed(11)
+    o = ho.hes_forward(spec, fx["prev_X"], fx["prev_y"], fx["prev_h"], Pq, path=path, enable_noise=True)
+    tot = (o["acqf_loss"] + (fx["budget"] - o["acqf_cost"]).abs()).mean()
+    gref = dict(zip(Pq.keys(), torch.autograd.grad(tot, list(Pq.values()))))
+    fx["out"] = {"orig": dict(rot=o["draws"].rot, cost_noise=o["draws"].cost_noise)}
+    eng, buf, grad = run_product(fx, "orig")
+    assert H.rel_err(buf.loss, o["acqf_loss"], atol=1e-2) < 1e-8
+    assert H.rel_err(buf.cost, o["acqf_cost"], atol=1e-3) < 1e-8
+    assert H.rel_err(buf.A, o["actions"].reshape(n_r, d), atol=1e-3) < 1e-8
+    gd = te.unflatten_params(grad.cpu(), d, Hd)
+    for k, ref in gref.items():
+        scale = max(float(ref.abs().max()), 1e-6)
+        assert float((gd[k] - ref).abs().max()) / scale < 1e-8, k
