@@ -106,11 +106,17 @@ class _BaseSampler(nn.Module):
         # BoTorch draws the seed from the global host generator at construction
         self.seed = int(seed) if seed is not None else int(torch.randint(0, 1_000_000, (1,)).item())
         self.base_samples = None
+        self._on_device = {}
 
     def base(self, dtype=torch.float64, device="cuda") -> Tensor:
         if self.base_samples is None:
             self.base_samples = self._draw(dtype)
-        return self.base_samples.to(device=device, dtype=dtype).reshape(-1).contiguous()
+        if self._on_device.get("src") is not self.base_samples:      # (re)assigned from outside: drop the copies
+            self._on_device = {"src": self.base_samples}
+        key = (str(device), dtype)
+        if key not in self._on_device:          # one upload; later calls (CUDA-graph capture included) reuse it
+            self._on_device[key] = self.base_samples.to(device=device, dtype=dtype).reshape(-1).contiguous()
+        return self._on_device[key]
 
 
 class SobolQMCNormalSampler(_BaseSampler):

@@ -360,6 +360,49 @@ def case_query(ref, name, env, n, L, n_r, H, seed, cost, n_iter):
     print(f"[golden] {name}: ok ({o['n_iter']} iterations, idx {int(o['idx'])})")
 
 
+def case_eval(ref, name, env, n, n_r, seed, cost, algo, lookahead=0, n_initial=None, lr=1e-2):
+    """``utils.eval_func`` verbatim (1000 AdamW steps) vs ``oracle/eval_oracle.py``.  For the non-HES
+    branch the two names utils.py forgets to import are supplied (SURVEY App. D#9)."""
+    from nonmyopia_b200.synthetic import objective
+    from oracle import eval_oracle as eo
+    prob = make_problem(env, seed=2)
+    model, X, Y = _shim_model(prob, n)
+    d = prob.d
+    n_initial = n if n_initial is None else n_initial
+    ref.utils.qBOAcqf = ref.acqfs.qBOAcqf
+    ref.utils.SobolQMCNormalSampler = bs.SobolQMCNormalSampler
+    parms = types.SimpleNamespace(
+        algo=algo, algo_lookahead_steps=lookahead, x_dim=d, y_dim=1, n_actions=1, n_restarts=n_r,
+        n_initial_points=n_initial, acq_opt_lr=lr, torch_dtype=F64, num_categories=None,
+        loss_function_class=ref.acqfs.qLossFunctionTopK, loss_func_hypers=dict(dist_weight=1, dist_threshold=0.5),
+        cost_function_class=ref.acqfs.qCostFunction, cost_func_hypers=_cost_hypers(cost))
+    g = torch.Generator().manual_seed(seed)
+    costs = 0.05 * torch.rand(n, generator=g, dtype=F64)
+    buffer = dict(x=X.clone(), y=Y.clone(), cost=costs)
+    iteration = n - 1
+    env_fn = lambda A: objective(env, A.reshape(-1, d))
+    import contextlib, io
+    torch.manual_seed(seed + 3)
+    with contextlib.redirect_stdout(io.StringIO()):
+        (u_obs, u_post, regret), A_ref = ref.utils.eval_func(env_fn, model, parms, buffer, iteration)
+    torch.manual_seed(seed + 3)
+    draws = []
+    (o_obs, o_post, o_reg), A_or = eo.eval_func(
+        env_fn, model.dense(), buffer, iteration, algo=algo, n_restarts=n_r, n_actions=1,
+        n_initial_points=n_initial, lr=lr, cost_spec=cost, lookahead_steps=lookahead, record=draws)
+    _close(A_or, A_ref, 1e-9, name + " A_chosen")
+    per = (len(draws) - 1) // 1000
+    assert len(draws) == 1 + 1000 * per
+    assert abs(o_post - u_post) < 1e-9 and abs(o_obs - u_obs) < 1e-12 and abs(o_reg - regret) < 1e-9
+    fx = dict(kind="eval_func", gp=_gp_inputs(prob, X, Y), d=d, n_r=n_r, env=env, algo=algo, lookahead=lookahead,
+              n_initial=n_initial, lr=lr, cost=_cost_hypers(cost), buffer=buffer, iteration=iteration,
+              # z0 = the initial jitter; steps[j] = the j-th draw of every step, stacked over the steps
+              draws=dict(z0=draws[0], steps=[torch.stack(draws[1 + j::per]) for j in range(per)]),
+              out=dict(u_observed=u_obs, u_posterior=u_post, regret=regret, A_chosen=A_ref.clone()))
+    torch.save(fx, os.path.join(GOLDEN_DIR, name + ".pt"))
+    print(f"[golden] {name}: ok (u_posterior {u_post:.6f})")
+
+
 def main():
     os.makedirs(GOLDEN_DIR, exist_ok=True)
     ref = bs.load_reference()
@@ -385,6 +428,12 @@ def main():
             kernel="matern12", ard=False)
     case_baselines(ref, "baselines_ackley", "Ackley", 30, 5, 41, euclid(0.075))
     case_query(ref, "query_ts_am_ackley_L1", "Ackley", 50, 1, 8, 32, 51, euclid(0.075), n_iter=12)
+    # utils.eval_func: HES branch, qEI (lookahead 0) and qKG (lookahead 1) branches
+    case_eval(ref, "eval_hes_ackley", "Ackley", 30, 6, 61, euclid(0.075), "HES-TS-AM-20", lookahead=3)
+    case_eval(ref, "eval_hes_hartmann_init", "Hartmann", 40, 5, 62, euclid(0.125), "HES-MC-3", lookahead=3,
+              n_initial=60)
+    case_eval(ref, "eval_qei_ackley", "Ackley", 30, 6, 63, euclid(0.075), "qEI", lookahead=0)
+    case_eval(ref, "eval_qkg_ackley", "Ackley", 30, 6, 64, euclid(0.075), "qKG", lookahead=1)
 
 
 if __name__ == "__main__":
