@@ -303,6 +303,7 @@ int nmb_peer_adamw_step(const nmb_peer_exchange_t* px, int dtype, int d, int H, 
  * (SURVEY App. A.4 "structural identity").  Tree layout as in nmb_tree_cost_*.
  * ---------------------------------------------------------------------- */
 #define NMB_MAX_LEVELS 16
+#define NMB_TILE_STRIDE 68   /* doubles per tile row: 64 columns + 4 pad (bank-conflict-free fragment loads) */
 typedef struct nmb_gp {
     int32_t d, n, kernel_id;
     int32_t ldu;            /* row stride of U / gU (>= n, multiple of 4) */
@@ -314,7 +315,7 @@ typedef struct nmb_gp {
     const void* linv;       /* [ldl][ldl] inverse Cholesky root, row-major, lower triangular, zero padded */
     const void* linv_t;     /* [ldl][ldl] its transpose, zero padded */
     const void* alpha;      /* [n] (K + s2 I)^-1 (y - c) */
-    /* FP64 tensor-pipe kernels: the same two matrices tiled by 64-column blocks, [ceil(ldl/64)][ldl][72]
+    /* FP64 tensor-pipe kernels: the same two matrices tiled by 64-column blocks, [ceil(ldl/64)][ldl][NMB_TILE_STRIDE = 68]
      * (tile[b][k][c] = M[k][64 b + c] for c < 64 and 64 b + c < ldl, else 0): one bulk copy per operand chunk */
     const void* linv_tiles;
     const void* linv_t_tiles;

@@ -7,7 +7,7 @@
 //     32..64-row GEMMs is bound by the shared-memory data pipe at ~1/3 of the FP64 peak.
 //   * the weight chunks were staged through registers (LDG -> STS -> __syncthreads) with the L2
 //     latency exposed at the start of each of the 10 GEMMs of a policy step.
-// Here a producer warp streams the step's weight chunks ([32 k-rows][H cols], row stride 72 doubles so
+// Here a producer warp streams the step's weight chunks ([32 k-rows][H cols], row stride kSW = 68 doubles so
 // the B fragments are bank-conflict free) with cp.async.bulk into a 4-stage mbarrier ring, running
 // ahead across layers and steps; consumer warps own 8-row x 32-col tiles of the CTA's rows x 64 block.
 // Activations are row-major [row][KS = H + 4] so A fragments are conflict free as well.
@@ -18,7 +18,12 @@
 namespace nmb {
 
 constexpr int kStages = 4;        // weight ring depth
-constexpr int kSW = 72;           // stage row stride (doubles): 72 = 8 mod 16 -> conflict-free B fragments
+// Stage row stride (doubles).  A 64-bit shared load is served as two half-warp wavefronts (lanes 0-15, 16-31); the
+// B fragment of lane l sits at (l & 3) * kSW + (l >> 2), so a half-warp touches k = 0..3 x n = 0..3 and needs
+// kSW = 4 (mod 16) for 16 distinct 8-byte banks.  (72 = 8 mod 16 looked conflict-free for an arbitrary lane split but
+// measured 2-way conflicts on every B load: ncu l1tex__data_bank_conflicts_pipe_lsu_mem_shared_op_ld, 1.7x the
+// ideal wavefronts in all five tensor-pipe kernels.)
+constexpr int kSW = 68;
 constexpr int kStageElems = kKC * kSW;
 constexpr int kMaxRowsMma = 56;   // 14 consumer warps + 1 producer warp = 480 threads
 constexpr int kGemmsPerStep = 10;

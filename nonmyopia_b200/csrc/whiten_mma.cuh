@@ -6,12 +6,12 @@
 //             fused with g_x = sum_j (g_K[j] + g_m0 alpha_j) d k(x, X_j) / dx  in the accumulator epilogue.
 //
 // Same machinery as the policy GEMMs (policy_mma.cuh): a producer warp streams [32 k-rows][64 cols] chunks of the
-// triangular operand with cp.async.bulk into an mbarrier ring (row stride 72 doubles: conflict-free B fragments),
+// triangular operand with cp.async.bulk into an mbarrier ring (row stride kSW = 68 doubles: conflict-free B fragments),
 // consumer warps own 8-row x 32-col accumulator tiles, A fragments come from a row-major tile with stride
 // KS = 4 mod 16 doubles (conflict free).  Replaces the DFMA 2x4 register-tile product (18 % of the FP64 peak at
 // n = 500: bound by the shared-memory data pipe, see the header of policy_mma.cuh).
 // The triangular operands are passed zero-padded to ldl = n rounded up to 8 (k extents are multiples of 4) and
-// pre-tiled by 64-column blocks, [ceil(ldl/64)][ldl][72], so that a chunk is one contiguous, 16-byte aligned bulk copy.
+// pre-tiled by 64-column blocks, [ceil(ldl/64)][ldl][68], so that a chunk is one contiguous, 16-byte aligned bulk copy.
 // Reference: GPyTorch's exact prediction strategy behind model.posterior (acqfs.py:366, 414).
 #pragma once
 #include "policy_mma.cuh"
@@ -48,7 +48,7 @@ struct WhSmem {
 };
 
 // Producer warp: chunks of the triangular operand in consumption order.  The operand is pre-tiled on the host,
-// Bt[column block][k][kSW] (64 columns + 8 pad = the stage row stride), so a [kn k-rows][kSW] chunk is ONE contiguous
+// Bt[column block][k][kSW] (64 columns + 4 pad = the stage row stride), so a [kn k-rows][kSW] chunk is ONE contiguous
 // bulk copy that lands in the stage layout as is (32 per-row copies of 512 B left the consumers waiting on the
 // copy engine: 18 % of the samples on the full-barrier wait).
 // forward (LOWER_ROWS = false): column block cb needs rows [0, cb + 64); backward: rows [cb, ldl).

@@ -40,8 +40,8 @@ class TreeState(C.Structure):
     _fields_ = [(n, C.c_void_p) for n in _names]
 
 
-def _col_tiles(M: Tensor, width: int = 64, stride: int = 72) -> Tensor:
-    """[ldl][ldl] -> [ceil(ldl/width)][ldl][stride]: 64-column blocks padded to the 72-double row stride of the
+def _col_tiles(M: Tensor, width: int = 64, stride: int = 68) -> Tensor:
+    """[ldl][ldl] -> [ceil(ldl/width)][ldl][stride]: 64-column blocks padded to the 68-double row stride of the
     shared-memory stage, so one contiguous bulk copy moves a whole operand chunk (csrc/whiten_mma.cuh)."""
     ldl = M.shape[0]
     nb = (ldl + width - 1) // width
