@@ -27,10 +27,23 @@ import torch
 from torch import Tensor
 
 from . import _lib
+# the helpers the reference's actor.py takes from utils (utils.py:313-365) live beside the Actor here
+from .actor import generate_random_points_batch, generate_random_rotation_matrix, rotate_points  # noqa: F401
 from .gp import SurrogateGP
 from .mc_tree import MCTree
 
 N_EVAL_STEPS = 1000                                                         # utils.py:171,250
+
+
+def set_seed(seed: int) -> None:
+    """utils.py:42-49: seed the host generators (python, numpy, torch) and every CUDA generator."""
+    import random
+
+    import numpy as np
+    random.seed(seed)
+    np.random.seed(seed)
+    torch.manual_seed(seed)
+    torch.cuda.manual_seed_all(seed)
 
 
 def _previous_cost(buffer, iteration: int, parms) -> float:

@@ -31,3 +31,42 @@ def test_product_never_imports_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".cpp", ".h")):
                 txt = open(os.path.join(dp, f)).read()
                 assert not re.search(r"^\s*(from|import)\s+oracle\b", txt, flags=re.M), f
+
+
+def test_reference_module_names_are_mirrored():
+    """The names the reference's main.py / actor.py / compute_metrics.py import from acqfs, actor,
+    amortized_network and utils (main.py:19-33, actor.py:13-22, compute_metrics.py:23) exist here."""
+    import importlib
+    want = {
+        "acqfs": ["qBOAcqf", "qMultiStepHEntropySearch", "qLossFunctionTopK", "qCostFunction",
+                  "qCostFunctionEditDistance"],
+        "actor": ["Actor"],
+        "amortized_network": ["AmortizedNetwork", "Project2Range"],
+        "utils": ["eval_func", "set_seed", "generate_random_points_batch", "generate_random_rotation_matrix",
+                  "rotate_points"],
+    }
+    for mod, names in want.items():
+        m = importlib.import_module("nonmyopia_b200." + mod)
+        for n in names:
+            assert hasattr(m, n), f"{mod}.{n}"
+
+
+def test_eval_func_fails_loudly_without_cuda():
+    """No CPU fallback: on a box without a GPU the product call raises instead of computing on the host."""
+    import types
+
+    import pytest
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("needs a CPU-only box")
+    from nonmyopia_b200 import acqfs
+    from nonmyopia_b200.utils import eval_func
+    parms = types.SimpleNamespace(
+        algo="HES-TS-AM-20", algo_lookahead_steps=3, x_dim=2, n_actions=1, n_restarts=4, n_initial_points=5,
+        acq_opt_lr=1e-2, torch_dtype=torch.float64, loss_function_class=acqfs.qLossFunctionTopK,
+        loss_func_hypers=dict(dist_weight=1, dist_threshold=0.5), cost_function_class=acqfs.qCostFunction,
+        cost_func_hypers=dict(radius=0.1))
+    X, Y = torch.rand(5, 2, dtype=torch.float64), torch.randn(5, 1, dtype=torch.float64)
+    model = types.SimpleNamespace(train_inputs=(X,), train_targets=Y.reshape(-1))
+    with pytest.raises(Exception):
+        eval_func(lambda a: a.sum(), model, parms, dict(x=X, y=Y, cost=torch.zeros(5)), 4)
