@@ -207,15 +207,16 @@ def test_free_loop_graph_replay_equals_eager(name):
     acqf.dump_model(f=_product_path(fx) if ts else None)
     prev_X, prev_y = fx["prev_X"].cuda(), fx["prev_y"].cuda()
     prev_h = torch.zeros(N, 4, dtype=F64, device="cuda")
-    outs = []
+    outs, logged = [], []
     for use_graph in (False, True):
         params = [l.clone().cuda().requires_grad_(True) for l in fx["logits"]]
         opt = _FlatAdamW(params, lr=1e-2)
         objective = lambda maps: acqf.forward(prev_X=prev_X, prev_y=prev_y, prev_hid_state=prev_h, maps=maps,
                                               prev_cost=0.0, enable_noise=False)
         res = sh.free_restart_loop(objective, params, opt.step, budget=fx["budget"], n_iter=25, past_initial=True,
-                                   log=None, use_graph=use_graph)
+                                   log=logged.append, use_graph=use_graph)
         outs.append((params, res))
+    assert not [m for m in logged if "eagerly" in m], logged      # the capture itself must succeed
     (pa, ra), (pb, rb) = outs
     assert ra["n_iter"] == rb["n_iter"] == 25
     # multi-level MC trees accumulate ancestor adjoints with FP64 atomics (order varies run to run): 1e-7 there,

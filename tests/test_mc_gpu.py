@@ -147,13 +147,16 @@ def test_baseline_loop_graph_replay_equals_eager(algo):
                          loss_func_hypers=dict(dist_weight=1, dist_threshold=0.5), cost_function_class=acqfs.qCostFunction,
                          cost_func_hypers=dict(fx["cost"], max_noise=0.0), sampler=smp, best_f=fx["best_f"])
     prev_X = g["prev_X"].cuda()
-    outs = []
+    outs, logged = [], []
     for use_graph in (False, True):
         params = [torch.logit(m.clone().clamp(0.01, 0.99)).cuda().requires_grad_(True) for m in g["maps"]]
         opt = _FlatAdamW(params, lr=1e-2)
         res = sh.free_restart_loop(lambda maps: acqf.forward(prev_X, None, maps), params, opt.step, budget=fx.get("budget", 2.0),
-                                   n_iter=20, past_initial=True, log=None, use_graph=use_graph)
+                                   n_iter=20, past_initial=True, log=logged.append, use_graph=use_graph)
         outs.append((params, res))
+    # the capture must succeed: a host->device copy inside the objective (e.g. re-uploading the sampler's base samples)
+    # would silently drop the loop back to eager launches
+    assert not [m for m in logged if "eagerly" in m], logged
     (pa, ra), (pb, rb) = outs
     assert ra["n_iter"] == rb["n_iter"] == 20
     for a, b in zip(pa, pb):
