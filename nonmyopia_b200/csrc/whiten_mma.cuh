@@ -21,7 +21,9 @@ namespace nmb {
 __host__ __device__ inline int wh_ks(int ldl) { return (ldl + 15) / 16 * 16 + 4; }
 
 // per consumer warp (backward only): its 32 training points of the current column block, scaled, + their alpha
-template <int DMAX> __host__ __device__ constexpr int wh_tp_elems() { return 32 * (DMAX + 1); }
+// (row stride DMAX + 1: the 4 k-lanes of a fragment read points 2 apart - an even stride of 2 * DMAX doubles put all
+// four in one bank, 160 M conflicts per launch at cfg 3)
+template <int DMAX> __host__ __device__ constexpr int wh_tp_elems() { return 32 * (DMAX + 2); }
 
 template <int DMAX>
 inline size_t wh_mma_bytes(int ldl, int R, int nst, bool bwd) {
@@ -231,8 +233,8 @@ __global__ void __launch_bounds__(288, 1) whiten_bwd_mma_kernel(GpDev<double> g,
         mma_gemm<NST>(ring, w, sm.A + cb, ldl - cb, acc);
         __syncwarp();
 #pragma unroll
-        for (int k = 0; k < DMAX; ++k) tp[lane * DMAX + k] = tjr[k];
-        tp[32 * DMAX + lane] = alr;
+        for (int k = 0; k < DMAX; ++k) tp[lane * (DMAX + 1) + k] = tjr[k];
+        tp[32 * (DMAX + 1) + lane] = alr;
         __syncwarp();
 #pragma unroll
         for (int t = 0; t < 4; ++t) {
@@ -240,11 +242,11 @@ __global__ void __launch_bounds__(288, 1) whiten_bwd_mma_kernel(GpDev<double> g,
             for (int e = 0; e < 2; ++e) {
                 const int cl = 8 * t + 2 * w.fk + e;
                 if (cb + w.col0 + cl < n) {
-                    const double al = tp[32 * DMAX + cl];
+                    const double al = tp[32 * (DMAX + 1) + cl];
                     double sd[DMAX], r2 = 0.0;
 #pragma unroll
                     for (int k = 0; k < DMAX; ++k) {
-                        sd[k] = xr[k] - tp[cl * DMAX + k];
+                        sd[k] = xr[k] - tp[cl * (DMAX + 1) + k];
                         r2 = fma(sd[k], sd[k], r2);
                     }
                     double kap, gc;
