@@ -70,3 +70,17 @@ def test_eval_func_fails_loudly_without_cuda():
     model = types.SimpleNamespace(train_inputs=(X,), train_targets=Y.reshape(-1))
     with pytest.raises(Exception):
         eval_func(lambda a: a.sum(), model, parms, dict(x=X, y=Y, cost=torch.zeros(5)), 4)
+
+
+def test_tile_stride_constant_is_consistent():
+    """NMB_TILE_STRIDE (header) == kSW (kernels) == the host packer's default, and it is 4 mod 16 doubles - the
+    bank-conflict-free stride of the DMMA B-fragment loads (a half-warp reads k = 0..3 x n = 0..3)."""
+    import inspect
+    hdr = open(os.path.join(ROOT, "include", "nonmyopia_b200.h")).read()
+    cuh = open(os.path.join(ROOT, "nonmyopia_b200", "csrc", "policy_mma.cuh")).read()
+    h = int(re.search(r"#define\s+NMB_TILE_STRIDE\s+(\d+)", hdr).group(1))
+    k = int(re.search(r"constexpr int kSW = (\d+);", cuh).group(1))
+    from nonmyopia_b200 import mc_tree
+    py = inspect.signature(mc_tree._col_tiles).parameters["stride"].default
+    assert h == k == py
+    assert h % 16 in (4, 12) and h >= 64
