@@ -146,6 +146,9 @@ typedef struct nmb_ts_problem {
     uint64_t seed;             /* in-kernel RNG (used only where rot_q / cost_noise are NULL) */
     const int64_t* step_ptr;   /* device counter mixed into the in-kernel RNG, may be NULL */
     const int32_t* done_flag;  /* device flag: non-zero => kernels return immediately, may be NULL */
+    int64_t chain_offset;      /* global index of this rank's chain 0 (restarts sharded over GPUs): the
+                                  in-kernel RNG is keyed by the GLOBAL chain index, so a sharded run draws the same
+                                  numbers per restart as the unsharded one */
 } nmb_ts_problem_t;
 
 typedef struct nmb_ts_rollout {
@@ -164,6 +167,15 @@ typedef struct nmb_ts_rollout {
     void* loss;                /* out [N]         -f(a)  (top-k loss, n_actions = 1) */
     void* cost;                /* out [N]         accumulated spotlight cost */
     void* save;                /* workspace for backward (nmb_ts_save_bytes) or NULL for a no-grad rollout */
+    /* Host-stream ring (optional; takes precedence over rot_q / cost_noise and over the in-kernel RNG): the draws of
+     * ring_len consecutive Adam iterations, produced ahead of time on the host in the reference's generator order
+     * (nmb_host_rng_ts_am_stream) and uploaded while earlier iterations run; iteration `*step_ptr` reads slot
+     * step % ring_len, so ONE captured CUDA graph serves every iteration with the reference's exact random stream. */
+    const void* ring_cs;       /* [ring_len][L+1][N][2] float32 (cos, sin) of the rotation angle (amortized_network.py:144-153) */
+    const int32_t* ring_dims;  /* [ring_len][L+1][N][2] coordinate pairs */
+    const void* ring_noise;    /* [ring_len][L+1][N]    N(0,1) draws of the cost calls, problem dtype */
+    int32_t ring_len;          /* 0: no ring */
+    int32_t _pad2;
 } nmb_ts_rollout_t;
 
 int64_t nmb_ts_save_bytes(int dtype, int d, int H, int L, int64_t n_chains);
@@ -377,6 +389,38 @@ int nmb_mc_utility(int dtype, int which, double best_f, double beta, const void*
  * one op per call otherwise) to *host_result. Synchronous.
  * ---------------------------------------------------------------------- */
 int nmb_pipe_peak(int dtype, int which, double* host_result);
+
+/* Device-side evaluation of the straight-line FP64 transcendentals the rollout kernels use (csrc/fastmath.cuh), for
+ * accuracy tests against libm: y0 = table-driven variant, y1 = Taylor variant, n doubles each.
+ * which: 0 exp, 1 expm1, 2 sincospi (y0 = sin, y1 = cos, table), 3 sigmoid, 4 tanh, 5 reciprocal (2 / 3 Newton
+ * steps), 6 elu, 7 sincospi (Taylor).  They stand in for torch's exp / sigmoid / tanh / elu / sin / cos inside
+ * amortized_network.py:97-133 and the Matheron path features (acqfs.py:362). */
+int nmb_fastmath_probe(int which, const void* x, void* y0, void* y1, int64_t n, void* stream);
+
+/* ------------------------------------------------------------------------
+ * Host-side replica of torch's CPU generator streams (pure host code, no CUDA call): the random numbers the
+ * reference draws inside every Adam iteration of Actor.query, produced in bulk, in the reference's order, bit for
+ * bit, so that the CUDA-graph loop can read them from a device ring ("same inputs and seeds => identical next
+ * query").  `state` is the 5056-byte blob of torch.get_rng_state() (ATen CPUGeneratorImplState: mt19937 words,
+ * position, cached normal) and is advanced in place.
+ *   nmb_host_rng_rand_f32      torch.rand(n)                       amortized_network.py:136
+ *   nmb_host_rng_randperm      n_perms x torch.randperm(d) [int64] amortized_network.py:156
+ *   nmb_host_rng_randn_f64     n_calls x torch.randn(sizes[c], dtype=float64), back to back   acqfs.py:624
+ *   nmb_host_rng_ts_am_stream  n_iters Adam iterations of HES-TS-AM (actor.py:568-593): per iteration the main
+ *       rollout's action-call rotation draw (u_main [it][N] float32 in [0,1), dims_main [it][N][2]) and its L+1 cost
+ *       noises (nz_main [it][L+1][N]), then the frozen rollout's L+1 rotation draws (u_orig [it][L+1][N],
+ *       dims_orig [it][L+1][N][2]) and its L+1 cost noises (nz_orig [it][L+1][N]).  states_out (optional,
+ *       [n_iters][5056]) receives the generator state after every iteration, so an early stop can leave the
+ *       generator exactly where the reference would have.  n_threads: host threads for the uniform -> normal
+ *       transform (the word stream itself is serial).
+ * ---------------------------------------------------------------------- */
+int64_t nmb_host_rng_state_bytes(void);
+int nmb_host_rng_rand_f32(uint8_t* state, int64_t n, float* out);
+int nmb_host_rng_randperm(uint8_t* state, int n_perms, int d, int64_t* out);
+int nmb_host_rng_randn_f64(uint8_t* state, int n_calls, const int64_t* sizes, double* out, int n_threads);
+int nmb_host_rng_ts_am_stream(uint8_t* state, int n_iters, int L, int64_t N, int d, float* u_main, int32_t* dims_main,
+                              double* nz_main, float* u_orig, int32_t* dims_orig, double* nz_orig,
+                              uint8_t* states_out, int n_threads);
 
 #ifdef __cplusplus
 }

@@ -145,6 +145,18 @@ def set_sampler_and_n_fantasy(sampler, n_fantasy: Optional[int]) -> Tuple[_BaseS
     return sampler, n_fantasy
 
 
+def _host_cost_noise(sizes, like: Tensor) -> Tensor:
+    """``cat([randn(n) for n in sizes])`` on torch's global CPU generator - the ``randn_like`` of one cost call per
+    tree level (acqfs.py:421-441,624) - walked by the C side (``nmb_host_rng_randn_f64``, bit for bit) and uploaded."""
+    if like.dtype != torch.float64:
+        return torch.cat([torch.randn(int(n), dtype=like.dtype) for n in sizes]).to(like.device)
+    from .host_rng import CpuStream
+    cs = CpuStream()
+    z = cs.randn_f64(sizes)
+    cs.commit()
+    return z.to(like.device)
+
+
 # --------------------------------------------------------------------------------------
 # fused TS-AM rollout as an autograd node
 # --------------------------------------------------------------------------------------
@@ -261,15 +273,17 @@ class qMultiStepHEntropySearch(nn.Module):
             self.n_fantasy_at_design_pts.append(nf)
         self.action_sampler, self.n_fantasy_at_action_pts = set_sampler_and_n_fantasy(
             sampler=action_sampler, n_fantasy=n_fantasy_at_action_pts)
-        # "device": rotation angles / cost noise drawn in-kernel (Philox, keyed by rng_seed and a
-        # call counter); "host": drawn by the host generators in the reference's order
-        self.rng_mode = kwargs.get("rng_mode", "device")
+        # "host" (default): rotation angles / cost noise come from torch's global CPU generator in the reference's
+        # order (seed-stream parity; Actor.query feeds them through a device ring at CUDA-graph speed);
+        # "device": drawn in-kernel (Philox keyed by rng_seed, iteration, call and global chain index)
+        self.rng_mode = kwargs.get("rng_mode", "host")
         self.rng_seed = None
         self._calls = 0
         self._gp = None
         self._engines = {}
         self._mc = None
         self._given_draws = None      # tests: explicit draws of the next forward
+        self._fed_noise = None        # Actor.query, host stream: static device buffer refilled before every iteration
 
     # ---- surrogate state
     def gp(self) -> SurrogateGP:
@@ -285,7 +299,8 @@ class qMultiStepHEntropySearch(nn.Module):
         self._mc = None
         if self.enable_ts:
             self.f = draw_thompson_path(self.gp(), 1) if f is None else f
-        self.rng_seed = int(torch.randint(0, 2**31 - 1, (1,)).item())
+        # the in-kernel RNG needs a seed; in "host" mode nothing the reference does not draw may touch the generator
+        self.rng_seed = int(torch.randint(0, 2**31 - 1, (1,)).item()) if self.rng_mode == "device" else 0
         self._calls = 0
 
     def clean_dump_model(self):
@@ -294,6 +309,15 @@ class qMultiStepHEntropySearch(nn.Module):
         self._mc = None
         if self.enable_ts:
             self.f = None
+
+    def cost_noise_sizes(self, n_r: int) -> List[int]:
+        """Element counts of the ``randn_like`` calls of one free-parameter ``forward`` (one per tree level)."""
+        sizes, w = [], n_r
+        for s in range(self.algo_lookahead_steps + 1):
+            sizes.append(w)
+            if s < self.algo_lookahead_steps and not self.enable_ts:
+                w *= self.n_fantasy_at_design_pts[s]
+        return sizes
 
     # ---- forward
     def forward(self, prev_X: Tensor, prev_y: Tensor, prev_hid_state: Tensor, maps, embedder: nn.Module = None,
@@ -306,7 +330,7 @@ class qMultiStepHEntropySearch(nn.Module):
             raise _lib.NmbError("nonmyopia_b200 ops need CUDA tensors (no CPU fallback)")
         prev_cost = float(prev_cost)
         if self.rng_seed is None:
-            self.rng_seed = int(torch.randint(0, 2**31 - 1, (1,)).item())
+            self.rng_seed = int(torch.randint(0, 2**31 - 1, (1,)).item()) if self.rng_mode == "device" else 0
         self._calls += 1
         if isinstance(maps, nn.Module):
             if not self.enable_ts:
@@ -331,16 +355,16 @@ class qMultiStepHEntropySearch(nn.Module):
         return eng
 
     def _host_draws(self, L, N, d, like, noisy_design):
-        """Rotation blocks and cost noise in the reference's order: one rotation draw per noisy
-        policy call on the host generator, then one randn per cost call on the device generator."""
+        """Rotation blocks and cost noise of ONE forward in the reference's order, all on the global host generator
+        (the reference run on the CPU, which the golden fixtures pin): one rotation draw per noisy policy call
+        (amortized_network.py:136,156), then one ``randn_like`` per cost call (acqfs.py:624)."""
         rq = torch.zeros(L + 1, N, 4, dtype=like.dtype, device=like.device)
         rd = torch.zeros(L + 1, N, 2, dtype=torch.int32, device=like.device)
         for l in range(L + 1):
             if l == L or noisy_design:
                 Q, dims = draw_rotation(N, d, like)
                 rq[l], rd[l] = Q.reshape(N, 4), dims
-        cn = torch.stack([torch.randn(N, 1, 1, dtype=like.dtype, device=like.device).reshape(N)
-                          for _ in range(L + 1)])
+        cn = torch.stack([torch.randn(N, 1, 1, dtype=like.dtype).reshape(N) for _ in range(L + 1)]).to(like.device)
         return rq.contiguous(), rd.contiguous(), cn.contiguous()
 
     def _forward_ts_amortized(self, prev_X, prev_y, prev_h, maps: AmortizedNetwork, prev_cost, enable_noise):
@@ -376,7 +400,14 @@ class qMultiStepHEntropySearch(nn.Module):
         levels = [maps[s].reshape(N, d) for s in range(L + 1)]
         draws = self._given_draws
         self._given_draws = None
-        noise = draws if draws is not None else torch.randn(L + 1, N, dtype=prev_X.dtype, device=prev_X.device)
+        if draws is not None:
+            noise = draws
+        elif self._fed_noise is not None:
+            noise = self._fed_noise.reshape(L + 1, N)
+        elif self.rng_mode == "host":      # one randn_like per cost call on the host generator (acqfs.py:624)
+            noise = _host_cost_noise([N] * (L + 1), prev_X)
+        else:
+            noise = torch.randn(L + 1, N, dtype=prev_X.dtype, device=prev_X.device)
         y_a = self.f.eval_points(levels[L].contiguous(), N // self.f.n_paths)
         acc = _TreeCostFn.apply(prev_X, noise.contiguous(), self.cost_function.hypers(), prev_cost, *levels)
         X_ret = [levels[s].reshape(*([1] * s), N, 1, d) for s in range(L)]
@@ -400,7 +431,14 @@ class qMultiStepHEntropySearch(nn.Module):
         levels = [maps[s].reshape(cnt[s], d) for s in range(L + 1)]
         draws = self._given_draws
         self._given_draws = None
-        noise = draws if draws is not None else torch.randn(sum(cnt), dtype=prev_X.dtype, device=prev_X.device)
+        if draws is not None:
+            noise = draws
+        elif self._fed_noise is not None:
+            noise = self._fed_noise
+        elif self.rng_mode == "host":
+            noise = _host_cost_noise(cnt, prev_X)
+        else:
+            noise = torch.randn(sum(cnt), dtype=prev_X.dtype, device=prev_X.device)
         leaf_loss = self._mc.apply(levels)                               # [cnt_L]  (-mean_samples y)
         acc = _TreeCostFn.apply(prev_X, noise.contiguous(), self.cost_function.hypers(), prev_cost, *levels)
         nf_rev = lambda s: nf[:s][::-1]
@@ -440,11 +478,18 @@ class qBOAcqf(nn.Module):
             raise NotImplementedError
         self._gp = None
         self._given_draws = None
+        self._fed_noise = None
+        self.rng_mode = kwargs.get("rng_mode", "host")
 
     def gp(self) -> SurrogateGP:
         if self._gp is None:
             self._gp = SurrogateGP.from_model(self.model)
         return self._gp
+
+    def cost_noise_sizes(self, n_r: int) -> List[int]:
+        """Element counts of the ``randn_like`` calls of one ``forward`` (acqfs.py:137-161)."""
+        nf = self.num_fantasies
+        return [n_r, n_r * nf * nf] if self.name == "qKG" else [n_r]
 
     def forward(self, prev_X: Tensor, prev_y: Tensor, maps, embedder: nn.Module = None, prev_cost: float = 0.0,
                 **kwargs) -> Dict[str, Tensor]:

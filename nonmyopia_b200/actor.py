@@ -89,9 +89,10 @@ class Actor:
             self.maps = []
         self.algo_lookahead_steps = parms.algo_lookahead_steps
         self.acqf = None
-        # "device" (default): rotation angles / cost noise drawn in-kernel, CUDA-graph loop;
-        # "host": drawn by the host generators in the reference's order (seed-stream parity)
-        self.rng_mode = getattr(parms, "rng_mode", "device")
+        # "host" (default): rotation angles / cost noise follow torch's global CPU generator in the reference's order
+        # (same seed => same next query as the reference run on the CPU), fed to the CUDA-graph loop through a
+        # device ring; "device": drawn in-kernel (Philox), no host work
+        self.rng_mode = getattr(parms, "rng_mode", "host")
         # restarts sharded over the ranks of this torch.distributed group (None: single GPU); SURVEY 8e
         self.group = getattr(parms, "process_group", None)
 
@@ -332,12 +333,23 @@ class Actor:
         eng.seed = acqf.rng_seed
         theta0 = self.maps.flat_parameters().detach()
         record = bool(save_trajectory)
+        rank, world = sh.world_of(self.group)
+        own = sh.restart_range(p.n_restarts, rank, world)
+        eng.chain_offset = own[0]
+        stream = self.rng_mode == "host" and p.torch_dtype == torch.float64
+        if self.rng_mode == "host":
+            # the reference builds its frozen copy of the network twice before the loop (actor.py:524-555); the
+            # random initialisation of those modules consumes the host generator ahead of the loop's draws
+            for _ in range(2):
+                AmortizedNetwork(input_dim=p.x_dim + p.y_dim, output_dim=p.x_dim, hidden_dim=p.hidden_dim,
+                                 n_actions=p.n_actions, output_bounds=p.bounds)
         loop = TSAMLoop(eng, theta0, prev_X, prev_y, prev_h, budget=float(p.budget), lr=p.acq_opt_lr,
                         past_initial=past_initial, prev_cost=prev_cost, max_iter=p.acq_opt_iter,
-                        record_history=record, record_trajectory=record, n_global=p.n_restarts, group=self.group)
-        if self.rng_mode == "host":
-            rank, world = sh.world_of(self.group)
-            draws = _HostDraws(acqf, L, p.n_restarts, d, prev_X, sh.restart_range(p.n_restarts, rank, world))
+                        record_history=record, record_trajectory=record, n_global=p.n_restarts, group=self.group,
+                        rng="host" if stream else "device", own=own)
+        if self.rng_mode == "host" and not stream:
+            # float32 variant: torch's float32 normal stream (AVX2 normal_fill) is drawn by torch itself, eagerly
+            draws = _HostDraws(acqf, L, p.n_restarts, d, prev_X, own)
             st = loop.run(p.acq_opt_iter, draws_per_iter=draws)
         else:
             st = loop.run(p.acq_opt_iter)
@@ -375,12 +387,28 @@ class Actor:
             return acqf.forward(prev_X=prev_X, prev_y=prev_y, prev_hid_state=prev_h, maps=local_maps, embedder=None,
                                 prev_cost=prev_cost, enable_noise=False)
 
-        # every objective draws its cost noise on the device (graph-safe generator): replay the iteration as one
-        # CUDA graph; "host" RNG mode keeps the eager launch sequence (draws in the reference's host order)
-        use_graph = self.rng_mode != "host" and params[0].is_cuda
-        return sh.free_restart_loop(objective, params, opt.step, budget=p.budget, n_iter=p.acq_opt_iter,
-                                    past_initial=past_initial, n_global=p.n_restarts, group=self.group,
-                                    save_trajectory=save_trajectory, use_graph=use_graph)
+        # The iteration is replayed as one CUDA graph.  "device": the objective draws its cost noise with the
+        # graph-safe device generator.  "host": the noise of every iteration is drawn on torch's CPU generator in the
+        # reference's order (nmb_host_rng_randn_f64, ahead of time on a host thread) and copied into the static
+        # buffer the graph reads.  Sharded: every rank walks the full stream and keeps its restarts' entries.
+        use_graph = params[0].is_cuda
+        feed = None
+        if self.rng_mode == "host":
+            from .host_rng import HostNoiseFeed
+            rank, world = sh.world_of(self.group)
+            lo, hi = sh.restart_range(p.n_restarts, rank, world)
+            feed = HostNoiseFeed(acqf.cost_noise_sizes(p.n_restarts), prev_X.device, prev_X.dtype,
+                                 shard=(p.n_restarts, lo, hi) if world > 1 else None)
+            acqf._fed_noise = feed.dev
+        try:
+            return sh.free_restart_loop(objective, params, opt.step, budget=p.budget, n_iter=p.acq_opt_iter,
+                                        past_initial=past_initial, n_global=p.n_restarts, group=self.group,
+                                        save_trajectory=save_trajectory, use_graph=use_graph,
+                                        pre_iteration=feed.fill if feed is not None else None)
+        finally:
+            if feed is not None:
+                feed.close()
+                acqf._fed_noise = None
 
 
 def _prior_free_sample(gp, x: Tensor) -> Tensor:

@@ -48,7 +48,9 @@ def build(force: bool = False, verbose: bool = False) -> str:
             sys.stderr.write(out)
         if p.returncode:
             raise RuntimeError(f"nvcc failed on {src}")
-    subprocess.check_call(["nvcc", "-shared", "-cudart", "static", "-o", OUT, *objs])
+    # -arch at link time too: without it nvcc adds an empty sm_52 stub cubin (and a deprecation warning)
+    subprocess.check_call(["nvcc", "-shared", "-cudart", "static", "-gencode", "arch=compute_100a,code=sm_100a",
+                           "-Xlinker", "-lpthread", "-o", OUT, *objs])
     return OUT
 
 

@@ -102,6 +102,39 @@ __device__ __forceinline__ void kernel_profile(int kernel_id, T r2, T& kappa, T&
     }
 }
 
+// table-driven variant of kernel_profile (FP64, `tab` = shared-memory copy of g_fast_tab)
+__device__ __forceinline__ void kernel_profile_tab(int kernel_id, double r2, const double* __restrict__ tab, double& kappa,
+                                                   double& gcoef) {
+    if (kernel_id == NMB_KERNEL_RBF) {
+        kappa = nmb_exp_tab(-0.5 * r2, tab);
+        gcoef = -kappa;
+        return;
+    }
+    const bool clamped = r2 < 1e-30;
+    const double r = ::sqrt(clamped ? 1e-30 : r2);
+    if (kernel_id == NMB_KERNEL_MATERN52) {
+        const double s5 = 2.23606797749978969641;
+        const double e = nmb_exp_tab(-s5 * r, tab);
+        const double lin = 1.0 + s5 * r;
+        kappa = (lin + (5.0 / 3.0) * r * r) * e;
+        gcoef = (-5.0 / 3.0) * lin * e;
+    } else if (kernel_id == NMB_KERNEL_MATERN32) {
+        const double s3 = 1.73205080756887729353;
+        const double e = nmb_exp_tab(-s3 * r, tab);
+        kappa = (1.0 + s3 * r) * e;
+        gcoef = -3.0 * e;
+    } else {
+        kappa = nmb_exp_tab(-r, tab);
+        gcoef = clamped ? 0.0 : -kappa / r;
+    }
+}
+
+// lookup tables of the table-driven transcendentals (fastmath.cuh); kernels copy them into shared memory
+static __device__ const double g_fast_tab[NMB_FAST_TAB_LEN] = NMB_FAST_TAB_INIT;
+__device__ __forceinline__ void load_fast_tab(double* __restrict__ dst, int tid, int nthr) {
+    for (int e = tid; e < NMB_FAST_TAB_LEN; e += nthr) dst[e] = g_fast_tab[e];
+}
+
 // ---------------------------------------------------------------- warp helpers
 template <typename T> __device__ __forceinline__ T shfl_xor_(T v, int m) {
     return __shfl_xor_sync(0xffffffffu, v, m);

@@ -15,6 +15,7 @@
 #include <math.h>
 #include <stdint.h>
 #include <string.h>
+#include "fast_tables.h"
 
 namespace nmb {
 
@@ -140,6 +141,99 @@ NMB_HD double nmb_tanh(double x) {
     x = fmin(fmax(x, -20.0), 20.0);
     const double em = nmb_expm1(2.0 * x);
     return em * nmb_rcp(em + 2.0);
+}
+
+
+// ---------------------------------------------------------------- table-driven variants
+// ncu (profiles/ncu_lines_r01b_fwd.txt, round 1 final): the Taylor kernels above still made the forward rollout
+// issue-bound - 57 warp instructions per sincospi and 67 per activation, 47 % of all instructions of the launch.
+// With a small table in shared memory (fast_tables.h: 2^(j/64), j < 64 and (sin, cos)(pi j/128), j < 256) the
+// reduced argument is 64 x / 128 x smaller and the polynomials shrink from degree 12 / 9+9 to 5 / 2+3:
+//   nmb_exp_tab / nmb_expm1_tab   12 FP64 ops + 1 LDS.64     |rel err| < 3e-16
+//   nmb_sincospi_tab              14 FP64 ops + 1 LDS.128    |abs err| < 3e-16
+// `tab` points at the NMB_FAST_TAB_LEN doubles of fast_tables.h (16-byte aligned).
+NMB_HD double exp_reduce_tab(double x, const double* __restrict__ tab, double& s) {
+    const double magic = 6755399441055744.0;     // 1.5 * 2^52
+    const double kd = fma(x, 92.33248261689366, magic);          // 64 / ln 2
+    const int ki = (int)(uint32_t)f64_bits(kd);
+    const double kf = kd - magic;
+    double r = fma(kf, -0.010830424696249145, x);                // ln 2 / 64, high part
+    r = fma(kf, -3.623510646634843e-19, r);                      // low part
+    // expm1(r), |r| <= ln2/128: r + r^2 (1/2 + r/6 + r^2/24 + r^3/120), next term r^6/720 < 4e-17
+    const double z = r * r;
+    double q = fma(8.333333333333333e-03, r, 4.1666666666666664e-02);
+    q = fma(q, r, 1.6666666666666666e-01);
+    q = fma(q, r, 0.5);
+    const double p = fma(q, z, r);
+    // s = 2^(ki/64) = tab[ki & 63] * 2^(ki >> 6): the exponent is added to the table entry's bits
+    s = bits_f64(f64_bits(tab[ki & 63]) + ((int64_t)(ki >> 6) << 52));
+    return p;
+}
+
+NMB_HD double nmb_exp_tab(double x, const double* __restrict__ tab) {
+    x = fmin(fmax(x, -700.0), 700.0);
+    double s;
+    const double p = exp_reduce_tab(x, tab, s);
+    return fma(s, p, s);
+}
+
+NMB_HD double nmb_expm1_tab(double x, const double* __restrict__ tab) {
+    x = fmin(fmax(x, -60.0), 700.0);
+    double s;
+    const double p = exp_reduce_tab(x, tab, s);
+    return fma(s, p, s - 1.0);
+}
+
+// sin(pi x), cos(pi x): x = j/128 + r, |r| <= 1/256 (exact); angle addition with the table entry of j mod 256
+NMB_HD void nmb_sincospi_tab(double x, const double* __restrict__ tab, double* sn, double* cs) {
+    const double magic = 6755399441055744.0;
+    const double kd = fma(x, 128.0, magic);
+    const int j = (int)(uint32_t)f64_bits(kd) & 255;
+    const double r = fma(kd - magic, -0.0078125, x);
+    const double z = r * r;
+#ifdef __CUDA_ARCH__
+    const double2 t = *reinterpret_cast<const double2*>(tab + 64 + 2 * j);
+    const double ts = t.x, tc = t.y;
+#else
+    const double ts = tab[64 + 2 * j], tc = tab[64 + 2 * j + 1];
+#endif
+    // s = sin(pi r) = r (pi - pi^3/6 z + pi^5/120 z^2)      (next term: 7e-16 relative to s, |s| < 0.0123)
+    double s = fma(2.5501640398773455, z, -5.16771278004997);
+    s = fma(s, z, 3.141592653589793);
+    s *= r;
+    // dc = cos(pi r) - 1 = z (-pi^2/2 + pi^4/24 z - pi^6/720 z^2)   (next term < 2e-20)
+    double dc = fma(-1.3352627688545895, z, 4.0587121264167685);
+    dc = fma(dc, z, -4.934802200544679);
+    dc *= z;
+    *sn = fma(ts, dc, fma(tc, s, ts));
+    *cs = fma(tc, dc, fma(-ts, s, tc));
+}
+
+NMB_HD double nmb_rcp2(double a) {      // 1 / a, a in [2^-500, 2^500]: rcp.approx (2^-23) + 2 Newton steps
+#ifdef __CUDA_ARCH__
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(a));
+    double e = fma(-a, r, 1.0);
+    r = fma(r, e, r);
+    e = fma(-a, r, 1.0);
+    return fma(r, e, r);
+#else
+    return 1.0 / a;
+#endif
+}
+
+NMB_HD double nmb_sigmoid_tab(double x, const double* __restrict__ tab) {
+    x = fmin(fmax(x, -40.0), 40.0);
+    return nmb_rcp(1.0 + nmb_exp_tab(-x, tab));
+}
+NMB_HD double nmb_tanh_tab(double x, const double* __restrict__ tab) {
+    x = fmin(fmax(x, -20.0), 20.0);
+    const double em = nmb_expm1_tab(2.0 * x, tab);
+    return em * nmb_rcp(em + 2.0);
+}
+NMB_HD double nmb_elu_tab(double x, const double* __restrict__ tab) {
+    const double e = nmb_expm1_tab(fmin(x, 0.0), tab);
+    return x > 0.0 ? x : e;
 }
 
 }  // namespace nmb

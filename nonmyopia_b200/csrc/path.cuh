@@ -32,9 +32,10 @@ template <typename T> inline PathDev<T> to_dev(const nmb_path_t& p) {
 
 // x: the point (registers, DMAX padded), s: path index, (lane, nl): this thread's slot
 // in its group.  Outputs are partial: y_part excludes mean_const.
-template <typename T, int DMAX, bool GRAD = true>
+// TAB (FP64 only): sincospi / exp through the shared-memory lookup tables at `tab` (fastmath.cuh).
+template <typename T, int DMAX, bool GRAD = true, bool TAB = false>
 __device__ __forceinline__ void path_partial(const PathDev<T>& P, const T (&x)[DMAX], int s, int lane,
-                                             int nl, T& y_part, T (&g_part)[DMAX]) {
+                                             int nl, T& y_part, T (&g_part)[DMAX], const double* __restrict__ tab = nullptr) {
     const int d = P.d;
     T acc = T(0);
     T gacc[DMAX];
@@ -55,7 +56,8 @@ __device__ __forceinline__ void path_partial(const PathDev<T>& P, const T (&x)[D
             u = fma(wk[k], x[k], u);
         }
         T sn, cs;
-        Num<T>::sincospi(u, &sn, &cs);
+        if constexpr (TAB) nmb_sincospi_tab(u, tab, &sn, &cs);
+        else Num<T>::sincospi(u, &sn, &cs);
         const T ws = __ldg(wsin + m), wc = __ldg(wcos + m);
         acc = fma(sn, ws, fma(cs, wc, acc));
         if (GRAD) {
@@ -88,7 +90,8 @@ __device__ __forceinline__ void path_partial(const PathDev<T>& P, const T (&x)[D
             r2 = fma(sd[k], sd[k], r2);
         }
         T kap, gc;
-        kernel_profile<T>(P.kernel_id, r2, kap, gc);
+        if constexpr (TAB) kernel_profile_tab(P.kernel_id, r2, tab, kap, gc);
+        else kernel_profile<T>(P.kernel_id, r2, kap, gc);
         const T vj = __ldg(vv + j);
         kacc = fma(kap, vj, kacc);
         if (GRAD) {

@@ -79,7 +79,7 @@ struct MmaRing {
 };
 
 struct MmaSmem {
-    double *IN, *OUT, *B0, *B1, *HA, *HB, *stage, *cost_acc;
+    double *IN, *OUT, *B0, *B1, *HA, *HB, *stage, *cost_acc, *tab;
     unsigned full0, empty0;     // shared addresses of the mbarrier arrays
     int rows, KS;
     __device__ void carve(double* base, int d, int H, int rows_) {
@@ -87,6 +87,7 @@ struct MmaSmem {
         KS = H + 4;
         double* p = base;
         stage = p; p += kStages * kStageElems;                 // 16-byte aligned bulk-copy destinations first
+        tab = p; p += NMB_FAST_TAB_LEN;
         B0 = p; p += rows * KS;
         B1 = p; p += rows * KS;
         HA = p; p += rows * KS;
@@ -104,7 +105,8 @@ struct MmaSmem {
         KS = H + 4;
         const int per_row = 4 * KS + 2 * d + 2;
         stage = base;
-        double* p = base + kStages * kStageElems + (size_t)row_off * per_row;
+        tab = base + kStages * kStageElems;
+        double* p = tab + NMB_FAST_TAB_LEN + (size_t)row_off * per_row;
         B0 = p; p += rows * KS;
         B1 = p; p += rows * KS;
         HA = p; p += rows * KS;
@@ -112,11 +114,12 @@ struct MmaSmem {
         IN = p; p += (d + 1) * rows;
         OUT = p; p += d * rows;
         cost_acc = p;
-        full0 = smem_u32(base + kStages * kStageElems + (size_t)rows_total * per_row);
+        full0 = smem_u32(tab + NMB_FAST_TAB_LEN + (size_t)rows_total * per_row);
         empty0 = full0 + 8 * kStages;
     }
     static size_t bytes(int d, int H, int rows) {
-        return ((size_t)kStages * kStageElems + (size_t)4 * rows * (H + 4) + (size_t)(2 * d + 2) * rows + 2 * kStages) * 8;
+        return ((size_t)kStages * kStageElems + NMB_FAST_TAB_LEN + (size_t)4 * rows * (H + 4) + (size_t)(2 * d + 2) * rows +
+                2 * kStages) * 8;
     }
     __device__ MmaRing ring() const { return MmaRing{stage, full0, empty0, KS}; }
 };
@@ -267,6 +270,10 @@ __device__ __forceinline__ void mma_policy_forward(const PolicyLayout& lay, cons
     const int d = lay.d, H = lay.H, rows = sm.rows, KS = sm.KS;
     const int tid = w.tid, nthr = w.nthr;
     const MmaRing ring = sm.ring();
+    const double* tab = sm.tab;
+    auto nmb_elu_tab_ = [tab](double x) { return nmb_elu_tab(x, tab); };
+    auto nmb_sigmoid_tab_ = [tab](double x) { return nmb_sigmoid_tab(x, tab); };
+    auto nmb_tanh_tab_ = [tab](double x) { return nmb_tanh_tab(x, tab); };
     // ---- embedding (K = d+1): B0 = elu(We [x;y] + be)
     {
         const double* Wt = theta_t + lay.off[S_WE];      // [d+1][H]
@@ -275,7 +282,7 @@ __device__ __forceinline__ void mma_policy_forward(const PolicyLayout& lay, cons
             const int r = e / H, o = e - r * H;
             double a = __ldg(b + o);
             for (int k = 0; k <= d; ++k) a = fma(sm.IN[k * rows + r], __ldg(Wt + k * H + o), a);
-            const double v = elu_(a);
+            const double v = nmb_elu_tab_(a);
             sm.B0[r * KS + o] = v;
             if (save && r < nvalid) save->EA[(node0 + r) * H + o] = v;
         }
@@ -299,7 +306,7 @@ __device__ __forceinline__ void mma_policy_forward(const PolicyLayout& lay, cons
         const int o = w.col0 + 8 * t + 2 * w.fk;
         if (o < H) {
             const double2 bb = __ldg(reinterpret_cast<const double2*>(theta_t + lay.off[S_BP] + o));
-            const double2 v = make_double2(elu_(acc[t][0] + bb.x), elu_(acc[t][1] + bb.y));
+            const double2 v = make_double2(nmb_elu_tab_(acc[t][0] + bb.x), nmb_elu_tab_(acc[t][1] + bb.y));
             *reinterpret_cast<double2*>(sm.B1 + row * KS + o) = v;
             if (save && rv) *reinterpret_cast<double2*>(save->P + nrow + o) = v;
         }
@@ -317,7 +324,7 @@ __device__ __forceinline__ void mma_policy_forward(const PolicyLayout& lay, cons
         for (int t = 0; t < 4; ++t) {
             const int o = min(w.col0 + 8 * t + 2 * w.fk, H - 2);
 #pragma unroll
-            for (int j = 0; j < 2; ++j) rg[t][j] = sigmoid_(acc[t][j] + __ldg(bih + o + j) + __ldg(bhh + o + j));
+            for (int j = 0; j < 2; ++j) rg[t][j] = nmb_sigmoid_tab_(acc[t][j] + __ldg(bih + o + j) + __ldg(bhh + o + j));
         }
         zero_acc4(acc);
         mma_gemm<kStages>(ring, w, sm.B1, H, acc);
@@ -326,7 +333,7 @@ __device__ __forceinline__ void mma_policy_forward(const PolicyLayout& lay, cons
         for (int t = 0; t < 4; ++t) {
             const int o = min(w.col0 + 8 * t + 2 * w.fk, H - 2);
 #pragma unroll
-            for (int j = 0; j < 2; ++j) zg[t][j] = sigmoid_(acc[t][j] + __ldg(bih + H + o + j) + __ldg(bhh + H + o + j));
+            for (int j = 0; j < 2; ++j) zg[t][j] = nmb_sigmoid_tab_(acc[t][j] + __ldg(bih + H + o + j) + __ldg(bhh + H + o + j));
         }
         zero_acc4(acc);
         zero_acc4(gh);
@@ -340,7 +347,7 @@ __device__ __forceinline__ void mma_policy_forward(const PolicyLayout& lay, cons
 #pragma unroll
                 for (int j = 0; j < 2; ++j) {
                     hn[j] = gh[t][j] + __ldg(bhh + 2 * H + o + j);
-                    ng[j] = Num<double>::tanh(acc[t][j] + __ldg(bih + 2 * H + o + j) + rg[t][j] * hn[j]);
+                    ng[j] = nmb_tanh_tab_(acc[t][j] + __ldg(bih + 2 * H + o + j) + rg[t][j] * hn[j]);
                     const double hp = hprev[row * KS + o + j];
                     hv[j] = (1.0 - zg[t][j]) * ng[j] + zg[t][j] * hp;
                 }
@@ -369,7 +376,7 @@ __device__ __forceinline__ void mma_policy_forward(const PolicyLayout& lay, cons
         const int o = w.col0 + 8 * t + 2 * w.fk;
         if (o < H) {
             const double2 bb = __ldg(reinterpret_cast<const double2*>(theta_t + lay.off[sB0] + o));
-            const double2 v = make_double2(elu_(acc[t][0] + bb.x), elu_(acc[t][1] + bb.y));
+            const double2 v = make_double2(nmb_elu_tab_(acc[t][0] + bb.x), nmb_elu_tab_(acc[t][1] + bb.y));
             *reinterpret_cast<double2*>(sm.B0 + row * KS + o) = v;
             if (save && rv) *reinterpret_cast<double2*>(save->U1 + nrow + o) = v;
         }
@@ -383,7 +390,7 @@ __device__ __forceinline__ void mma_policy_forward(const PolicyLayout& lay, cons
         const int o = w.col0 + 8 * t + 2 * w.fk;
         if (o < H) {
             const double2 bb = __ldg(reinterpret_cast<const double2*>(theta_t + lay.off[sB3] + o));
-            const double2 v = make_double2(elu_(acc[t][0] + bb.x), elu_(acc[t][1] + bb.y));
+            const double2 v = make_double2(nmb_elu_tab_(acc[t][0] + bb.x), nmb_elu_tab_(acc[t][1] + bb.y));
             *reinterpret_cast<double2*>(hprev + row * KS + o) = v;
             if (save && rv) *reinterpret_cast<double2*>(save->U2 + nrow + o) = v;
         }
@@ -407,7 +414,7 @@ __device__ __forceinline__ void mma_policy_forward(const PolicyLayout& lay, cons
             a += __shfl_xor_sync(0xffffffffu, a, 1);
             a += __shfl_xor_sync(0xffffffffu, a, 2);
             if (ok && sub == 0) {
-                const double v = sigmoid_(a + __ldg(b + o));
+                const double v = nmb_sigmoid_tab_(a + __ldg(b + o));
                 sm.OUT[o * rows + r] = v;
                 if (save && r < nvalid) save->OUT[(node0 + r) * d + o] = v;
             }

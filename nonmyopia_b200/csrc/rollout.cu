@@ -39,6 +39,10 @@ template <typename T> struct RolloutDev {
     T *X, *A, *Y, *loss, *cost;
     SaveAreas<T> sv;
     int has_save;
+    const float2* ring_cs;
+    const int* ring_dims;
+    const T* ring_noise;
+    int ring_len;
 };
 
 template <typename T> struct ProblemDev {
@@ -51,6 +55,7 @@ template <typename T> struct ProblemDev {
     unsigned long long seed;
     const long long* step_ptr;
     const int* done_flag;
+    long long chain_offset;
 };
 
 // rotation block + coordinate pair of (call, chain): given tensors or in-kernel draws that
@@ -58,13 +63,21 @@ template <typename T> struct ProblemDev {
 template <typename T>
 __device__ __forceinline__ void get_rotation(const RolloutDev<T>& ro, const ProblemDev<T>& pb, long long step, int call,
                                              long long chain, T (&q)[4], int& di, int& dj) {
-    if (ro.rot_q) {
+    if (ro.ring_len > 0) {
+        // host-stream ring: slot of this Adam iteration, float32 (cos, sin) as the reference rounds them
+        const size_t idx = ((size_t)(step % ro.ring_len) * (pb.L + 1) + call) * pb.N + chain;
+        const float2 cs = ro.ring_cs[idx];
+        q[0] = (T)cs.x; q[1] = (T)(-cs.y); q[2] = (T)cs.y; q[3] = (T)cs.x;
+        const int2 dd = reinterpret_cast<const int2*>(ro.ring_dims)[idx];
+        di = dd.x; dj = dd.y;
+    } else if (ro.rot_q) {
         const T* p = ro.rot_q + ((size_t)call * pb.N + chain) * 4;
         q[0] = p[0]; q[1] = p[1]; q[2] = p[2]; q[3] = p[3];
         const int* dd = ro.rot_dims + ((size_t)call * pb.N + chain) * 2;
         di = dd[0]; dj = dd[1];
     } else {
-        const uint4 r = philox4x32_10(make_uint4((unsigned)chain, (unsigned)(chain >> 32), (unsigned)step,
+        const long long gc = chain + pb.chain_offset;       // global chain index: shard-invariant stream
+        const uint4 r = philox4x32_10(make_uint4((unsigned)gc, (unsigned)(gc >> 32), (unsigned)step,
                                                  (ro.rng_stream << 8) | (unsigned)call),
                                       make_uint2((unsigned)pb.seed, (unsigned)(pb.seed >> 32)));
         const float u = (float)(r.x >> 8) * (1.0f / 16777216.0f);
@@ -79,8 +92,11 @@ __device__ __forceinline__ void get_rotation(const RolloutDev<T>& ro, const Prob
 template <typename T>
 __device__ __forceinline__ T get_cost_noise(const RolloutDev<T>& ro, const ProblemDev<T>& pb, long long step, int call,
                                             long long chain) {
+    if (ro.ring_len > 0)
+        return ro.ring_noise[((size_t)(step % ro.ring_len) * (pb.L + 1) + call) * pb.N + chain];
     if (ro.cost_noise) return ro.cost_noise[(size_t)call * pb.N + chain];
-    const uint4 r = philox4x32_10(make_uint4((unsigned)chain, (unsigned)(chain >> 32), (unsigned)step,
+    const long long gc = chain + pb.chain_offset;
+    const uint4 r = philox4x32_10(make_uint4((unsigned)gc, (unsigned)(gc >> 32), (unsigned)step,
                                              0x80000000u | (ro.rng_stream << 8) | (unsigned)call),
                                   make_uint2((unsigned)pb.seed, (unsigned)(pb.seed >> 32)));
     const double u1 = ((double)r.x * 4294967296.0 + (double)r.y + 1.0) * (1.0 / 18446744073709551616.0);
@@ -235,6 +251,7 @@ __global__ void __launch_bounds__(kMaxRowsMma * 8 + 32, 1)
         }
         fence_barrier_init();
     }
+    load_fast_tab(sm.tab, (int)threadIdx.x, (int)blockDim.x);
     __syncthreads();
     if ((int)threadIdx.x >= nthr_all) {      // producer warp
         mma_producer<kStages, false>(pb.lay, ro.theta_t, L, sm.ring());
@@ -301,8 +318,8 @@ __global__ void __launch_bounds__(kMaxRowsMma * 8 + 32, 1)
 #pragma unroll
         for (int k = 0; k < DMAX; ++k) gp[k] = T(0);
         if (live) {
-            if (ro.has_save) path_partial<T, DMAX, true>(pb.path, pt, (int)(chain / pb.cpp), lane, 8, yp, gp);
-            else path_partial<T, DMAX, false>(pb.path, pt, (int)(chain / pb.cpp), lane, 8, yp, gp);
+            if (ro.has_save) path_partial<T, DMAX, true, true>(pb.path, pt, (int)(chain / pb.cpp), lane, 8, yp, gp, sm.tab);
+            else path_partial<T, DMAX, false, true>(pb.path, pt, (int)(chain / pb.cpp), lane, 8, yp, gp, sm.tab);
         }
         yp = group_sum(yp, 8);
         if (ro.has_save) {
@@ -592,6 +609,7 @@ template <typename T> static ProblemDev<T> make_problem(const nmb_ts_problem_t& 
     o.lay.init(p.d, p.H, 1);
     o.prev_x = (const T*)p.prev_x; o.prev_y = (const T*)p.prev_y; o.prev_h = (const T*)p.prev_h;
     o.seed = p.seed; o.step_ptr = (const long long*)p.step_ptr; o.done_flag = p.done_flag;
+    o.chain_offset = p.chain_offset;
     return o;
 }
 
@@ -602,6 +620,8 @@ template <typename T> static RolloutDev<T> make_rollout(const nmb_ts_problem_t& 
     o.rot_q = (const T*)r.rot_q; o.rot_dims = r.rot_dims; o.cost_noise = (const T*)r.cost_noise;
     o.rng_stream = r.rng_stream;
     o.X = (T*)r.X; o.A = (T*)r.A; o.Y = (T*)r.Y; o.loss = (T*)r.loss; o.cost = (T*)r.cost;
+    o.ring_cs = (const float2*)r.ring_cs; o.ring_dims = r.ring_dims; o.ring_noise = (const T*)r.ring_noise;
+    o.ring_len = r.ring_cs ? r.ring_len : 0;
     o.has_save = r.save != nullptr;
     if (r.save) o.sv = carve_save<T>(r.save, p.d, p.H, p.L, p.n_chains);
     else memset(&o.sv, 0, sizeof(o.sv));
@@ -732,6 +752,8 @@ extern "C" int nmb_ts_rollout_fwd(const nmb_ts_problem_t* prob, const nmb_ts_rol
                     "nmb_ts_rollout_fwd: rollout %d has null theta_t/outputs", i);
         NMB_REQUIRE((r.rot_q == nullptr) == (r.rot_dims == nullptr), NMB_EINVAL,
                     "nmb_ts_rollout_fwd: rot_q and rot_dims must be given together");
+        NMB_REQUIRE(r.ring_cs == nullptr || (r.ring_dims && r.ring_noise && r.ring_len > 0 && prob->step_ptr), NMB_EINVAL,
+                    "nmb_ts_rollout_fwd: the host-stream ring needs ring_dims, ring_noise, ring_len > 0 and step_ptr");
     }
     cudaStream_t st = (cudaStream_t)stream;
     if (mma_fwd_ok(prob, rollouts, n_rollouts)) {

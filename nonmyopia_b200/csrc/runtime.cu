@@ -83,7 +83,42 @@ template <typename T, int WHICH> static int run_peak(double* host_result) {
     return 0;
 }
 
+// ---- device-side evaluation of the fastmath.cuh kernels (accuracy tests: rcp.approx only exists on the device)
+__global__ void fastmath_probe_kernel(int which, const double* __restrict__ x, double* __restrict__ y0,
+                                      double* __restrict__ y1, long long n) {
+    __shared__ __align__(16) double tab[NMB_FAST_TAB_LEN];
+    load_fast_tab(tab, threadIdx.x, blockDim.x);
+    __syncthreads();
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const double v = x[i];
+    double a = 0.0, b = 0.0;
+    switch (which) {
+        case 0: a = nmb_exp_tab(v, tab); b = nmb_exp(v); break;
+        case 1: a = nmb_expm1_tab(v, tab); b = nmb_expm1(v); break;
+        case 2: nmb_sincospi_tab(v, tab, &a, &b); break;
+        case 3: a = nmb_sigmoid_tab(v, tab); b = nmb_sigmoid(v); break;
+        case 4: a = nmb_tanh_tab(v, tab); b = nmb_tanh(v); break;
+        case 5: a = nmb_rcp2(v); b = nmb_rcp(v); break;
+        case 6: a = nmb_elu_tab(v, tab); b = elu_<double>(v); break;
+        default: nmb_sincospi(v, &a, &b); break;
+    }
+    y0[i] = a;
+    y1[i] = b;
+}
+
 }  // namespace nmb
+
+extern "C" int nmb_fastmath_probe(int which, const void* x, void* y0, void* y1, int64_t n, void* stream) {
+    using namespace nmb;
+    NMB_REQUIRE(x && y0 && y1 && n >= 0, NMB_EINVAL, "nmb_fastmath_probe: null argument");
+    NMB_REQUIRE(which >= 0 && which <= 7, NMB_EINVAL, "nmb_fastmath_probe: which=%d", which);
+    if (n == 0) return 0;
+    fastmath_probe_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+        which, (const double*)x, (double*)y0, (double*)y1, (long long)n);
+    NMB_LAUNCH_CHECK();
+    return 0;
+}
 
 extern "C" const char* nmb_last_error(void) { return nmb::g_err; }
 extern "C" int nmb_version(void) { return 100; }

@@ -282,8 +282,14 @@ def baseline_forward(acqf, prev_X: Tensor, maps, prev_cost: float, draws=None):
         lv = [Xa.reshape(n_r, d), Xf.permute(1, 0, 2).reshape(nfant * n_r, d)]
         mean_leaf, _ = tree.leaf_posterior(lv)
         acqf_loss = -tree.restart_mean(mean_leaf)
-        nz = draws if draws is not None else [torch.randn(n_r, 1, 1, dtype=dt, device=dev),
-                                              torch.randn(n_r, nfant, nfant, dtype=dt, device=dev)]
+        if draws is not None:
+            nz = draws
+        elif acqf._fed_noise is not None or acqf.rng_mode == "host":
+            from .acqfs import _host_cost_noise
+            flat = acqf._fed_noise if acqf._fed_noise is not None else _host_cost_noise(acqf.cost_noise_sizes(n_r), prev_X)
+            nz = [flat[:n_r].reshape(n_r, 1, 1), flat[n_r:].reshape(n_r, nfant, nfant)]
+        else:
+            nz = [torch.randn(n_r, 1, 1, dtype=dt, device=dev), torch.randn(n_r, nfant, nfant, dtype=dt, device=dev)]
         pX = prev_X[:, None, :]
         cost = _cost_pairwise(acqf.cost_function, pX.expand_as(Xa), Xa, nz[0], prev_cost)
         cost = cost + _cost_pairwise(acqf.cost_function, Xa.expand_as(Xf), Xf, nz[1], cost + prev_cost)
@@ -305,7 +311,15 @@ def baseline_forward(acqf, prev_X: Tensor, maps, prev_cost: float, draws=None):
         value = _UtilityFn.apply(mean, sig, base, which, acqf.best_f if acqf.best_f is not None else 0.0,
                                  getattr(acqf, "beta", 0.0))
         acqf_loss = -value
-        noise = draws if draws is not None else torch.randn(n_r, dtype=dt, device=dev)
+        if draws is not None:
+            noise = draws
+        elif acqf._fed_noise is not None:
+            noise = acqf._fed_noise
+        elif acqf.rng_mode == "host":
+            from .acqfs import _host_cost_noise
+            noise = _host_cost_noise([n_r], prev_X)
+        else:
+            noise = torch.randn(n_r, dtype=dt, device=dev)
         acqf_cost = _TreeCostFn.apply(prev_X, noise.reshape(-1).contiguous(), hyp, prev_cost, pts)
         X_ret = [actions]
     return {"acqf_loss": acqf_loss, "acqf_cost": acqf_cost, "X": X_ret, "actions": actions, "hidden_state": None}

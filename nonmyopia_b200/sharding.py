@@ -141,7 +141,8 @@ def broadcast_from_owner(t: Optional[Tensor], shape, dtype, device, owner: int, 
 def free_restart_loop(objective: Callable[[List[Tensor]], Dict], params: List[Tensor],
                       opt_step: Callable[[Sequence[Optional[Tensor]]], None], *, budget: float, n_iter: int,
                       past_initial: bool, n_global: Optional[int] = None, group=None, save_trajectory: bool = False,
-                      log: Optional[Callable[[str], None]] = print, use_graph: bool = False) -> Dict:
+                      log: Optional[Callable[[str], None]] = print, use_graph: bool = False,
+                      pre_iteration: Optional[Callable[[], None]] = None) -> Dict:
     """The reference's AdamW loop for free-parameter algorithms (actor.py:558-656; HES-TS, HES-MC, qEI ... qKG)
     over this rank's restarts.
 
@@ -153,7 +154,9 @@ def free_restart_loop(objective: Callable[[List[Tensor]], Dict], params: List[Te
     ``use_graph`` (CUDA only): after two eager iterations the device work of one iteration - sigmoid, objective,
     backward, AdamW, the two decision minima - is captured once and replayed as a CUDA graph; the host still reads
     the minima every iteration for the reference's snapshot / early-stop rule (one synchronisation per iteration
-    instead of ~100 eager launches).  Requires an objective without per-call host randomness."""
+    instead of ~100 eager launches).  Requires an objective without per-call host randomness: host-stream draws
+    are made resident by ``pre_iteration()`` (called before every iteration, eager or replayed) in a static device
+    buffer the objective reads."""
     best = dict(loss=None, cost=None, KL=0)
     best_min = float("inf")
     snap, stall = {}, 0
@@ -177,6 +180,8 @@ def free_restart_loop(objective: Callable[[List[Tensor]], Dict], params: List[Te
     if use_graph:
         side = torch.cuda.Stream(device=params[0].device)
     for ep in range(n_iter):
+        if pre_iteration is not None:
+            pre_iteration()
         if use_graph and ep >= warm and graph is not False:
             if graph is None:
                 try:

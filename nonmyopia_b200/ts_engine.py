@@ -66,7 +66,8 @@ class ProblemStruct(C.Structure):
                 ("n_chains", C.c_int64), ("chains_per_path", C.c_int64),
                 ("path", C.POINTER(_lib.PathStruct)), ("cost", CostStruct),
                 ("prev_x", C.c_void_p), ("prev_y", C.c_void_p), ("prev_h", C.c_void_p),
-                ("seed", C.c_uint64), ("step_ptr", C.c_void_p), ("done_flag", C.c_void_p)]
+                ("seed", C.c_uint64), ("step_ptr", C.c_void_p), ("done_flag", C.c_void_p),
+                ("chain_offset", C.c_int64)]
 
 
 class RolloutStruct(C.Structure):
@@ -75,7 +76,9 @@ class RolloutStruct(C.Structure):
                 ("rot_q", C.c_void_p), ("rot_dims", C.c_void_p), ("cost_noise", C.c_void_p),
                 ("rng_stream", C.c_uint32), ("_pad", C.c_uint32),
                 ("X", C.c_void_p), ("A", C.c_void_p), ("Y", C.c_void_p), ("loss", C.c_void_p),
-                ("cost", C.c_void_p), ("save", C.c_void_p)]
+                ("cost", C.c_void_p), ("save", C.c_void_p),
+                ("ring_cs", C.c_void_p), ("ring_dims", C.c_void_p), ("ring_noise", C.c_void_p),
+                ("ring_len", C.c_int32), ("_pad2", C.c_int32)]
 
 
 class LoopState(C.Structure):
@@ -144,6 +147,7 @@ class TSRollout:
         self.seg_splits = (C.c_int32 * 20)()
         self.step_ptr = None
         self.done_ptr = None
+        self.chain_offset = 0       # global index of this rank's first chain (restarts sharded over GPUs)
 
     # ---- struct builders
     def problem(self, prev_x: Tensor, prev_y: Tensor, prev_h: Tensor, prev_cost: float = 0.0) -> ProblemStruct:
@@ -152,12 +156,17 @@ class TSRollout:
             dtype=self.dt, d=self.d, H=self.H, L=self.L, n_chains=self.N, chains_per_path=self.cpp,
             path=C.pointer(self._path_struct), cost=cost_struct(self.cost_hypers, prev_cost),
             prev_x=prev_x.data_ptr(), prev_y=prev_y.data_ptr(), prev_h=prev_h.data_ptr(), seed=self.seed,
-            step_ptr=self.step_ptr or 0, done_flag=self.done_ptr or 0)
+            step_ptr=self.step_ptr or 0, done_flag=self.done_ptr or 0, chain_offset=int(self.chain_offset))
 
     def rollout_struct(self, buf: RolloutBuffers, theta: Optional[Tensor], theta_t: Tensor, noisy_design: bool,
                        rot_q: Optional[Tensor] = None, rot_dims: Optional[Tensor] = None,
-                       cost_noise: Optional[Tensor] = None, rng_stream: int = 0) -> RolloutStruct:
+                       cost_noise: Optional[Tensor] = None, rng_stream: int = 0, ring=None) -> RolloutStruct:
+        """``ring`` = (cs [R, L+1, N, 2] float32, dims [R, L+1, N, 2] int32, noise [R, L+1, N]) device tensors of the
+        host-stream ring (see ``nmb_ts_rollout_t``); iteration ``*step_ptr`` reads slot ``step % R``."""
+        rc, rd, rn = ring if ring is not None else (None, None, None)
         return RolloutStruct(
+            ring_cs=rc.data_ptr() if rc is not None else 0, ring_dims=rd.data_ptr() if rd is not None else 0,
+            ring_noise=rn.data_ptr() if rn is not None else 0, ring_len=int(rc.shape[0]) if rc is not None else 0,
             theta=theta.data_ptr() if theta is not None else 0, theta_t=theta_t.data_ptr(),
             noisy_design=int(noisy_design), noisy_action=1,
             rot_q=rot_q.data_ptr() if rot_q is not None else 0,

@@ -13,11 +13,19 @@ graph and replayed with no host synchronisation; the host only polls the ``done`
 every few replays.  The reference synchronises four times per iteration
 (actor.py:580-581, 618-619).
 
-Random numbers.  The reference consumes the CPU generator inside every noisy policy call
-(per-sample ``randperm``) and the device generator inside every cost call.  ``draws=None``
-(default, fast) draws statistically identical numbers in-kernel (Philox keyed by seed,
-iteration, call, chain); passing per-iteration draw tensors reproduces a recorded stream
-bit for bit (parity tests) at the price of one eager launch sequence per iteration.
+Random numbers.  The reference consumes the global CPU generator inside every noisy policy
+call (``rand`` + per-sample ``randperm``, amortized_network.py:136,156) and inside every cost call
+(``randn_like``, acqfs.py:624).  Three modes:
+
+* ``rng="host"``: the reference's exact stream at CUDA-graph speed.  ``HostStreamRing`` walks the
+  generator ahead of the loop in chunks (``nmb_host_rng_ts_am_stream``: torch's mt19937 stream bit
+  for bit), uploads each chunk into one half of a device ring while the previous chunk computes,
+  and the captured graph indexes the ring by the device step counter.  After the loop the torch
+  generator is left exactly where the reference's loop would have left it (early stop included).
+* ``rng="device"``: statistically equivalent draws in-kernel (Philox keyed by seed, iteration,
+  call, GLOBAL chain index), no host work at all.
+* explicit per-iteration draw tensors (``run(draws_per_iter=...)``): recorded streams of the
+  golden fixtures, one eager launch sequence per iteration.
 """
 from __future__ import annotations
 
@@ -29,6 +37,115 @@ from torch import Tensor
 
 from . import _lib
 from . import ts_engine as te
+from .host_rng import CpuStream
+
+
+class HostStreamRing:
+    """Double-buffered device ring of the per-iteration draws of HES-TS-AM in the reference's generator order.
+
+    Chunk ``c`` = iterations ``[c K, (c + 1) K)`` lives in ring slots ``(c & 1) K ...``; it is generated on a host
+    thread while chunk ``c - 1`` computes, staged in pinned memory and copied on a side stream.  ``n_global`` restarts
+    are drawn (every rank walks the same stream) and the rank's slice ``own = (lo, hi)`` is uploaded."""
+
+    def __init__(self, eng: te.TSRollout, n_global: int, own, chunk: int = 16, generator=None):
+        import threading
+        self._threading = threading
+        self.L, self.d, self.N, self.Ng = eng.L, eng.d, eng.N, int(n_global)
+        self.lo, self.hi = own
+        assert self.hi - self.lo == self.N, (own, self.N)
+        self.K = K = int(chunk)
+        self.dtype, dev, c, N = eng.dtype, eng.device, eng.L + 1, eng.N
+        ring = lambda: (torch.zeros(2 * K, c, N, 2, dtype=torch.float32, device=dev),
+                        torch.zeros(2 * K, c, N, 2, dtype=torch.int32, device=dev),
+                        torch.zeros(2 * K, c, N, dtype=eng.dtype, device=dev))
+        self.main, self.orig = ring(), ring()
+        pin = lambda *shape, dt: torch.zeros(*shape, dtype=dt).pin_memory()
+        self.stage = [dict(main=(pin(K, c, N, 2, dt=torch.float32), pin(K, c, N, 2, dt=torch.int32),
+                                 pin(K, c, N, dt=eng.dtype)),
+                           orig=(pin(K, c, N, 2, dt=torch.float32), pin(K, c, N, 2, dt=torch.int32),
+                                 pin(K, c, N, dt=eng.dtype)), raw={}) for _ in range(2)]
+        self.cpu = CpuStream(generator)
+        self.start_states = {0: self.cpu.state.copy()}      # chunk index -> generator state before the chunk
+        self.copy_stream = torch.cuda.Stream(device=dev)
+        self.ready = [None, None]       # upload of the chunk in half h has landed
+        self.free = [None, None]        # the replays that read half h have run
+        self._thread, self._generated = None, -1
+        self.bytes_per_iter = c * N * (2 * (8 + 8) + 2 * (8 if eng.dtype == torch.float64 else 4))
+
+    # ---- host side
+    def _generate(self, c: int) -> None:
+        st = self.stage[c & 1]
+        raw = self.cpu.ts_am_stream(self.K, self.L, self.Ng, self.d, out=st["raw"])
+        self.start_states[c + 1] = self.cpu.state.copy()
+        lo, hi, L = self.lo, self.hi, self.L
+        # float32 angle, cos and sin in the reference's op order (amortized_network.py:136,144-153)
+        th = (raw["u_main"][:, lo:hi] * 2 * torch.pi - torch.pi).contiguous()
+        mcs, mdim, mnz = st["main"]
+        mcs[:, L, :, 0], mcs[:, L, :, 1] = torch.cos(th), torch.sin(th)
+        mdim[:, L] = raw["dims_main"][:, lo:hi]
+        mnz.copy_(raw["nz_main"][:, :, lo:hi])
+        th = (raw["u_orig"][:, :, lo:hi] * 2 * torch.pi - torch.pi).contiguous()
+        ocs, odim, onz = st["orig"]
+        ocs[..., 0], ocs[..., 1] = torch.cos(th), torch.sin(th)
+        odim.copy_(raw["dims_orig"][:, :, lo:hi])
+        onz.copy_(raw["nz_orig"][:, :, lo:hi])
+        self._generated = c
+
+    def _start_generate(self, c: int) -> None:
+        h = c & 1
+        if self.ready[h] is not None:
+            self.ready[h].synchronize()      # the staging set of chunk c - 2 has been copied out
+        self._thread = self._threading.Thread(target=self._generate, args=(c,), daemon=True)
+        self._thread.start()
+
+    def feed(self, ep: int) -> None:
+        """Call before enqueueing iteration ``ep``: at a chunk boundary make the chunk's draws resident (generated
+        ahead on the host thread), start generating the next chunk, and order the main stream behind the upload."""
+        if ep % self.K:
+            return
+        c, h, K = ep // self.K, (ep // self.K) & 1, self.K
+        if self._thread is not None:
+            self._thread.join()
+            self._thread = None
+        if self._generated < c:
+            if self.ready[h] is not None:
+                self.ready[h].synchronize()
+            self._generate(c)
+        main = torch.cuda.current_stream()
+        with torch.cuda.stream(self.copy_stream):
+            if self.free[h] is not None:
+                self.copy_stream.wait_event(self.free[h])
+            for ring, key in ((self.main, "main"), (self.orig, "orig")):
+                for dst, src in zip(ring, self.stage[h][key]):
+                    dst[h * K:(h + 1) * K].copy_(src, non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(self.copy_stream)
+            self.ready[h] = ev
+        self._start_generate(c + 1)
+        main.wait_event(ev)
+
+    def chunk_enqueued(self, ep_last: int) -> None:
+        """Call after enqueueing the last iteration of a chunk (or of the run): its ring half may be refilled once
+        the work enqueued so far has run."""
+        h = (ep_last // self.K) & 1
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream())
+        self.free[h] = ev
+
+    def finish(self, n_done: int) -> None:
+        """Leave the torch generator where the reference's loop leaves it after ``n_done`` iterations."""
+        if self._thread is not None:
+            self._thread.join()
+            self._thread = None
+        c0 = n_done // self.K
+        while c0 not in self.start_states:      # loop ended before this chunk was ever needed
+            self._generate(max(self.start_states) )
+        tail = CpuStream(self.cpu.generator)
+        tail.state = self.start_states[c0].copy()
+        rem = n_done - c0 * self.K
+        if rem:
+            tail.ts_am_stream(rem, self.L, self.Ng, self.d)
+        tail.commit()
 
 
 class TSAMLoop:
@@ -36,7 +153,10 @@ class TSAMLoop:
                  budget: float, lr: float, past_initial: bool, prev_cost: float = 0.0, n_global: Optional[int] = None,
                  max_iter: int = 500, record_history: bool = False, record_trajectory: bool = False,
                  patience: int = 50, betas=(0.9, 0.999), eps: float = 1e-8,
-                 weight_decay: float = 1e-2, group=None, exchange: str = "auto"):
+                 weight_decay: float = 1e-2, group=None, exchange: str = "auto", rng: str = "device",
+                 own=None, chunk: int = 16, generator=None):
+        if rng not in ("device", "host"):
+            raise ValueError(f"rng={rng!r}")
         self.eng = eng
         d, H, L, N = eng.d, eng.H, eng.L, eng.N
         dt, dev = eng.dtype, eng.device
@@ -76,6 +196,10 @@ class TSAMLoop:
         self._dst = (C.c_void_p * 6)(*[t.data_ptr() for t in dsts])
         self._cnt = (C.c_int64 * 6)(*[t.numel() for t in srcs])
         self.graph = None
+        # host-stream ring (the reference's generator order at graph speed); own = this rank's restarts of n_global
+        self.ring = None
+        if rng == "host":
+            self.ring = HostStreamRing(eng, self.n_global, own if own is not None else (0, N), chunk, generator)
         # process group over which the restarts are sharded (None: single GPU)
         self.group = group
         self.px, self.exchange = None, "none"
@@ -108,7 +232,10 @@ class TSAMLoop:
         mark = mark or (lambda name: None)
         eng, lib = self.eng, self.eng.lib
         st = _lib.stream_ptr()
-        if draws is None:
+        if draws is None and self.ring is not None:
+            rm = eng.rollout_struct(self.main, self.theta, self.theta_t, noisy_design=False, ring=self.ring.main)
+            ro = eng.rollout_struct(self.orig, self.theta0, self.theta0_t, noisy_design=True, ring=self.ring.orig)
+        elif draws is None:
             rm = eng.rollout_struct(self.main, self.theta, self.theta_t, noisy_design=False, rng_stream=0)
             ro = eng.rollout_struct(self.orig, self.theta0, self.theta0_t, noisy_design=True, rng_stream=1)
         else:
@@ -209,18 +336,27 @@ class TSAMLoop:
             return self.read_state()
         if use_graph:
             self.capture()
+        if self.ring is not None:
+            poll_every = self.ring.K        # one poll per ring chunk
         ep = 0
         while ep < n_iter:
             k = min(poll_every, n_iter - ep)
-            for _ in range(k):
+            for i in range(k):
+                if self.ring is not None:
+                    self.ring.feed(ep + i)
                 if use_graph:
                     self.graph.replay()
                 else:
                     self._iteration()
             ep += k
+            if self.ring is not None:
+                self.ring.chunk_enqueued(ep - 1)
             if self.read_state().done:
                 break
-        return self.read_state()
+        st = self.read_state()
+        if self.ring is not None:
+            self.ring.finish(int(st.step))
+        return st
 
     def _enable_alt_inputs(self) -> None:
         """Second set of input buffers with its own captured graph, so the host can copy the NEXT step's inputs
@@ -249,6 +385,9 @@ class TSAMLoop:
         on a side stream into the other input-buffer set while this iteration runs (every step's copy still happens,
         it just no longer sits in front of the kernels)."""
         main = torch.cuda.current_stream()
+        if self.ring is not None:
+            ep = self._host_steps = getattr(self, "_host_steps", -1) + 1
+            self.ring.feed(ep)
         alt = self._alt
         if next_inputs is not None and alt is None and self.graph is not None:
             self._enable_alt_inputs()
@@ -280,6 +419,8 @@ class TSAMLoop:
                 alt["which"], alt["staged"] = 1 - which, True
         host_out[0].copy_(self.main.loss, non_blocking=True)
         host_out[1].copy_(self.main.cost, non_blocking=True)
+        if self.ring is not None and (self._host_steps + 1) % self.ring.K == 0:
+            self.ring.chunk_enqueued(self._host_steps)
         main.synchronize()
 
     # ------------------------------------------------------------------ results (actor.py:661-733)
