@@ -6,8 +6,8 @@
  * acqfs.py / actor.py / amortized_network.py.  The host-side mirror
  * of those classes lives in nonmyopia_b200/{acqfs,actor,amortized_network}.py and
  * reaches the GPU only through the entry points declared here (ctypes binding in
- * nonmyopia_b200/_lib.py; the C++ torch.library layer in csrc/torch_ops.cpp calls
- * the same symbols).  Each entry point names the reference code it replaces.
+ * nonmyopia_b200/_lib.py + torch.autograd.Function nodes; there is no C++ torch.library
+ * shim).  Each entry point names the reference code it replaces.
  *
  * Conventions
  *  - every pointer is a DEVICE pointer unless the name says host; tensors are dense
@@ -191,6 +191,13 @@ int nmb_ts_rollout_fwd(const nmb_ts_problem_t* prob, const nmb_ts_rollout_t* rol
  * g_prev (optional) receives [N][d+1+H] adjoints of (prev_x, prev_y, prev_h). */
 int nmb_ts_rollout_bwd(const nmb_ts_problem_t* prob, const nmb_ts_rollout_t* rollout, const void* g_loss,
                        const void* g_cost, const void* g_X, const void* g_A, void* g_prev, void* stream);
+
+/* Test hook: the in-kernel ("device" rng mode) draws of Adam iteration `step`, exactly as the rollout kernels make
+ * them (same device functions): cs [n_calls][N][2] = (cos, sin) of the rotation angle (amortized_network.py:136,
+ * 144-153), dims [n_calls][N][2] = the coordinate pair (amortized_network.py:156), noise [n_calls][N] = the N(0,1)
+ * draw of the cost call (acqfs.py:624).  Keyed by (seed, step, rng_stream, call, chain_offset + chain). */
+int nmb_ts_device_draws(uint64_t seed, int64_t step, unsigned rng_stream, int n_calls, int64_t n_chains,
+                        int64_t chain_offset, int d, double* cs, int32_t* dims, double* noise, void* stream);
 
 /* Weight gradients of a saved+back-propagated rollout: split-K GEMMs over all nodes.
  * partials: [n_splits_max][n_params]; seg_splits[20] (host, out) = how many leading

@@ -65,6 +65,9 @@ class qCostFunction(nn.Module):
         self.register_buffer("radius", torch.as_tensor(radius))
         self.k, self.max_noise, self.p_norm = k, max_noise, p_norm
         self.discount, self.discount_threshold = discount, discount_threshold
+        # "host": the noise of a stand-alone call comes from torch's global CPU generator, as in the reference run on
+        # the CPU (seed-stream parity, actor.py:715); "device": the CUDA generator.  Set by the owning acquisition.
+        self.rng_mode = "host"
 
     def hypers(self) -> dict:
         return dict(radius=float(self.radius), k=self.k, max_noise=self.max_noise, p_norm=self.p_norm,
@@ -72,7 +75,11 @@ class qCostFunction(nn.Module):
 
     def forward(self, prev_X: Tensor, current_X: Tensor, previous_cost=None) -> Tensor:
         dist = torch.cdist(current_X, prev_X, p=self.p_norm)
-        hinge = torch.clamp_min(self.k * (dist - self.radius), 0.0) + torch.randn_like(dist) * self.max_noise
+        if self.rng_mode == "host" and dist.is_cuda:
+            noise = torch.randn(dist.shape, dtype=dist.dtype).to(dist.device)
+        else:
+            noise = torch.randn_like(dist)
+        hinge = torch.clamp_min(self.k * (dist - self.radius), 0.0) + noise * self.max_noise
         if self.discount > 0.0:
             over = (previous_cost + hinge > self.discount_threshold).float()
             hinge = hinge * (1 - self.discount * over)
@@ -277,6 +284,7 @@ class qMultiStepHEntropySearch(nn.Module):
         # order (seed-stream parity; Actor.query feeds them through a device ring at CUDA-graph speed);
         # "device": drawn in-kernel (Philox keyed by rng_seed, iteration, call and global chain index)
         self.rng_mode = kwargs.get("rng_mode", "host")
+        self.cost_function.rng_mode = self.rng_mode
         self.rng_seed = None
         self._calls = 0
         self._gp = None
@@ -364,7 +372,7 @@ class qMultiStepHEntropySearch(nn.Module):
             if l == L or noisy_design:
                 Q, dims = draw_rotation(N, d, like)
                 rq[l], rd[l] = Q.reshape(N, 4), dims
-        cn = torch.stack([torch.randn(N, 1, 1, dtype=like.dtype).reshape(N) for _ in range(L + 1)]).to(like.device)
+        cn = _host_cost_noise([N] * (L + 1), like).reshape(L + 1, N)
         return rq.contiguous(), rd.contiguous(), cn.contiguous()
 
     def _forward_ts_amortized(self, prev_X, prev_y, prev_h, maps: AmortizedNetwork, prev_cost, enable_noise):
@@ -480,6 +488,7 @@ class qBOAcqf(nn.Module):
         self._given_draws = None
         self._fed_noise = None
         self.rng_mode = kwargs.get("rng_mode", "host")
+        self.cost_function.rng_mode = self.rng_mode
 
     def gp(self) -> SurrogateGP:
         if self._gp is None:

@@ -112,9 +112,10 @@ class Actor:
             enable_ts=p.algo_ts, sampler=sampler, best_f=buffer["y"].max(), rng_mode=self.rng_mode)
 
     # ------------------------------------------------------------------ reset_parameters
-    def _random_tree(self, prev_point: Tensor, nf: List[int], n_first: int) -> List[Tensor]:
+    def _random_tree(self, prev_point: Tensor, nf: List[int], n_first: int, clamp_designs: bool = False) -> List[Tensor]:
         """Random designs level by level, each in the radius-ball of its parent
-        (reference actor.py:116-160 / 226-293).  Returns L+1 host tensors [cnt_s, d]."""
+        (reference actor.py:116-160 / 226-293).  Returns L+1 host tensors [cnt_s, d].  ``clamp_designs``: the
+        amortized branch clamps every design level to [0.01, 0.99] BEFORE the next level is drawn around it."""
         p = self.parms
         L, r = self.algo_lookahead_steps, p.cost_func_hypers["radius"]
         out: List[Tensor] = []
@@ -126,7 +127,10 @@ class Actor:
                 n = nf[s - 1]
             else:
                 n = nf[-1] * p.n_actions
-            out.append(generate_random_points_batch(parent, r, n))
+            x = generate_random_points_batch(parent, r, n)
+            if clamp_designs and s < L:
+                x = torch.clamp(x, max=0.99, min=0.01)
+            out.append(x)
         return out
 
     def reset_parameters(self, buffer, bo_iter=0, embedder=None, prev_chosen_idx=0):
@@ -178,9 +182,12 @@ class Actor:
         dev, dt = p.device, p.torch_dtype
         prev_h = buffer["h"][-1:].clone().expand(n, -1)
         opt = torch.optim.AdamW(self._parameters, lr=0.01, capturable=True)
-        tree = self._random_tree(prev_X[0:1], nf, n)
-        target = torch.stack([torch.clamp(x.to(device=dev, dtype=dt).reshape(-1, d), min=0.01, max=0.99)
-                              for x in tree], dim=0).detach()
+        tree = self._random_tree(prev_X[0:1], nf, n, clamp_designs=True)
+        # design levels were clamped on the host in their float32 form; the action level after the cast
+        # (reference actor.py:126-137 vs 158-162)
+        target = torch.stack([x.to(device=dev, dtype=dt).reshape(-1, d) if s < L else
+                              torch.clamp(x.to(device=dev, dtype=dt).reshape(-1, d), min=0.01, max=0.99)
+                              for s, x in enumerate(tree)], dim=0).detach()
         self.hidden_noise = torch.randn(n, p.hidden_dim).to(target[-1])
         prev_h = prev_h + self.hidden_noise
         gp = self.acqf.gp()
@@ -336,8 +343,9 @@ class Actor:
         rank, world = sh.world_of(self.group)
         own = sh.restart_range(p.n_restarts, rank, world)
         eng.chain_offset = own[0]
-        stream = self.rng_mode == "host" and p.torch_dtype == torch.float64
-        if self.rng_mode == "host":
+        recorded = getattr(self, "_recorded_draws", None)      # tests: explicit per-iteration draws (golden fixtures)
+        stream = self.rng_mode == "host" and p.torch_dtype == torch.float64 and recorded is None
+        if self.rng_mode == "host" and recorded is None:
             # the reference builds its frozen copy of the network twice before the loop (actor.py:524-555); the
             # random initialisation of those modules consumes the host generator ahead of the loop's draws
             for _ in range(2):
@@ -346,8 +354,10 @@ class Actor:
         loop = TSAMLoop(eng, theta0, prev_X, prev_y, prev_h, budget=float(p.budget), lr=p.acq_opt_lr,
                         past_initial=past_initial, prev_cost=prev_cost, max_iter=p.acq_opt_iter,
                         record_history=record, record_trajectory=record, n_global=p.n_restarts, group=self.group,
-                        rng="host" if stream else "device", own=own)
-        if self.rng_mode == "host" and not stream:
+                        rng="host" if stream else "device", own=own, exchange=getattr(p, "exchange", "auto"))
+        if recorded is not None:
+            st = loop.run(p.acq_opt_iter, draws_per_iter=recorded)
+        elif self.rng_mode == "host" and not stream:
             # float32 variant: torch's float32 normal stream (AVX2 normal_fill) is drawn by torch itself, eagerly
             draws = _HostDraws(acqf, L, p.n_restarts, d, prev_X, own)
             st = loop.run(p.acq_opt_iter, draws_per_iter=draws)

@@ -33,10 +33,18 @@ def draw_rotation(n: int, dim: int, like: Tensor) -> Tuple[Tensor, Tensor]:
     ``rand(n)`` float32 angles on the host generator, float32 cos/sin cast to ``like``'s dtype
     afterwards, then ``n`` x ``randperm(dim)[:2]`` coordinate pairs.
     Returns ``Q [n, 2, 2]`` and ``dims [n, 2]`` (int32) on ``like``'s device."""
-    theta = torch.rand(n) * 2 * torch.pi - torch.pi
+    if n >= 8 and dim >= 2:
+        # the same generator stream walked in bulk by the C side (bit for bit; tests/test_host_rng.py)
+        from .host_rng import CpuStream
+        cs = CpuStream()
+        theta = cs.rand_f32(n) * 2 * torch.pi - torch.pi
+        dims = cs.randperm(n, dim)[:, :2]
+        cs.commit()
+    else:
+        theta = torch.rand(n) * 2 * torch.pi - torch.pi
+        dims = torch.stack([torch.randperm(dim)[:2] for _ in range(n)]) if n else torch.zeros(0, 2, dtype=torch.int64)
     c, s = torch.cos(theta), torch.sin(theta)
     Q = torch.stack([torch.stack([c, -s], -1), torch.stack([s, c], -1)], -2)
-    dims = torch.stack([torch.randperm(dim)[:2] for _ in range(n)]) if n else torch.zeros(0, 2, dtype=torch.int64)
     return Q.to(like), dims.to(device=like.device, dtype=torch.int32)
 
 

@@ -715,9 +715,43 @@ static int launch_bwd_mma(const nmb_ts_problem_t* p, const nmb_ts_rollout_t* r, 
     return 0;
 }
 
+// the in-kernel draws of (step, call, chain) exactly as the rollout kernels make them (same device functions)
+__global__ void ts_device_draws_kernel(ProblemDev<double> pb, RolloutDev<double> ro, long long step, int n_calls,
+                                       double* cs, int* dims, double* noise) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= pb.N * n_calls) return;
+    const int call = (int)(i / pb.N);
+    const long long chain = i % pb.N;
+    double q[4];
+    int di, dj;
+    get_rotation(ro, pb, step, call, chain, q, di, dj);
+    cs[2 * i] = q[0];
+    cs[2 * i + 1] = q[2];
+    dims[2 * i] = di;
+    dims[2 * i + 1] = dj;
+    noise[i] = get_cost_noise(ro, pb, step, call, chain);
+}
+
 }  // namespace nmb
 
 using namespace nmb;
+
+extern "C" int nmb_ts_device_draws(uint64_t seed, int64_t step, unsigned rng_stream, int n_calls, int64_t n_chains,
+                                   int64_t chain_offset, int d, double* cs, int32_t* dims, double* noise, void* stream) {
+    NMB_REQUIRE(cs && dims && noise && n_calls >= 1 && n_calls <= 63 && n_chains >= 1 && d >= 1 && d <= NMB_MAX_DIM,
+                NMB_EINVAL, "nmb_ts_device_draws: bad argument");
+    ProblemDev<double> pb;
+    memset(&pb, 0, sizeof(pb));
+    pb.d = d; pb.L = n_calls - 1; pb.N = n_chains; pb.seed = seed; pb.chain_offset = chain_offset;
+    RolloutDev<double> ro;
+    memset(&ro, 0, sizeof(ro));
+    ro.rng_stream = rng_stream;
+    const long long total = (long long)n_chains * n_calls;
+    ts_device_draws_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(pb, ro, step, n_calls, cs,
+                                                                                            dims, noise);
+    NMB_LAUNCH_CHECK();
+    return 0;
+}
 
 extern "C" int64_t nmb_policy_param_count(int d, int H, int n_actions) {
     PolicyLayout lay;

@@ -360,6 +360,74 @@ def case_query(ref, name, env, n, L, n_r, H, seed, cost, n_iter):
     print(f"[golden] {name}: ok ({o['n_iter']} iterations, idx {int(o['idx'])})")
 
 
+def case_query_seeded(ref, name, env, n, L, n_r, H, seed, cost, n_iter, check_oracle=True):
+    """Whole ``Actor.query`` (HES-TS-AM) at the reference's own operating point, pinned by SEED only: the fixture
+    holds the torch CPU generator state at the entry of ``query`` and after it, no draws.  The product's
+    ``rng_mode="host"`` must reproduce ``chosen_idx`` / ``next_X`` from that state alone (BASELINE configs[0]:
+    main.py:499-513, actor.py:558-662) and leave the generator where the reference leaves it."""
+    prob = make_problem(env, seed=2)
+    model, X, Y = _shim_model(prob, n)
+    d = prob.d
+    tmp = tempfile.mkdtemp()
+    parms = types.SimpleNamespace(
+        algo="HES", algo_ts=True, amortized=True, algo_lookahead_steps=L, x_dim=d, y_dim=1,
+        hidden_dim=H, n_actions=1, n_restarts=n_r, n_samples=64, env_discretized=False,
+        num_categories=None, bounds=torch.tensor([[0.0, 1.0]] * d, dtype=F64), torch_dtype=F64,
+        device="cpu", acq_opt_lr=1e-3, acq_opt_iter=n_iter, n_initial_points=n, save_dir=tmp,
+        budget=2 * d**0.5, plot=False, loss_function_class=ref.acqfs.qLossFunctionTopK,
+        loss_func_hypers=dict(dist_weight=1, dist_threshold=0.5),
+        cost_function_class=ref.acqfs.qCostFunction, cost_func_hypers=_cost_hypers(cost))
+    torch.manual_seed(seed)
+    actor = ref.actor.Actor(parms)
+    P0 = {k: v.detach().clone() for k, v in actor.maps.state_dict().items()}
+    hbuf = torch.zeros(n, H, dtype=F64)
+    buffer = bs.TensorDict(dict(x=X, y=Y, h=hbuf, cost=torch.zeros(n, dtype=F64)))
+    actor.construct_acqf(model, buffer)
+    actor.hidden_noise = torch.randn(n_r, H).to(F64)
+    path = gp_math.draw_matheron_path(model.dense(), model.train_targets, 1)
+    torch.manual_seed(seed + 5)
+    state_in = torch.get_rng_state().clone()
+    import contextlib, io, time
+    t0 = time.time()
+    with contextlib.redirect_stdout(io.StringIO()):
+        out = actor.query(buffer, iteration=n, f_posterior=path, save_trajectory=False)
+    t_ref = time.time() - t0
+    state_out = torch.get_rng_state().clone()
+    tot = out["all_losses"] + out["all_costs"]
+    prev_X = X[-1:].expand(n_r, -1)
+    prev_y = Y[-1:].expand(n_r, -1)
+    prev_h = hbuf[-1:].expand(n_r, -1) + actor.hidden_noise
+    n_done = -1
+    if check_oracle:
+        torch.set_rng_state(state_in)
+        _burn = [_ref_net(ref, P0, d, H) for _ in range(2)]
+        spec = ho.HESSpec(L, [1] * L, 1, cost, enable_ts=True)
+        P = {k: v.clone() for k, v in P0.items()}
+        o = ho.query_loop(spec, prev_X, prev_y, prev_h, P, budget=parms.budget, lr=1e-3,
+                          n_iter=n_iter, past_initial=False, path=path, record=lambda *a: None)
+        _close(o["best_loss"], out["all_losses"], 1e-9, name + " best_loss")
+        _close(o["best_cost"], out["all_costs"], 1e-9, name + " best_cost")
+        assert int(o["idx"]) == int(out["chosen_idx"]), (o["idx"], out["chosen_idx"])
+        _close(o["next_X"], out["next_X"], 1e-9, name + " next_X")
+        torch.randn(1, 1, dtype=F64)       # the stand-alone cost call on the chosen design (actor.py:715)
+        assert torch.equal(torch.get_rng_state(), state_out), "oracle leaves the generator elsewhere"
+        n_done = o["n_iter"]
+    fx = dict(kind="query_ts_am_seeded", gp=_gp_inputs(prob, X, Y), d=d, H=H, L=L, n_r=n_r,
+              cost=_cost_hypers(cost), budget=parms.budget, lr=1e-3, max_iter=n_iter, n_iter=n_done,
+              path=dict(W=path.W.clone(), w=path.w.clone(), v=path.v.clone()),
+              policy=P0, prev_X=prev_X.clone(), prev_y=prev_y.clone(), prev_h=prev_h.clone(),
+              hidden_noise=actor.hidden_noise.clone(), rng_state_in=state_in, rng_state_out=state_out,
+              ref_cpu_seconds=t_ref,
+              out=dict(all_losses=out["all_losses"], all_costs=out["all_costs"],
+                       chosen_idx=int(out["chosen_idx"]), next_X=out["next_X"], cost=out["cost"], loss=out["loss"],
+                       actions=out["actions"], hidden_state=out["hidden_state"],
+                       final_policy={k: v.detach().clone() for k, v in actor.maps.state_dict().items()}))
+    torch.save(fx, os.path.join(GOLDEN_DIR, name + ".pt"))
+    srt = torch.sort(tot).values
+    print(f"[golden] {name}: ok ({n_done} iterations, idx {int(out['chosen_idx'])}, margin "
+          f"{float(srt[1] - srt[0]):.3e}, reference loop {t_ref:.1f} s on the host)")
+
+
 def case_eval(ref, name, env, n, n_r, seed, cost, algo, lookahead=0, n_initial=None, lr=1e-2):
     """``utils.eval_func`` verbatim (1000 AdamW steps) vs ``oracle/eval_oracle.py``.  For the non-HES
     branch the two names utils.py forgets to import are supplied (SURVEY App. D#9)."""
@@ -404,8 +472,21 @@ def case_eval(ref, name, env, n, n_r, seed, cost, algo, lookahead=0, n_initial=N
 
 
 def main():
+    """``python -m oracle.make_golden [case-name-substring ...]``: all cases, or only those whose name matches."""
     os.makedirs(GOLDEN_DIR, exist_ok=True)
     ref = bs.load_reference()
+    only = sys.argv[1:]
+    g = globals()
+
+    def _filtered(fn):
+        def run(ref_, name, *a, **k):
+            if only and not any(o in name for o in only):
+                return
+            return fn(ref_, name, *a, **k)
+        return run
+    case_ts_am, case_ts_free, case_mc, case_baselines, case_query, case_query_seeded, case_eval = (
+        _filtered(g[n]) for n in ("case_ts_am", "case_ts_free", "case_mc", "case_baselines", "case_query",
+                                  "case_query_seeded", "case_eval"))
     euclid = lambda r: ho.CostSpec(radius=r, k=1, max_noise=1e-5, p_norm=2.0)
     # TS-AM: cfg-2a shape (Ackley 2D, n=50, L=3) at 8 restarts; H=64
     case_ts_am(ref, "ts_am_ackley_L3", "Ackley", 50, 3, 8, 64, 11, euclid(0.075))
@@ -428,6 +509,10 @@ def main():
             kernel="matern12", ard=False)
     case_baselines(ref, "baselines_ackley", "Ackley", 30, 5, 41, euclid(0.075))
     case_query(ref, "query_ts_am_ackley_L1", "Ackley", 50, 1, 8, 32, 51, euclid(0.075), n_iter=12)
+    # BASELINE configs[0] at full size: 64 restarts, H = 64, <= 500 iterations, early stop active (seed-pinned)
+    case_query_seeded(ref, "query_ts_am_ackley_L1_full", "Ackley", 50, 1, 64, 64, 2, euclid(0.075), n_iter=500)
+    # configs[1]'s reference-exact shape (2a): L = 3, 64 restarts, one path
+    case_query_seeded(ref, "query_ts_am_ackley_L3_full", "Ackley", 50, 3, 64, 64, 3, euclid(0.075), n_iter=500)
     # utils.eval_func: HES branch, qEI (lookahead 0) and qKG (lookahead 1) branches
     case_eval(ref, "eval_hes_ackley", "Ackley", 30, 6, 61, euclid(0.075), "HES-TS-AM-20", lookahead=3)
     case_eval(ref, "eval_hes_hartmann_init", "Hartmann", 40, 5, 62, euclid(0.125), "HES-MC-3", lookahead=3,
