@@ -367,12 +367,16 @@ typedef struct nmb_tree_state {
     void *Gc, *Gb, *Gq, *Gm0;   /* [total] */
     void *gU;           /* [total][ldu] */
     void *g_pts;        /* [total][d] */
+    void *Gscr;         /* [nmb_mc_level_bwd_scratch_elems] per-level scratch of the deterministic ancestor reduction */
 } nmb_tree_state_t;
 
 /* forward of one level (levels must be issued in order 0..n_levels-1 after nmb_gp_whiten_fwd on all points) */
 int nmb_mc_level_fwd(const nmb_gp_t* gp, const nmb_tree_t* tree, const nmb_tree_state_t* st, int dtype, int level,
                      void* stream);
-/* backward of one level (issue levels n_levels-1..0; Gw/Gc/Gb/g_pts zeroed by the caller first);
+/* elements (of the call's dtype) of nmb_tree_state_t.Gscr */
+int64_t nmb_mc_level_bwd_scratch_elems(const nmb_tree_t* tree, int d);
+/* backward of one level (issue levels n_levels-1..0; Gw/Gc/Gb/g_pts zeroed by the caller first); deterministic:
+ * a node's contributions to its ancestors go through Gscr and are summed in a fixed order (no atomics);
  * g_leaf_sig == NULL: g_leaf [counts[n_levels-1]] is the adjoint of leaf_loss; otherwise g_leaf / g_leaf_sig are
  * the adjoints of the leaf nodes' posterior mean / sigma (baselines) */
 int nmb_mc_level_bwd(const nmb_gp_t* gp, const nmb_tree_t* tree, const nmb_tree_state_t* st, int dtype, int level,

@@ -12,8 +12,10 @@
 //                g_x = sum_j (g_K[j] + g_m0 alpha_j) d k(x, X_j) / dx  (K rows are recomputed).
 //   level_fwd  : one warp per node: the s dots u(z_t).u(x) against its ancestors (contiguous
 //                n-vectors), then the O(s^2) scalar recursion.
-//   level_bwd  : one thread per node: reverse recursion; contributions to ancestors go to their
-//                adjoint slots with FP64 atomics (levels are issued leaf -> root, so a node's
+//   level_bwd  : one thread per node: reverse recursion; the node's contributions to its ancestors'
+//                adjoint slots go to a scratch record per (target level, field, node) and
+//                level_bwd_reduce sums every ancestor's records over its descendants in a fixed
+//                order (deterministic: no atomics; levels are issued leaf -> root, so a node's
 //                slots are complete when its own level runs).
 //   gather_gu  : one warp per node: gU = 2 g_q u + sum_t g_dot_t u(z_t) + sum_desc g_dot u(desc),
 //                descendants visited in a fixed order.
@@ -247,14 +249,14 @@ static int make_tree(const nmb_tree_t* t, TreeDev& o) {
 template <typename T> struct StateDev {
     const T* pts;
     T *U, *m0, *q, *W, *var, *mean, *cst, *sig, *bv, *leaf_loss;
-    T *Gw, *Gdot, *Gc, *Gb, *Gq, *Gm0, *gU, *g_pts;
+    T *Gw, *Gdot, *Gc, *Gb, *Gq, *Gm0, *gU, *g_pts, *Gscr;
 };
 template <typename T> static StateDev<T> to_dev(const nmb_tree_state_t& s) {
     StateDev<T> o;
     o.pts = (const T*)s.pts; o.U = (T*)s.U; o.m0 = (T*)s.m0; o.q = (T*)s.q; o.W = (T*)s.W; o.var = (T*)s.var;
     o.mean = (T*)s.mean; o.cst = (T*)s.cst; o.sig = (T*)s.sig; o.bv = (T*)s.bv; o.leaf_loss = (T*)s.leaf_loss;
     o.Gw = (T*)s.Gw; o.Gdot = (T*)s.Gdot; o.Gc = (T*)s.Gc; o.Gb = (T*)s.Gb; o.Gq = (T*)s.Gq; o.Gm0 = (T*)s.Gm0;
-    o.gU = (T*)s.gU; o.g_pts = (T*)s.g_pts;
+    o.gU = (T*)s.gU; o.g_pts = (T*)s.g_pts; o.Gscr = (T*)s.Gscr;
     return o;
 }
 
@@ -385,12 +387,20 @@ __global__ void __launch_bounds__(128) level_bwd_kernel(GpDev<T> g, const __grid
             g_var = g_c / (T(2) * c) + (sig > T(0) ? g_sig / (T(2) * sig) : T(0));
         }
         T w[NMB_MAX_LEVELS], gw[NMB_MAX_LEVELS];
+        // scratch record of (target level t, field f) for this node: Gscr[(t R + f) cnt_s + i], R = 2 + d + NL;
+        // fields: 0 -> Gc, 1 -> Gb, 2.. -> g_pts[d], 2 + d.. -> Gw[t2 < t]
+        const int R = 2 + g.d + NL;
+        const size_t cs = (size_t)tr.cnt[s];
+        T* scr = st.Gscr + i;
         for (int t = 0; t < s; ++t) {
             w[t] = st.W[(size_t)node * NL + t];
             const long long bn = tr.off[t + 1] + i % tr.cnt[t + 1];
             gw[t] = st.Gw[(size_t)node * NL + t] - T(2) * w[t] * g_var + st.bv[bn] * g_mean;
-            if (g_mean != T(0)) atomicAdd(st.Gb + bn, w[t] * g_mean);
+            // b of the branch under ancestor level t + 1 (the node itself when t + 1 == s)
+            if (t + 1 == s) st.Gb[node] += w[t] * g_mean;
+            else scr[((size_t)(t + 1) * R + 1) * cs] = w[t] * g_mean;
         }
+        if (s > 0) scr[(size_t)1 * cs] = T(0);          // level-0 nodes have no b
         T gx[DMAX];
 #pragma unroll
         for (int k = 0; k < DMAX; ++k) gx[k] = T(0);
@@ -398,7 +408,8 @@ __global__ void __launch_bounds__(128) level_bwd_kernel(GpDev<T> g, const __grid
             const long long anc = tr.off[t] + i % tr.cnt[t];
             const T ct = st.cst[anc];
             const T g_acc = gw[t] / ct;
-            atomicAdd(st.Gc + anc, -gw[t] * w[t] / ct);
+            T* rec = scr + (size_t)t * R * cs;
+            rec[0] = -gw[t] * w[t] / ct;
             st.Gdot[(size_t)node * NL + t] = -g_acc;
             T ga[DMAX];
             kern_pair<T, DMAX>(g, st.pts + node * g.d, st.pts + anc * g.d, ga);
@@ -406,19 +417,52 @@ __global__ void __launch_bounds__(128) level_bwd_kernel(GpDev<T> g, const __grid
             for (int k = 0; k < DMAX; ++k) {
                 if (k < g.d) {
                     gx[k] = fma(g_acc, ga[k], gx[k]);
-                    atomicAdd(st.g_pts + anc * g.d + k, -g_acc * ga[k]);
+                    rec[(size_t)(2 + k) * cs] = -g_acc * ga[k];
                 }
             }
             const T* wz = st.W + (size_t)anc * NL;
             for (int t2 = 0; t2 < t; ++t2) {
-                atomicAdd(st.Gw + (size_t)anc * NL + t2, -g_acc * w[t2]);
+                rec[(size_t)(2 + g.d + t2) * cs] = -g_acc * w[t2];
                 gw[t2] = fma(-g_acc, wz[t2], gw[t2]);
             }
         }
         st.Gq[node] = -g_var;
         st.Gm0[node] = g_mean;
 #pragma unroll
-        for (int k = 0; k < DMAX; ++k) if (k < g.d) atomicAdd(st.g_pts + node * g.d + k, gx[k]);
+        for (int k = 0; k < DMAX; ++k) if (k < g.d) st.g_pts[node * g.d + k] += gx[k];
+    }
+}
+
+// Sum the level-s nodes' scratch records into their level-t ancestors' adjoint slots (blockIdx.y = t < s).
+// Ancestor a of level t owns the nodes i = a + j cnt_t, j < cnt_s / cnt_t; a group of G lanes (G a power of two,
+// <= 32, warp-uniform) walks j = lane, lane + G, ... and the partial sums meet in a fixed xor-shuffle order.
+template <typename T>
+__global__ void __launch_bounds__(256) level_bwd_reduce_kernel(const __grid_constant__ TreeDev tr, StateDev<T> st, int s, int d) {
+    const int t = blockIdx.y, NL = tr.n_levels, R = 2 + d + NL;
+    const int nf = 2 + d + t;                          // fields that level t receives
+    const long long ct = tr.cnt[t], cs = tr.cnt[s], desc = cs / ct;
+    int G = 1;
+    while (G < 32 && G < desc) G <<= 1;
+    const long long items = ct * nf;
+    const int lane = threadIdx.x & (G - 1);
+    for (long long item = ((long long)blockIdx.x * blockDim.x + threadIdx.x) / G; item < ((items + 31) / 32) * 32;
+         item += (long long)gridDim.x * blockDim.x / G) {
+        const bool live = item < items;
+        const int f = live ? (int)(item / ct) : 0;
+        const long long a = live ? item % ct : 0;
+        T acc = T(0);
+        if (live && !(f == 1 && t == 0)) {
+            const T* src = st.Gscr + ((size_t)t * R + f) * cs + a;
+            for (long long j = lane; j < desc; j += G) acc += src[(size_t)j * ct];
+        }
+        for (int o = G >> 1; o > 0; o >>= 1) acc += shfl_xor_(acc, o);
+        if (live && lane == 0) {
+            const long long anc = tr.off[t] + a;
+            if (f == 0) st.Gc[anc] += acc;
+            else if (f == 1) st.Gb[anc] += acc;
+            else if (f < 2 + d) st.g_pts[anc * d + (f - 2)] += acc;
+            else st.Gw[(size_t)anc * NL + (f - 2 - d)] += acc;
+        }
     }
 }
 
@@ -723,6 +767,18 @@ static int launch_level(const nmb_gp_t* gp, const TreeDev& tr, const nmb_tree_st
 #define NMB_LB(DM) level_bwd_kernel<T, DM><<<grid, 128, 0, st>>>(g, tr, sd, level, (const T*)g_leaf, (const T*)g_leaf_sig)
         NMB_MC_D(gp->d, NMB_LB);
 #undef NMB_LB
+        if (level > 0) {
+            long long mx = 0;
+            for (int t = 0; t < level; ++t) {
+                long long G = 1;
+                const long long desc = tr.cnt[level] / tr.cnt[t];
+                while (G < 32 && G < desc) G <<= 1;
+                mx = std::max(mx, tr.cnt[t] * (2 + gp->d + t) * G);
+            }
+            long long rb = (mx + 255) / 256;
+            rb = rb < 1 ? 1 : (rb > cap ? cap : rb);
+            level_bwd_reduce_kernel<T><<<dim3((unsigned)rb, (unsigned)level), 256, 0, st>>>(tr, sd, level, gp->d);
+        }
     }
     NMB_LAUNCH_CHECK();
     return 0;
@@ -744,6 +800,14 @@ extern "C" int nmb_mc_level_fwd(const nmb_gp_t* gp, const nmb_tree_t* tree, cons
                             : launch_level<float>(gp, tr, st, level, false, nullptr, nullptr, s);
 }
 
+extern "C" int64_t nmb_mc_level_bwd_scratch_elems(const nmb_tree_t* tree, int d) {
+    if (!tree || tree->n_levels < 1 || tree->n_levels > NMB_MAX_LEVELS) return -1;
+    int64_t mx = 1;
+    for (int s = 1; s < tree->n_levels; ++s)
+        mx = std::max<int64_t>(mx, tree->counts[s] * (int64_t)s * (2 + d + tree->n_levels));
+    return mx;
+}
+
 extern "C" int nmb_mc_level_bwd(const nmb_gp_t* gp, const nmb_tree_t* tree, const nmb_tree_state_t* st, int dtype,
                                 int level, const void* g_leaf, const void* g_leaf_sig, void* stream) {
     int rc = validate_gp(gp, dtype, "nmb_mc_level_bwd");
@@ -754,6 +818,7 @@ extern "C" int nmb_mc_level_bwd(const nmb_gp_t* gp, const nmb_tree_t* tree, cons
     NMB_REQUIRE(st && level >= 0 && level < tr.n_levels, NMB_EINVAL, "nmb_mc_level_bwd: level %d", level);
     NMB_REQUIRE(st->Gw && st->Gdot && st->Gc && st->Gb && st->Gq && st->Gm0 && st->g_pts, NMB_EINVAL,
                 "nmb_mc_level_bwd: null adjoint array");
+    NMB_REQUIRE(level == 0 || st->Gscr, NMB_EINVAL, "nmb_mc_level_bwd: null Gscr (nmb_mc_level_bwd_scratch_elems)");
     NMB_REQUIRE(level < tr.n_levels - 1 || g_leaf, NMB_EINVAL, "nmb_mc_level_bwd: null g_leaf");
     cudaStream_t s = (cudaStream_t)stream;
     return dtype == NMB_F64 ? launch_level<double>(gp, tr, st, level, true, g_leaf, g_leaf_sig, s)

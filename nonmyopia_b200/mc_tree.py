@@ -36,7 +36,7 @@ class TreeStruct(C.Structure):
 class TreeState(C.Structure):
     """``nmb_tree_state_t``"""
     _names = ["pts", "U", "m0", "q", "W", "var", "mean", "cst", "sig", "bv", "leaf_loss",
-              "Gw", "Gdot", "Gc", "Gb", "Gq", "Gm0", "gU", "g_pts"]
+              "Gw", "Gdot", "Gc", "Gb", "Gq", "Gm0", "gU", "g_pts", "Gscr"]
     _fields_ = [(n, C.c_void_p) for n in _names]
 
 
@@ -104,6 +104,10 @@ class MCTree:
                   leaf_loss=z(self.counts[-1]))
         return ws
 
+    def _scratch_elems(self, d: int) -> int:
+        self.lib.nmb_mc_level_bwd_scratch_elems.restype = C.c_int64
+        return int(self.lib.nmb_mc_level_bwd_scratch_elems(C.byref(self.tree), int(d)))
+
     def _state(self, pts: Tensor, ws: dict) -> TreeState:
         st = TreeState(pts=pts.data_ptr())
         for k, v in ws.items():
@@ -131,7 +135,8 @@ class MCTree:
         T, NL, ldu = self.total, len(self.counts), self.gp_struct.ldu
         ws = dict(ws)
         ws.update(Gw=z(T, NL), Gdot=z(T, NL), Gc=z(T), Gb=z(T), Gq=z(T), Gm0=z(T),
-                  gU=torch.empty(T, ldu, dtype=self.dtype, device=self.device), g_pts=z(T, pts.shape[1]))
+                  gU=torch.empty(T, ldu, dtype=self.dtype, device=self.device), g_pts=z(T, pts.shape[1]),
+                  Gscr=torch.empty(self._scratch_elems(pts.shape[1]), dtype=self.dtype, device=self.device))
         st = self._state(pts, ws)
         sp = _lib.stream_ptr()
         for s in reversed(range(NL)):

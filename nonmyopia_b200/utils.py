@@ -147,7 +147,8 @@ def eval_func(env, model, parms, buffer, iteration, embedder=None, *args, n_step
                        n_actions=parms.n_actions, n_fantasy_at_design_pts=[1],
                        loss_function_class=parms.loss_function_class, loss_func_hypers=parms.loss_func_hypers,
                        cost_function_class=parms.cost_function_class, cost_func_hypers=parms.cost_func_hypers,
-                       sampler=sampler, best_f=buffer["y"][: iteration + 1].max())
+                       sampler=sampler, best_f=buffer["y"][: iteration + 1].max(),
+                       rng_mode=getattr(parms, "rng_mode", "device"))
         lead = [prev_X.clone()] if parms.algo_lookahead_steps > 0 else []
         prev_y = buffer["y"][iteration: iteration + 1].expand(n_r, -1).to(dev, dt)
         n_noise = 2 if parms.algo == "qKG" else 1
