@@ -110,8 +110,8 @@ class ClockSampler:
     def stop(self):
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        self.proc.terminate()
-        self.t.join(timeout=2)
+        self.proc.kill()
+        self.t.join(timeout=1)
         sm = sorted(float(r[1]) for r in self.rows if len(r) >= 9 and r[1].replace(".", "").isdigit())
         mx = [float(r[2]) for r in self.rows if len(r) >= 9 and r[2].replace(".", "").isdigit()]
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
@@ -268,6 +268,8 @@ def run_b200(args, rank, world, local_rank):
         e1.record(stream)
         barrier()
         ms_total = e0.elapsed_time(e1)
+        clk = clocks.stop() if rank == 0 else None
+        barrier()
         # ---- sustained: the same replay back to back for >= args.sustained_s seconds (a real Actor.query is 500
         # iterations; the 100-step number above never leaves the burst clock state)
         sustained = None
@@ -284,13 +286,13 @@ def run_b200(args, rank, world, local_rank):
             s1.record(stream)
             barrier()
             sustained = {"steps": n_sus, "ms_total": s0.elapsed_time(s1), "clocks": sclk.stop() if rank == 0 else None}
+            barrier()       # rank 0 may spend a moment reaping nvidia-smi: nobody enters the next exchange without it
         # per-kernel timing of the same steps (eager launches, events on the launching stream)
         # (every rank runs them when sharded: the iteration holds the two all-reduces)
         kern = time_kernels(loop, stream, min(args.steps, 20)) if (rank == 0 or world > 1) else {}
         # ---- e2e: the public class API with HOST buffers, copies inside the timed region
         e2e = run_e2e_loop(args, loop, prev_x, prev_y, prev_h, stream, barrier)
         e2e_api = run_e2e(args, gp, path, net, prev_x, prev_y, prev_h, budget, dev, stream, barrier)
-    clk = clocks.stop() if rank == 0 else None
     t = torch.tensor([ms_total, e2e["ms_total"], e2e_api["ms_total"], sustained["ms_total"] if sustained else 0.0],
                      dtype=torch.float64, device=dev)
     if world > 1:

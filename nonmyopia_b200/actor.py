@@ -273,7 +273,7 @@ class Actor:
         is_hes = p.algo.startswith("HES")
         if is_hes:
             self.acqf.dump_model(f=f_posterior)
-            if p.algo_ts and f_posterior is None:
+            if p.algo_ts and f_posterior is None and rank == 0:
                 with open(os.path.join(p.save_dir, f"posterior_sample_{iteration}.pkl"), "wb") as fh:
                     pickle.dump(self.acqf.f, fh)
         past_initial = iteration > p.n_initial_points
@@ -343,6 +343,13 @@ class Actor:
         rank, world = sh.world_of(self.group)
         own = sh.restart_range(p.n_restarts, rank, world)
         eng.chain_offset = own[0]
+        if world > 1:
+            # replicated by construction (same host seed on every rank): checked, not assumed
+            f = acqf.f
+            chk = torch.stack([theta0.double().sum(), theta0.double().abs().sum(),
+                               self.hidden_noise.double().sum(), self.hidden_noise.double().abs().sum(),
+                               f.W.double().sum(), f.w.double().sum(), f.v.double().sum()])
+            sh.assert_replicated(chk, self.group, "policy weights / hidden noise / Thompson path")
         recorded = getattr(self, "_recorded_draws", None)      # tests: explicit per-iteration draws (golden fixtures)
         stream = self.rng_mode == "host" and p.torch_dtype == torch.float64 and recorded is None
         if self.rng_mode == "host" and recorded is None:

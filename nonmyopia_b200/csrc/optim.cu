@@ -1,6 +1,7 @@
 // Optimiser-loop kernels: parameter transpose, per-restart objective + best-restart
 // bookkeeping, conditional snapshot, fused AdamW (reference actor.py:489-662).
 #include <algorithm>
+#include <stdlib.h>
 #include "policy_dev.cuh"
 
 namespace nmb {
@@ -317,7 +318,7 @@ __global__ void __launch_bounds__(256) peer_publish_kernel(PeerTab pt, SegTab tb
 }
 
 __global__ void __launch_bounds__(32) peer_wait_decide_kernel(PeerTab pt, nmb_loop_state_t* state, int past_initial,
-                                                              int patience) {
+                                                              int patience, long long timeout_cycles) {
     if (state->done) return;
     const PeerHdr* hdr = reinterpret_cast<const PeerHdr*>(pt.base[pt.rank]);
     const unsigned long long e = hdr->epoch;
@@ -325,11 +326,12 @@ __global__ void __launch_bounds__(32) peer_wait_decide_kernel(PeerTab pt, nmb_lo
     double ct = INFINITY, cl = INFINITY;
     bool timed_out = false;
     if (lane < pt.world) {
-        // a rank that died must not hang this GPU: give up after ~4e9 cycles (about 2 s) and stop the loop
+        // a rank that died must not hang this GPU: give up after the timeout (NMB_PEER_TIMEOUT_MS, default 10 s,
+        // converted with the SM clock rate on the host) and stop the loop
         const long long t0 = clock64();
         while (ld_acquire_sys(&hdr->flag[lane]) < e + 1) {
             __nanosleep(40);
-            if (clock64() - t0 > 4000000000LL) { timed_out = true; break; }
+            if (clock64() - t0 > timeout_cycles) { timed_out = true; break; }
         }
     }
     if (__any_sync(0xffffffffu, timed_out)) {
@@ -551,7 +553,16 @@ extern "C" int nmb_peer_wait_decide(const nmb_peer_exchange_t* px, int dtype, nm
     if (rc) return rc;
     NMB_REQUIRE(state && (dtype == NMB_F64 || dtype == NMB_F32), NMB_EINVAL, "nmb_peer_wait_decide: bad argument");
     const PeerTab pt = dtype == NMB_F64 ? make_peertab<double>(px) : make_peertab<float>(px);
-    peer_wait_decide_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(pt, state, past_initial, patience);
+    static long long timeout_cycles = 0;
+    if (timeout_cycles == 0) {
+        int dev = 0, khz = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, dev);
+        const char* env = getenv("NMB_PEER_TIMEOUT_MS");
+        const double ms = env && atof(env) > 0 ? atof(env) : 10000.0;
+        timeout_cycles = (long long)(ms * (khz > 0 ? (double)khz : 2.0e6));
+    }
+    peer_wait_decide_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(pt, state, past_initial, patience, timeout_cycles);
     NMB_LAUNCH_CHECK();
     return 0;
 }

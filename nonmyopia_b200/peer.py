@@ -83,5 +83,11 @@ class PeerExchange:
             return None, why or "a peer rank could not map the exchange buffer"
         return px, None
 
+    def evict(self) -> None:
+        """Forget this buffer (after a timeout the epoch counters of the ranks disagree)."""
+        for k, v in list(self._cache.items()):
+            if v is self:
+                del self._cache[k]
+
     def byref(self):
         return C.byref(self.struct)

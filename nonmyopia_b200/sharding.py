@@ -85,6 +85,24 @@ def allreduce_sum(values: Tensor, group) -> Tensor:
     return values
 
 
+def assert_replicated(t: Tensor, group, what: str) -> None:
+    """Raise unless ``t`` is bit-identical on every rank of ``group``.  The sharded loops keep replicated state
+    (policy weights, hidden noise, Thompson path, base samples) consistent by construction - same host seed on
+    every rank - and the per-iteration exchange applies identical updates, so a rank seeded differently would
+    otherwise drift silently."""
+    if group is None:
+        return
+    dist = _dist()
+    world = dist.get_world_size(group)
+    mine = t.detach().reshape(-1).contiguous()
+    parts = [torch.empty_like(mine) for _ in range(world)]
+    dist.all_gather(parts, mine, group=group)
+    bad = [r for r, q in enumerate(parts) if not torch.equal(q.view(torch.uint8), parts[0].view(torch.uint8))]
+    if bad:
+        raise RuntimeError(f"replicated state differs across ranks ({what}): ranks {bad} disagree with rank 0 - seed "
+                           "every rank identically (torch.manual_seed) before Actor.reset_parameters / query")
+
+
 def gather_restarts(local: Tensor, n_restarts: int, group) -> Tensor:
     """All-gather a per-restart vector ``[n_local, ...]`` into ``[n_restarts, ...]`` (rank order = restart
     order).  Ragged shards are padded to the largest shard for the collective."""

@@ -308,7 +308,11 @@ class TSAMLoop:
         raw = self.state[:C.sizeof(te.LoopState)].cpu().numpy().tobytes()
         st = te.LoopState.from_buffer_copy(raw)
         if st.stall == -777:
-            raise _lib.NmbError("peer exchange timed out: a rank did not publish within ~2 s (loop stopped)")
+            # the ranks' epochs / flags are out of lock step now: drop the cached exchange buffer so that the next
+            # loop rendezvouses on a fresh, zeroed one
+            if self.px is not None:
+                self.px.evict()
+            raise _lib.NmbError("peer exchange timed out: a rank did not publish within NMB_PEER_TIMEOUT_MS (default 10 s; loop stopped)")
         return st
 
     def capture(self) -> None:
@@ -324,6 +328,10 @@ class TSAMLoop:
         with torch.cuda.graph(g):
             self._iteration()
         self.graph = g
+        if self.group is not None:
+            # capture / instantiate skew between ranks must not eat into the exchange's spin timeout
+            torch.cuda.synchronize()
+            self._dist.barrier(self.group)
 
     def run(self, n_iter: Optional[int] = None, draws_per_iter: Optional[List] = None, poll_every: int = 16,
             use_graph: bool = True) -> te.LoopState:

@@ -397,3 +397,80 @@ def query_loop(spec: HESSpec, prev_X, prev_y, prev_h, params, *, budget: float, 
                 next_X=snap["X"][0][idx].reshape(1, -1), actions=snap["actions"][..., idx, :, :],
                 hidden_state=(snap["hidden"][0][idx:idx + 1] if amortised else None),
                 n_iter=n_done, snapshot=snap)
+
+
+# --------------------------------------------------------------------------
+# Amortized pre-training (reference actor.py:106-220)
+# --------------------------------------------------------------------------
+def ball_points(parents: Tensor, radius: float, n: int) -> Tensor:
+    """utils.py:313-335 ``generate_random_points_batch``: ``n`` uniform points in the radius-ball of every parent
+    (float32 host draws cast to the parents' dtype); new leading dim ``n``."""
+    batch, dim = parents.shape[:-1], parents.shape[-1]
+    direction = torch.randn(n, *batch, dim).to(parents)
+    direction = direction / torch.norm(direction, dim=-1, keepdim=True)
+    r = torch.rand(n, *batch).pow(1 / dim).unsqueeze(-1).to(parents) * radius
+    return parents.unsqueeze(0).expand(n, *batch, dim) + r * direction
+
+
+def pretrain_targets(prev_x: Tensor, L: int, n: int, radius: float) -> Tensor:
+    """actor.py:116-162 with every fantasy width 1 (amortized => Thompson sampling): L design levels, each a random
+    ball point of its (clamped) parent, then the action level (clamped after the draw).  [L+1, n, d]."""
+    d = prev_x.shape[-1]
+    X: List[Tensor] = []
+    for s in range(L):
+        parent, cnt = (prev_x.reshape(1, d), n) if s == 0 else (X[-1], 1)
+        X.append(torch.clamp(ball_points(parent, radius, cnt), max=0.99, min=0.01).reshape(-1, d))
+    parent, cnt = (prev_x.reshape(1, d), n) if L == 0 else (X[-1], 1)
+    X.append(torch.clamp(ball_points(parent, radius, cnt).reshape(-1, d), max=0.99, min=0.01))
+    return torch.stack(X, dim=0)
+
+
+def pretrain_loop(P: Dict[str, Tensor], gp, prev_x: Tensor, prev_y: Tensor, prev_h: Tensor, targets: Tensor, *,
+                  n_epochs: int = 300, lr: float = 0.01, patience: int = 50, draws: Optional[List[Tensor]] = None,
+                  record: Optional[list] = None):
+    """actor.py:164-220: imitation of the random ball designs.  Per epoch: L design calls of the network, each
+    followed by ONE draw of the surrogate's marginal posterior at the (detached, through ``sample``'s no_grad)
+    output as the next observation - ``model(out.unsqueeze(-2)).sample(Size([1]))``, one ``randn`` of n values on
+    the global generator per level - then the action call; L1 loss to the targets; AdamW(lr 0.01); early stop after
+    ``patience`` epochs without a new best loss (checked after the step, actor.py:207-219).
+    ``prev_h`` already holds ``+ hidden_noise``.  ``draws``: per-epoch [L, n] normals instead of the generator.
+    Optimises ``P`` in place; returns the per-epoch losses."""
+    L, n = targets.shape[0] - 1, targets.shape[1]
+    leaves = list(P.values())
+    for p in leaves:
+        p.requires_grad_(True)
+    opt = torch.optim.AdamW(leaves, lr=lr)
+    best, stall, losses = float("inf"), 0, []
+    for ep in range(n_epochs):
+        outs, h = [], prev_h
+        x, y = prev_x.expand(n, -1), prev_y.expand(n, -1)
+        zs = []
+        for j in range(L):
+            out, h = policy_forward(P, x, y, h, "X")
+            outs.append(out)
+            x = out
+            with torch.no_grad():
+                mean, cov = gp.posterior(out.unsqueeze(-2))                   # [n, 1], [n, 1, 1]
+                z = (torch.randn(1, *mean.shape, dtype=mean.dtype) if draws is None
+                     else draws[ep][j].reshape(1, *mean.shape))
+                zs.append(z.reshape(-1))
+                root = gp_math.psd_safe_cholesky(cov)
+                y = (mean + root.matmul(z.unsqueeze(-1)).squeeze(-1)).reshape(-1, 1)
+        out, h = policy_forward(P, x, y, h, "A")
+        outs.append(out)
+        loss = torch.mean(abs(targets - torch.stack(outs, dim=0)))
+        losses.append(float(loss))
+        if record is not None:
+            record.append(torch.stack(zs) if zs else torch.zeros(0, n, dtype=targets.dtype))
+        if float(loss) < best:
+            best, stall = float(loss), 0
+        else:
+            stall += 1
+        loss.backward()
+        opt.step()
+        opt.zero_grad()
+        if stall >= patience:
+            break
+    for p in leaves:
+        p.requires_grad_(False)
+    return losses

@@ -428,6 +428,64 @@ def case_query_seeded(ref, name, env, n, L, n_r, H, seed, cost, n_iter, check_or
           f"{float(srt[1] - srt[0]):.3e}, reference loop {t_ref:.1f} s on the host)")
 
 
+def case_pretrain(ref, name, env, n, L, n_r, H, seed, cost):
+    """``Actor.reset_parameters`` (amortized branch, actor.py:106-220) verbatim vs ``hes_oracle.pretrain_loop`` on the
+    same generator stream: loss trajectory, final weights, ``hidden_noise``, generator state afterwards."""
+    import contextlib
+    import io
+    prob = make_problem(env, seed=2)
+    model, X, Y = _shim_model(prob, n)
+    d = prob.d
+    parms = types.SimpleNamespace(
+        algo="HES", algo_ts=True, amortized=True, algo_lookahead_steps=L, x_dim=d, y_dim=1,
+        hidden_dim=H, n_actions=1, n_restarts=n_r, n_samples=64, env_discretized=False,
+        num_categories=None, bounds=torch.tensor([[0.0, 1.0]] * d, dtype=F64), torch_dtype=F64,
+        device="cpu", acq_opt_lr=1e-3, acq_opt_iter=10, n_initial_points=n, save_dir=tempfile.mkdtemp(),
+        budget=2 * d**0.5, plot=False, loss_function_class=ref.acqfs.qLossFunctionTopK,
+        loss_func_hypers=dict(dist_weight=1, dist_threshold=0.5),
+        cost_function_class=ref.acqfs.qCostFunction, cost_func_hypers=_cost_hypers(cost))
+    torch.manual_seed(seed)
+    actor = ref.actor.Actor(parms)
+    P0 = {k: v.detach().clone() for k, v in actor.maps.state_dict().items()}
+    hbuf = torch.zeros(n, H, dtype=F64)
+    buffer = bs.TensorDict(dict(x=X, y=Y, h=hbuf, cost=torch.zeros(n, dtype=F64)))
+    actor.construct_acqf(model, buffer)
+    torch.manual_seed(seed + 7)
+    state_in = torch.get_rng_state().clone()
+    out = io.StringIO()
+    import time
+    t0 = time.time()
+    with contextlib.redirect_stdout(out):
+        actor.reset_parameters(buffer)
+    t_ref = time.time() - t0
+    state_out = torch.get_rng_state().clone()
+    printed = [float(l.split(":")[1]) for l in out.getvalue().splitlines() if l.startswith("Loss:")]
+    P_ref = {k: v.detach().clone() for k, v in actor.maps.state_dict().items()}
+    # oracle on the same stream
+    torch.set_rng_state(state_in)
+    targets = ho.pretrain_targets(X[-1], L, n_r, cost.radius)
+    hidden_noise = torch.randn(n_r, H).to(F64)
+    assert torch.equal(hidden_noise, actor.hidden_noise)
+    P = {k: v.clone() for k, v in P0.items()}
+    zs = []
+    losses = ho.pretrain_loop(P, model.dense(), X[-1:], Y[-1:], hbuf[-1:].expand(n_r, -1) + hidden_noise, targets,
+                              record=zs)
+    assert torch.equal(torch.get_rng_state(), state_out), "oracle leaves the generator elsewhere"
+    for k in P_ref:
+        _close(P[k].detach(), P_ref[k], 1e-10, name + " weights " + k)
+    for i, v in enumerate(printed):
+        assert abs(losses[10 * i] - v) < 1e-12, (i, losses[10 * i], v)
+    fx = dict(kind="pretrain", gp=_gp_inputs(prob, X, Y), d=d, H=H, L=L, n_r=n_r, cost=_cost_hypers(cost),
+              budget=parms.budget, lr=1e-3, policy=P0, rng_state_in=state_in, rng_state_out=state_out,
+              targets=targets, hidden_noise=hidden_noise, draws=torch.stack(zs) if L else None,
+              ref_cpu_seconds=t_ref,
+              out=dict(losses=torch.tensor(losses, dtype=F64), printed=printed,
+                       final_policy={k: v.clone() for k, v in P_ref.items()}))
+    torch.save(fx, os.path.join(GOLDEN_DIR, name + ".pt"))
+    print(f"[golden] {name}: ok ({len(losses)} epochs, loss {losses[0]:.4f} -> {losses[-1]:.5f}, reference "
+          f"{t_ref:.1f} s on the host)")
+
+
 def case_eval(ref, name, env, n, n_r, seed, cost, algo, lookahead=0, n_initial=None, lr=1e-2):
     """``utils.eval_func`` verbatim (1000 AdamW steps) vs ``oracle/eval_oracle.py``.  For the non-HES
     branch the two names utils.py forgets to import are supplied (SURVEY App. D#9)."""
@@ -484,9 +542,9 @@ def main():
                 return
             return fn(ref_, name, *a, **k)
         return run
-    case_ts_am, case_ts_free, case_mc, case_baselines, case_query, case_query_seeded, case_eval = (
+    case_ts_am, case_ts_free, case_mc, case_baselines, case_query, case_query_seeded, case_eval, case_pretrain = (
         _filtered(g[n]) for n in ("case_ts_am", "case_ts_free", "case_mc", "case_baselines", "case_query",
-                                  "case_query_seeded", "case_eval"))
+                                  "case_query_seeded", "case_eval", "case_pretrain"))
     euclid = lambda r: ho.CostSpec(radius=r, k=1, max_noise=1e-5, p_norm=2.0)
     # TS-AM: cfg-2a shape (Ackley 2D, n=50, L=3) at 8 restarts; H=64
     case_ts_am(ref, "ts_am_ackley_L3", "Ackley", 50, 3, 8, 64, 11, euclid(0.075))
@@ -513,6 +571,11 @@ def main():
     case_query_seeded(ref, "query_ts_am_ackley_L1_full", "Ackley", 50, 1, 64, 64, 2, euclid(0.075), n_iter=500)
     # configs[1]'s reference-exact shape (2a): L = 3, 64 restarts, one path
     case_query_seeded(ref, "query_ts_am_ackley_L3_full", "Ackley", 50, 3, 64, 64, 3, euclid(0.075), n_iter=500)
+    # Actor.reset_parameters, amortized pre-training at the reference's operating point
+    case_pretrain(ref, "pretrain_ackley_L3", "Ackley", 50, 3, 64, 64, 71, euclid(0.075))
+    case_pretrain(ref, "pretrain_ackley_L1", "Ackley", 50, 1, 64, 64, 72, euclid(0.075))
+    case_pretrain(ref, "pretrain_cosine8_L2", "Cosine8", 60, 2, 24, 32, 73,
+                  ho.CostSpec(radius=0.15, k=1, max_noise=1e-5, p_norm=1.0))
     # utils.eval_func: HES branch, qEI (lookahead 0) and qKG (lookahead 1) branches
     case_eval(ref, "eval_hes_ackley", "Ackley", 30, 6, 61, euclid(0.075), "HES-TS-AM-20", lookahead=3)
     case_eval(ref, "eval_hes_hartmann_init", "Hartmann", 40, 5, 62, euclid(0.125), "HES-MC-3", lookahead=3,

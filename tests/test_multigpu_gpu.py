@@ -162,3 +162,45 @@ def _free_worker(rank, group, tmp, name):
 def test_actor_query_free_sharded_equals_unsharded(name):
     _need_two()
     _spawn(_free_worker, name)
+
+
+# ----------------------------------------------------------------------------- HES-TS-AM through Actor, both rng modes
+def _actor_am_worker(rank, group, tmp, rng_mode):
+    """Actor.query (HES-TS-AM) sharded over two ranks == the same query unsharded, in the seed-stream mode ("host":
+    every rank walks the full generator stream and keeps its restarts) and in the in-kernel mode ("device": the Philox
+    counter is keyed by the GLOBAL chain index)."""
+    from nonmyopia_b200 import actor as A
+    from tests.test_dropin_gpu import _parms, product_gp
+    from tests.test_path_gpu import _product_path
+    fx = H.load("query_ts_am_ackley_L1")
+    n = fx["gp"]["train_X"].shape[0]
+    g = fx["gp"]
+    buffer = dict(x=g["train_X"].cuda(), y=g["train_Y"].cuda(), h=torch.zeros(n, fx["H"], dtype=F64, device="cuda"),
+                  cost=torch.zeros(n, dtype=F64, device="cuda"))
+    outs = []
+    for grp in (None, group):
+        parms = _parms(fx, tmp, 40, rng_mode)
+        parms.process_group = grp
+        act = A.Actor(parms)
+        act.maps.load_state_dict({k: v.clone() for k, v in fx["policy"].items()})
+        act.construct_acqf(product_gp(g), buffer)
+        act.hidden_noise = fx["prev_h"].cuda()
+        torch.manual_seed(11)
+        outs.append(act.query(buffer, iteration=n, f_posterior=_product_path(fx), save_trajectory=False))
+        state = torch.get_rng_state()
+        if grp is None:
+            state_one = state
+    one, two = outs
+    assert int(one["chosen_idx"]) == int(two["chosen_idx"])
+    assert H.rel_err(two["all_losses"], one["all_losses"], atol=1e-2) < 1e-8
+    assert H.rel_err(two["all_costs"], one["all_costs"], atol=1e-3) < 1e-8
+    assert H.rel_err(two["next_X"], one["next_X"], atol=1e-3) < 1e-8
+    assert H.rel_err(two["hidden_state"], one["hidden_state"], atol=1e-3) < 1e-8
+    if rng_mode == "host":
+        assert torch.equal(state, state_one)        # both leave the generator where the reference would
+
+
+@pytest.mark.parametrize("rng_mode", ["host", "device"])
+def test_actor_query_amortized_sharded_equals_unsharded(rng_mode):
+    _need_two()
+    _spawn(_actor_am_worker, rng_mode)
