@@ -274,7 +274,11 @@ def run_b200(args, rank, world, local_rank):
         # iterations; the 100-step number above never leaves the burst clock state)
         sustained = None
         if args.sustained_s > 0:
-            n_sus = max(args.steps, int(args.sustained_s * 1e3 / max(ms_total / args.steps, 1e-3)))
+            n_sus_t = torch.tensor([max(args.steps, int(args.sustained_s * 1e3 / max(ms_total / args.steps, 1e-3)))],
+                                   device=dev, dtype=torch.int64)
+            if world > 1:               # every rank must replay the SAME number of iterations (they exchange)
+                dist.broadcast(n_sus_t, src=0)
+            n_sus = int(n_sus_t.item())
             sclk = ClockSampler(local_rank)
             if rank == 0:
                 sclk.start()
@@ -521,7 +525,7 @@ def run_e2e(args, gp, path, net, prev_x, prev_y, prev_h, budget, dev, stream, ba
     acqf = acqfs.qMultiStepHEntropySearch(
         model=gp, loss_function_class=acqfs.qLossFunctionTopK, loss_func_hypers=dict(dist_weight=1, dist_threshold=0.5),
         cost_function_class=acqfs.qCostFunction, cost_func_hypers=cost_hypers(), lookahead_steps=Lk, n_actions=1,
-        n_fantasy_at_design_pts=[1] * Lk, n_fantasy_at_action_pts=64, enable_ts=True)
+        n_fantasy_at_design_pts=[1] * Lk, n_fantasy_at_action_pts=64, enable_ts=True, rng_mode="device")
     acqf.dump_model(f=path)
     maps = copy.deepcopy(net).to(dev)
     frozen = copy.deepcopy(net).to(dev)

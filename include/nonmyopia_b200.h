@@ -176,6 +176,14 @@ typedef struct nmb_ts_rollout {
     const void* ring_noise;    /* [ring_len][L+1][N]    N(0,1) draws of the cost calls, problem dtype */
     int32_t ring_len;          /* 0: no ring */
     int32_t _pad2;
+    /* Imitation mode (optional; Actor.reset_parameters, reference actor.py:164-220): y_obs [L][N] non-NULL => this
+     * launch runs only level `level_begin` (level_end = level_begin + 1) of the rollout, with no Thompson path and no
+     * cost: the observation fed to level l > 0 is y_obs[l-1] - a draw of the surrogate's marginal posterior at the
+     * previous output (nmb_gp_whiten_fwd + nmb_gp_marginal_sample between the launches), detached like the
+     * reference's `.sample()` - its input point is X[l-1] and its hidden state the saved HS[l].  The saved rollout
+     * (dy/dx = 0) is then differentiated by nmb_ts_rollout_bwd / nmb_policy_wgrad unchanged, seeded through g_X / g_A. */
+    const void* y_obs;
+    int32_t level_begin, level_end;
 } nmb_ts_rollout_t;
 
 int64_t nmb_ts_save_bytes(int dtype, int d, int H, int L, int64_t n_chains);
@@ -391,6 +399,28 @@ int nmb_tree_restart_mean(int dtype, const void* leaf, int64_t n_leaf, int64_t n
  * 2 qSR y, 3 qUCB mu^ + sqrt(beta pi/2) |y - mu^| with mu^ = mean_s y. */
 int nmb_mc_utility(int dtype, int which, double best_f, double beta, const void* mean, const void* sig, int64_t n,
                    const void* base, int n_samples, void* value, void* d_mean, void* d_sig, void* stream);
+
+/* ------------------------------------------------------------------------
+ * Amortized pre-training of Actor.reset_parameters (reference actor.py:164-220) - the pieces that are not already
+ * the query loop's kernels (nmb_ts_rollout_fwd in imitation mode, nmb_ts_rollout_bwd, nmb_policy_wgrad,
+ * nmb_policy_adamw_step):
+ *   nmb_gp_marginal_sample   y[i] = mean_const + m0[i] + sqrt(amplitude - q[i]) z[i]: one draw of the surrogate's
+ *       marginal posterior per point (`model(x.unsqueeze(-2)).sample()`, actor.py:186-191) from the outputs of
+ *       nmb_gp_whiten_fwd; the 1x1 "Cholesky" follows GPyTorch's jitter rule.  z: explicit [n], or slot
+ *       (*step_ptr % ring_len, level) of a host-stream ring z_ring [ring_len][n_levels][n] (the reference's
+ *       generator order, nmb_host_rng_randn_f64), or NULL/NULL = in-kernel Philox keyed by (seed, *step_ptr,
+ *       level, chain_offset + i).  done_flag (optional): non-zero => no-op.
+ *   nmb_imitation_objective  loss = mean |target - out| over the (L+1) N d rollout outputs (actor.py:198), its
+ *       adjoint seeds g_X [L][N][d], g_A [N][d] (= sign(out - target) / numel; g_loss, g_cost [N] are zeroed), the
+ *       per-epoch record hist[step] and the early-stop rule of actor.py:200-219 in `state` (best loss in best_min,
+ *       counter in stall, done_next once stall >= patience; patience < 0 disables).  One CTA, fixed order.
+ * ---------------------------------------------------------------------- */
+int nmb_gp_marginal_sample(int dtype, double amplitude, double mean_const, const void* m0, const void* q, int64_t n,
+                           const void* z, const void* z_ring, int ring_len, int n_levels, int level, uint64_t seed,
+                           int64_t chain_offset, const int64_t* step_ptr, const int32_t* done_flag, void* y, void* stream);
+int nmb_imitation_objective(int dtype, int d, int L, int64_t n_chains, const void* X, const void* A, const void* target,
+                            void* g_X, void* g_A, void* g_loss, void* g_cost, void* hist, int64_t max_epochs,
+                            int patience, nmb_loop_state_t* state, void* stream);
 
 /* ------------------------------------------------------------------------
  * FP64 / FP32 pipe micro-benchmarks used for the roofline denominators

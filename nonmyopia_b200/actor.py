@@ -192,7 +192,25 @@ class Actor:
         prev_h = prev_h + self.hidden_noise
         gp = self.acqf.gp()
         x0, y0 = prev_X[0].expand(n, d), prev_y[0].expand(n, p.y_dim)
+        from . import pretrain as pt
+        if pt.supported(d, p.hidden_dim, dt, dev) and p.y_dim == 1 and p.n_actions == 1:
+            # own kernels: the epoch (fused policy steps, surrogate draws, L1 seeds, reverse rollout, weight gradients,
+            # AdamW, early-stop rule) is one CUDA graph; nothing is read back before the loop ends
+            seed = int(torch.randint(0, 2**31 - 1, (1,)).item()) if self.rng_mode == "device" else 0
+            loop = pt.PretrainLoop(gp, self.maps.flat_parameters().detach(), x0, y0, prev_h, target, H=p.hidden_dim,
+                                   lr=0.01, max_epochs=300, patience=50, rng=self.rng_mode, seed=seed)
+            st = loop.run()
+            o = 0
+            with torch.no_grad():
+                for prm in self.maps.parameters():
+                    prm.copy_(loop.theta[o:o + prm.numel()].view_as(prm))
+                    o += prm.numel()
+            self.pretrain_losses = loop.losses(int(st.step))
+            for ep in range(0, int(st.step), 10):
+                print("Loss:", float(self.pretrain_losses[ep]))
+            return
 
+        # shapes outside the tensor-pipe kernel (float32 variant, odd d): the same epoch as device tensor ops
         def epoch():
             """One imitation epoch, device work only: rollout of the network on draws of the surrogate, L1 loss to
             the random ball designs, backward, AdamW."""

@@ -179,12 +179,13 @@ __device__ __forceinline__ void gemm_src_bwd(const PolicyLayout& lay, bool head_
 // theta_t; backward: steps L..0 from theta).
 template <int NST, bool BWD>
 __device__ __forceinline__ void mma_producer(const PolicyLayout& lay, const double* __restrict__ weights, int L,
-                                             const MmaRing& rg) {
+                                             const MmaRing& rg, int it_begin = 0, int it_end = -1) {
     const int lane = threadIdx.x & 31;
     const int H = lay.H;
     const unsigned row_bytes = (unsigned)H * 8u;
     unsigned c = 0;
-    for (int it = 0; it <= L; ++it) {
+    if (it_end < 0) it_end = L + 1;
+    for (int it = it_begin; it < it_end; ++it) {
         const int l = BWD ? L - it : it;
         for (int g = 0; g < kGemmsPerStep; ++g) {
             int off, ldw;

@@ -43,6 +43,9 @@ template <typename T> struct RolloutDev {
     const int* ring_dims;
     const T* ring_noise;
     int ring_len;
+    // imitation mode (Actor.reset_parameters, reference actor.py:164-220): observations come from outside
+    const T* y_obs;
+    int level_begin, level_end;
 };
 
 template <typename T> struct ProblemDev {
@@ -254,7 +257,7 @@ __global__ void __launch_bounds__(kMaxRowsMma * 8 + 32, 1)
     load_fast_tab(sm.tab, (int)threadIdx.x, (int)blockDim.x);
     __syncthreads();
     if ((int)threadIdx.x >= nthr_all) {      // producer warp
-        mma_producer<kStages, false>(pb.lay, ro.theta_t, L, sm.ring());
+        mma_producer<kStages, false>(pb.lay, ro.theta_t, L, sm.ring(), ro.level_begin, ro.level_end);
         return;
     }
     MmaWarp w;
@@ -262,25 +265,35 @@ __global__ void __launch_bounds__(kMaxRowsMma * 8 + 32, 1)
     w.tid = tid;
     w.bar = 1 + grp;
     const int KS = sm.KS;
+    // imitation mode: levels [l0, l1) of the rollout in this launch; the observation that feeds level l > 0 is
+    // y_obs[l - 1] (a draw of the surrogate at the previous output, made between the launches), its input point is
+    // the previous output X[l - 1], its hidden state the saved HS[l]
+    const bool imit = ro.y_obs != nullptr;
+    const int l0 = ro.level_begin, l1 = ro.level_end;
 
     // ---- load the tile's inputs
     for (int e = tid; e < (d + 1) * rows; e += nthr) {
         const int k = e / rows, r = e - k * rows;
         T v = T(0);
-        if (r < nvalid) v = k < d ? pb.prev_x[(chain0 + r) * d + k] : pb.prev_y[chain0 + r];
+        if (r < nvalid) {
+            if (l0 == 0) v = k < d ? pb.prev_x[(chain0 + r) * d + k] : pb.prev_y[chain0 + r];
+            else v = k < d ? ro.X[((size_t)(l0 - 1) * N + chain0 + r) * d + k] : ro.y_obs[(size_t)(l0 - 1) * N + chain0 + r];
+        }
         sm.IN[k * rows + r] = v;
     }
+    T* h_first = (l0 & 1) ? sm.HB : sm.HA;
     for (int e = tid; e < H * rows; e += nthr) {
         const int r = e / H, k = e - r * H;
-        const T v = r < nvalid ? pb.prev_h[(chain0 + r) * H + k] : T(0);
-        sm.HA[r * KS + k] = v;
-        if (ro.has_save && r < nvalid) ro.sv.HS[(chain0 + r) * H + k] = v;
+        T v = T(0);
+        if (r < nvalid) v = l0 == 0 ? pb.prev_h[(chain0 + r) * H + k] : ro.sv.HS[((size_t)l0 * N + chain0 + r) * H + k];
+        h_first[r * KS + k] = v;
+        if (ro.has_save && r < nvalid && l0 == 0) ro.sv.HS[(chain0 + r) * H + k] = v;
     }
     if (tid < rows) sm.cost_acc[tid] = T(0);
     consumer_sync(nthr, w.bar);
 
     const SaveAreas<T>* sv = ro.has_save ? &ro.sv : nullptr;
-    for (int l = 0; l <= L; ++l) {
+    for (int l = l0; l < l1; ++l) {
         const bool head_a = (l == L);
         const long long node0 = (long long)l * N + chain0;
         T* hs_out = ro.has_save ? ro.sv.HS + ((size_t)(l + 1) * N + chain0) * H : nullptr;
@@ -317,6 +330,23 @@ __global__ void __launch_bounds__(kMaxRowsMma * 8 + 32, 1)
         T yp = T(0), gp[DMAX];
 #pragma unroll
         for (int k = 0; k < DMAX; ++k) gp[k] = T(0);
+        if (imit) {
+            // the next observation is drawn outside the kernel and carries no gradient: dy/dx = 0, no cost
+            consumer_sync(nthr, w.bar);
+            if (live && lane == 0) {
+                if (ro.has_save) {
+                    ro.sv.CM[node0 + r] = T(1);
+#pragma unroll
+                    for (int k = 0; k < DMAX; ++k) if (k < d) ro.sv.DYDX[(node0 + r) * d + k] = T(0);
+                }
+                T* dst = head_a ? ro.A + chain * d : ro.X + ((size_t)l * N + chain) * d;
+#pragma unroll
+                for (int k = 0; k < DMAX; ++k) if (k < d) dst[k] = pt[k];
+                if (head_a) { ro.loss[chain] = T(0); ro.cost[chain] = T(0); }
+            }
+            consumer_sync(nthr, w.bar);
+            continue;               // the host launches level by level in this mode (l1 == l0 + 1)
+        }
         if (live) {
             if (ro.has_save) path_partial<T, DMAX, true, true>(pb.path, pt, (int)(chain / pb.cpp), lane, 8, yp, gp, sm.tab);
             else path_partial<T, DMAX, false, true>(pb.path, pt, (int)(chain / pb.cpp), lane, 8, yp, gp, sm.tab);
@@ -622,6 +652,9 @@ template <typename T> static RolloutDev<T> make_rollout(const nmb_ts_problem_t& 
     o.X = (T*)r.X; o.A = (T*)r.A; o.Y = (T*)r.Y; o.loss = (T*)r.loss; o.cost = (T*)r.cost;
     o.ring_cs = (const float2*)r.ring_cs; o.ring_dims = r.ring_dims; o.ring_noise = (const T*)r.ring_noise;
     o.ring_len = r.ring_cs ? r.ring_len : 0;
+    o.y_obs = (const T*)r.y_obs;
+    o.level_begin = r.y_obs ? r.level_begin : 0;
+    o.level_end = r.y_obs ? r.level_end : p.L + 1;
     o.has_save = r.save != nullptr;
     if (r.save) o.sv = carve_save<T>(r.save, p.d, p.H, p.L, p.n_chains);
     else memset(&o.sv, 0, sizeof(o.sv));
@@ -788,6 +821,16 @@ extern "C" int nmb_ts_rollout_fwd(const nmb_ts_problem_t* prob, const nmb_ts_rol
                     "nmb_ts_rollout_fwd: rot_q and rot_dims must be given together");
         NMB_REQUIRE(r.ring_cs == nullptr || (r.ring_dims && r.ring_noise && r.ring_len > 0 && prob->step_ptr), NMB_EINVAL,
                     "nmb_ts_rollout_fwd: the host-stream ring needs ring_dims, ring_noise, ring_len > 0 and step_ptr");
+    }
+    for (int i = 0; i < n_rollouts; ++i) {
+        const nmb_ts_rollout_t& r = rollouts[i];
+        if (!r.y_obs) continue;
+        NMB_REQUIRE(n_rollouts == 1 && r.save && r.level_begin >= 0 && r.level_end == r.level_begin + 1 &&
+                        r.level_end <= prob->L + 1 && !r.noisy_design && !r.noisy_action,
+                    NMB_EINVAL, "nmb_ts_rollout_fwd: imitation mode takes one saved, noise-free rollout and one level per "
+                                "launch (levels [%d, %d) of %d)", r.level_begin, r.level_end, prob->L + 1);
+        NMB_REQUIRE(mma_fwd_ok(prob, rollouts, n_rollouts), NMB_ELIMIT,
+                    "nmb_ts_rollout_fwd: imitation mode needs the FP64 tensor-pipe kernel (float64, even d, H >= 8)");
     }
     cudaStream_t st = (cudaStream_t)stream;
     if (mma_fwd_ok(prob, rollouts, n_rollouts)) {

@@ -78,7 +78,8 @@ class RolloutStruct(C.Structure):
                 ("X", C.c_void_p), ("A", C.c_void_p), ("Y", C.c_void_p), ("loss", C.c_void_p),
                 ("cost", C.c_void_p), ("save", C.c_void_p),
                 ("ring_cs", C.c_void_p), ("ring_dims", C.c_void_p), ("ring_noise", C.c_void_p),
-                ("ring_len", C.c_int32), ("_pad2", C.c_int32)]
+                ("ring_len", C.c_int32), ("_pad2", C.c_int32),
+                ("y_obs", C.c_void_p), ("level_begin", C.c_int32), ("level_end", C.c_int32)]
 
 
 class LoopState(C.Structure):
