@@ -463,7 +463,7 @@ class qBOAcqf(nn.Module):
     """qEI / qPI / qSR / qUCB[-beta] / qKG over the shared-root posterior kernels
     (reference acqfs.py:35-179; BoTorch classes restated in SURVEY A.7-8)."""
 
-    NAMES = ("qKG", "qEI", "qPI", "qSR", "qUCB")
+    NAMES = ("qKG", "qEI", "qPI", "qSR", "qUCB", "qMSL")
 
     def __init__(self, name, model, loss_function_class, loss_func_hypers, cost_function_class, cost_func_hypers,
                  lookahead_steps: int, n_actions: int, n_fantasy_at_design_pts: Optional[List[int]] = [64],
@@ -480,8 +480,19 @@ class qBOAcqf(nn.Module):
             self.beta = 0.1
         elif name.startswith("qUCB"):
             self.beta = float(name.split("-")[-1])
-        elif name in ("qMSL", "qNIPV"):
-            raise NotImplementedError(f"{name}: SURVEY 8f rank 4 (next), not on the B200 hot path yet")
+        elif name == "qMSL":
+            # BoTorch qMultiStepLookahead(batch_sizes=[1] * k, num_fantasies) with its defaults (reference
+            # acqfs.py:94-99): one Sobol sampler per stage, seeded from the global host generator at construction;
+            # zero stage values, posterior mean at the terminal points, uniform weights
+            self.batch_sizes = [1] * lookahead_steps
+            self.msl_fantasies = [int(f) for f in n_fantasy_at_design_pts][:lookahead_steps]
+            if len(self.msl_fantasies) != lookahead_steps:
+                raise ValueError("qMSL needs one fantasy width per lookahead step")
+            self.msl_samplers = [SobolQMCNormalSampler(f) for f in self.msl_fantasies]
+        elif name == "qNIPV":
+            # the reference hands mc_points=0 to BoTorch's constructor (acqfs.py:101-104), whose register_buffer
+            # accepts tensors only: the name cannot be instantiated upstream either - same error here
+            raise TypeError("cannot assign 'int' object to buffer 'mc_points' (torch Tensor or None required)")
         elif name not in self.NAMES:
             raise NotImplementedError
         self._gp = None
@@ -498,6 +509,9 @@ class qBOAcqf(nn.Module):
     def cost_noise_sizes(self, n_r: int) -> List[int]:
         """Element counts of the ``randn_like`` calls of one ``forward`` (acqfs.py:137-161)."""
         nf = self.num_fantasies
+        if self.name == "qMSL":
+            import math
+            return [n_r * math.prod(self.msl_fantasies[:i]) for i in range(len(self.msl_fantasies) + 1)]
         return [n_r, n_r * nf * nf] if self.name == "qKG" else [n_r]
 
     def forward(self, prev_X: Tensor, prev_y: Tensor, maps, embedder: nn.Module = None, prev_cost: float = 0.0,

@@ -45,7 +45,7 @@ __device__ __forceinline__ void path_partial(const PathDev<T>& P, const T (&x)[D
     // ---- random-Fourier-feature prior
     const T* wsin = P.w_feat + (size_t)s * 2 * P.n_freq;
     const T* wcos = wsin + P.n_freq;
-#pragma unroll 2
+#pragma unroll 4
     for (int m = lane; m < P.n_freq; m += nl) {
         const T* wr = P.w_phase + (size_t)m * d;
         T wk[DMAX];

@@ -70,6 +70,31 @@ __device__ __forceinline__ void dmma884(double (&c)[2], double a, double b) {
                  : "d"(a), "d"(b));
 }
 
+// ---------------------------------------------------------------- optional phase clocks (-DNMB_PHASE_CLOCKS)
+// Cycle accounting of one consumer warp's timeline inside the forward rollout (tools/phase_clocks.py): 0 embedding,
+// 1 GEMM loops (incl. waiting for weight chunks), 2 activation epilogues, 3 named barriers, 4 output layer, 5 rotation +
+// Thompson path, 6 cost / stores / step tail, 7 input load.  Compiles to nothing in the product build.
+#ifdef NMB_PHASE_CLOCKS
+static __device__ unsigned long long g_phase_clk[16];
+struct PhaseClk {
+    long long t;
+    unsigned long long acc[8];
+    __device__ void start() { t = clock64(); for (int i = 0; i < 8; ++i) acc[i] = 0; }
+    __device__ __forceinline__ void mark(int i) { const long long n = clock64(); acc[i] += (unsigned long long)(n - t); t = n; }
+    __device__ void flush(bool who) {
+        if (!who) return;
+        for (int i = 0; i < 8; ++i) atomicAdd(&g_phase_clk[i], acc[i]);
+        atomicAdd(&g_phase_clk[8], 1ULL);
+    }
+};
+#else
+struct PhaseClk {
+    __device__ __forceinline__ void start() {}
+    __device__ __forceinline__ void mark(int) {}
+    __device__ __forceinline__ void flush(bool) {}
+};
+#endif
+
 // ---------------------------------------------------------------- geometry / shared memory
 // weight ring as seen by producer and consumers
 struct MmaRing {
@@ -267,7 +292,7 @@ __device__ __forceinline__ void zero_acc4(double (&acc)[4][2]) {
 __device__ __forceinline__ void mma_policy_forward(const PolicyLayout& lay, const double* __restrict__ theta_t, bool head_a,
                                                    const MmaSmem& sm, MmaWarp& w, double* hprev, double* hnew,
                                                    const SaveAreas<double>* save, long long node0, int nvalid,
-                                                   double* __restrict__ hs_out) {
+                                                   double* __restrict__ hs_out, PhaseClk& pc) {
     const int d = lay.d, H = lay.H, rows = sm.rows, KS = sm.KS;
     const int tid = w.tid, nthr = w.nthr;
     const MmaRing ring = sm.ring();
@@ -279,6 +304,7 @@ __device__ __forceinline__ void mma_policy_forward(const PolicyLayout& lay, cons
     {
         const double* Wt = theta_t + lay.off[S_WE];      // [d+1][H]
         const double* b = theta_t + lay.off[S_BE];
+#pragma unroll 4
         for (int e = tid; e < rows * H; e += nthr) {
             const int r = e / H, o = e - r * H;
             double a = __ldg(b + o);
@@ -294,14 +320,18 @@ __device__ __forceinline__ void mma_policy_forward(const PolicyLayout& lay, cons
             }
         }
     }
+    pc.mark(0);
     consumer_sync(nthr, w.bar);
+    pc.mark(3);
     const int row = w.row0 + w.fr;
     const bool rv = row < nvalid;
     const size_t nrow = (size_t)(node0 + row) * H;
     double acc[4][2];
     // ---- prepro: B1 = p = elu(Wp ea + bp)
+    pc.mark(2);
     zero_acc4(acc);
     mma_gemm<kStages>(ring, w, sm.B0, H, acc);
+    pc.mark(1);
 #pragma unroll
     for (int t = 0; t < 4; ++t) {
         const int o = w.col0 + 8 * t + 2 * w.fk;
@@ -312,34 +342,42 @@ __device__ __forceinline__ void mma_policy_forward(const PolicyLayout& lay, cons
             if (save && rv) *reinterpret_cast<double2*>(save->P + nrow + o) = v;
         }
     }
+    pc.mark(2);
     consumer_sync(nthr, w.bar);
+    pc.mark(3);
     // ---- GRU cell (gates r, z, n of the same (row, col) stay in registers)
     {
         double rg[4][2], zg[4][2], gh[4][2];
         const double* bih = theta_t + lay.off[S_BIH];
         const double* bhh = theta_t + lay.off[S_BHH];
+        pc.mark(2);
         zero_acc4(acc);
         mma_gemm<kStages>(ring, w, sm.B1, H, acc);
         mma_gemm<kStages>(ring, w, hprev, H, acc);
+        pc.mark(1);
 #pragma unroll
         for (int t = 0; t < 4; ++t) {
             const int o = min(w.col0 + 8 * t + 2 * w.fk, H - 2);
 #pragma unroll
             for (int j = 0; j < 2; ++j) rg[t][j] = nmb_sigmoid_tab_(acc[t][j] + __ldg(bih + o + j) + __ldg(bhh + o + j));
         }
+        pc.mark(2);
         zero_acc4(acc);
         mma_gemm<kStages>(ring, w, sm.B1, H, acc);
         mma_gemm<kStages>(ring, w, hprev, H, acc);
+        pc.mark(1);
 #pragma unroll
         for (int t = 0; t < 4; ++t) {
             const int o = min(w.col0 + 8 * t + 2 * w.fk, H - 2);
 #pragma unroll
             for (int j = 0; j < 2; ++j) zg[t][j] = nmb_sigmoid_tab_(acc[t][j] + __ldg(bih + H + o + j) + __ldg(bhh + H + o + j));
         }
+        pc.mark(2);
         zero_acc4(acc);
         zero_acc4(gh);
         mma_gemm<kStages>(ring, w, sm.B1, H, acc);
         mma_gemm<kStages>(ring, w, hprev, H, gh);
+        pc.mark(1);
 #pragma unroll
         for (int t = 0; t < 4; ++t) {
             const int o = w.col0 + 8 * t + 2 * w.fk;
@@ -365,13 +403,17 @@ __device__ __forceinline__ void mma_policy_forward(const PolicyLayout& lay, cons
             }
         }
     }
+    pc.mark(2);
     consumer_sync(nthr, w.bar);
+    pc.mark(3);
     // ---- post MLP layer 0: B0 = u1 = elu(W0 [p; h'] + b0)
     const int sB0 = head_a ? S_AB0 : S_XB0, sB3 = head_a ? S_AB3 : S_XB3;
     const int sW6 = head_a ? S_AW6 : S_XW6, sB6 = head_a ? S_AB6 : S_XB6;
+    pc.mark(2);
     zero_acc4(acc);
     mma_gemm<kStages>(ring, w, sm.B1, H, acc);
     mma_gemm<kStages>(ring, w, hnew, H, acc);
+    pc.mark(1);
 #pragma unroll
     for (int t = 0; t < 4; ++t) {
         const int o = w.col0 + 8 * t + 2 * w.fk;
@@ -382,10 +424,14 @@ __device__ __forceinline__ void mma_policy_forward(const PolicyLayout& lay, cons
             if (save && rv) *reinterpret_cast<double2*>(save->U1 + nrow + o) = v;
         }
     }
+    pc.mark(2);
     consumer_sync(nthr, w.bar);
+    pc.mark(3);
     // ---- layer 3: u2 = elu(W3 u1 + b3) -> hprev buffer (dead)
+    pc.mark(2);
     zero_acc4(acc);
     mma_gemm<kStages>(ring, w, sm.B0, H, acc);
+    pc.mark(1);
 #pragma unroll
     for (int t = 0; t < 4; ++t) {
         const int o = w.col0 + 8 * t + 2 * w.fk;
@@ -396,7 +442,9 @@ __device__ __forceinline__ void mma_policy_forward(const PolicyLayout& lay, cons
             if (save && rv) *reinterpret_cast<double2*>(save->U2 + nrow + o) = v;
         }
     }
+    pc.mark(2);
     consumer_sync(nthr, w.bar);
+    pc.mark(3);
     // ---- output layer (O = d): out = sigmoid(W6 u2 + b6); 4 threads per output, 2 interleaved chains each
     {
         const double* Wt = theta_t + lay.off[sW6];       // [H][d]
@@ -421,7 +469,9 @@ __device__ __forceinline__ void mma_policy_forward(const PolicyLayout& lay, cons
             }
         }
     }
+    pc.mark(4);
     consumer_sync(nthr, w.bar);
+    pc.mark(3);
 }
 
 // ================================================================== backward step

@@ -265,6 +265,8 @@ __global__ void __launch_bounds__(kMaxRowsMma * 8 + 32, 1)
     w.tid = tid;
     w.bar = 1 + grp;
     const int KS = sm.KS;
+    PhaseClk pc;
+    pc.start();
     // imitation mode: levels [l0, l1) of the rollout in this launch; the observation that feeds level l > 0 is
     // y_obs[l - 1] (a draw of the surrogate at the previous output, made between the launches), its input point is
     // the previous output X[l - 1], its hidden state the saved HS[l]
@@ -291,6 +293,7 @@ __global__ void __launch_bounds__(kMaxRowsMma * 8 + 32, 1)
     }
     if (tid < rows) sm.cost_acc[tid] = T(0);
     consumer_sync(nthr, w.bar);
+    pc.mark(7);
 
     const SaveAreas<T>* sv = ro.has_save ? &ro.sv : nullptr;
     for (int l = l0; l < l1; ++l) {
@@ -299,7 +302,7 @@ __global__ void __launch_bounds__(kMaxRowsMma * 8 + 32, 1)
         T* hs_out = ro.has_save ? ro.sv.HS + ((size_t)(l + 1) * N + chain0) * H : nullptr;
         T* hprev = (l & 1) ? sm.HB : sm.HA;
         T* hnew = (l & 1) ? sm.HA : sm.HB;
-        mma_policy_forward(pb.lay, ro.theta_t, head_a, sm, w, hprev, hnew, sv, node0, nvalid, hs_out);
+        mma_policy_forward(pb.lay, ro.theta_t, head_a, sm, w, hprev, hnew, sv, node0, nvalid, hs_out, pc);
 
         // ---- output point, Thompson path, cost: 8 threads per chain (nthr = 8 rows)
         const int r = tid >> 3, lane = tid & 7;
@@ -357,7 +360,9 @@ __global__ void __launch_bounds__(kMaxRowsMma * 8 + 32, 1)
             for (int k = 0; k < DMAX; ++k) gp[k] = group_sum(gp[k], 8);
         }
         const T yv = yp + pb.path.mean_const;
+        pc.mark(5);
         consumer_sync(nthr, w.bar);     // every thread has read sm.IN / sm.OUT of this step
+        pc.mark(3);
         if (live && lane == 0) {
             T dir[DMAX];
             const T dist = move_dist<T, DMAX>(pb.cost, d, pt, xin, dir);
@@ -388,9 +393,21 @@ __global__ void __launch_bounds__(kMaxRowsMma * 8 + 32, 1)
             for (int k = 0; k < DMAX; ++k) if (k < d) sm.IN[k * rows + r] = pt[k];
             sm.IN[d * rows + r] = yv;
         }
+        pc.mark(6);
         consumer_sync(nthr, w.bar);
+        pc.mark(3);
     }
+    pc.flush(threadIdx.x == 0);
 }
+
+#ifdef NMB_PHASE_CLOCKS
+extern "C" int nmb_debug_phase_clocks(unsigned long long* host_out, int reset) {
+    cudaDeviceSynchronize();
+    if (host_out) cudaMemcpyFromSymbol(host_out, g_phase_clk, sizeof(unsigned long long) * 16);
+    if (reset) { unsigned long long z[16] = {0}; cudaMemcpyToSymbol(g_phase_clk, z, sizeof(z)); }
+    return 0;
+}
+#endif
 
 // ================================================================== backward
 template <typename T, int DMAX>

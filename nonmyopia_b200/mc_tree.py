@@ -271,8 +271,10 @@ def baseline_forward(acqf, prev_X: Tensor, maps, prev_cost: float, draws=None):
     dt, dev = prev_X.dtype, prev_X.device
     gp = acqf.gp()
     actions = torch.concat(list(maps)).reshape(n_r, -1, d)      # row-major scramble for qKG
-    base = acqf.sampler.base(dt, dev)
     hyp = acqf.cost_function.hypers()
+    if acqf.name == "qMSL":
+        return _msl_forward(acqf, prev_X, actions, prev_cost, draws)
+    base = acqf.sampler.base(dt, dev)
     if acqf.name == "qKG":
         nfant = acqf.num_fantasies
         Xa = actions[:, :-nfant, :]
@@ -328,3 +330,43 @@ def baseline_forward(acqf, prev_X: Tensor, maps, prev_cost: float, draws=None):
         acqf_cost = _TreeCostFn.apply(prev_X, noise.reshape(-1).contiguous(), hyp, prev_cost, pts)
         X_ret = [actions]
     return {"acqf_loss": acqf_loss, "acqf_cost": acqf_cost, "X": X_ret, "actions": actions, "hidden_state": None}
+
+
+def _msl_forward(acqf, prev_X: Tensor, actions: Tensor, prev_cost: float, draws=None):
+    """qMSL (reference acqfs.py:94-99,137-145,166-167): BoTorch's k-step lookahead over the one-shot representation
+    ``actions [b, q', d]``, q' = 1 + f_1 + f_1 f_2 + ...; stage i's points are ``X_i [f_i, .., f_1, b, 1, d]`` - the
+    same restart-fastest tree layout as HES-MC - fantasies with observation noise, value = posterior mean of the
+    k-times fantasised model at the terminal points averaged over the leaves: the ``nmb_mc_level_*`` kernels with a
+    zero action base sample.  The reference runs this name in float32 (main.py:73-77): the dtype follows the inputs."""
+    from .acqfs import _TreeCostFn, _host_cost_noise
+    n_r, d = prev_X.shape
+    dt, dev = prev_X.dtype, prev_X.device
+    nf = acqf.msl_fantasies
+    sizes = [math.prod(nf[:i]) for i in range(len(nf) + 1)]
+    if actions.shape[1] != sum(sizes):
+        raise ValueError(f"qMSL: {actions.shape[1]} points per restart, the tree {nf} needs {sum(sizes)}")
+    key = ("msl", n_r, dt)
+    if getattr(acqf, "_tree_key", None) != key:
+        bases = [smp.base(dt, dev) for smp in acqf.msl_samplers]
+        acqf._tree = MCTree(acqf.gp(), nf, n_r, bases, None, obs_noise_fantasy=True, dtype=dt)
+        acqf._tree_key = key
+    tree = acqf._tree
+    levels, off = [], 0
+    for qt in sizes:
+        levels.append(actions[:, off:off + qt, :].permute(1, 0, 2).reshape(qt * n_r, d))
+        off += qt
+    mean_leaf, _ = tree.leaf_posterior(levels)
+    acqf_loss = -tree.restart_mean(mean_leaf)
+    cnt = tree.counts
+    if draws is not None:
+        noise = draws
+    elif acqf._fed_noise is not None:
+        noise = acqf._fed_noise
+    elif acqf.rng_mode == "host":
+        noise = _host_cost_noise(cnt, prev_X)
+    else:
+        noise = torch.randn(sum(cnt), dtype=dt, device=dev)
+    acc = _TreeCostFn.apply(prev_X, noise.reshape(-1).contiguous(), acqf.cost_function.hypers(), prev_cost, *levels)
+    X_ret = [levels[i].reshape(*nf[:i][::-1], n_r, 1, d) for i in range(len(sizes))]
+    return {"acqf_loss": acqf_loss, "acqf_cost": tree.restart_mean(acc), "X": X_ret, "actions": actions,
+            "hidden_state": None}

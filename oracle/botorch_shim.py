@@ -456,12 +456,57 @@ class qKnowledgeGradient(MCAcquisitionFunction):
         return values.mean(dim=0)
 
 
-class _Unsupported(MCAcquisitionFunction):
-    def __init__(self, *a, **kw):
-        raise NotImplementedError(
-            "qMultiStepLookahead / qNegIntegratedPosteriorVariance are 'next' rows "
-            "(SURVEY 8f rank 4), not restated by the oracle shim"
-        )
+class qMultiStepLookahead(MCAcquisitionFunction):
+    """BoTorch 0.10.0 ``qMultiStepLookahead`` as the reference uses it (acqfs.py:94-99): ``batch_sizes = [1] * k``,
+    ``num_fantasies = [f_1..f_k]``, default samplers (one ``SobolQMCNormalSampler(Size([f_i]))`` per stage, seed from
+    the global generator), default value functions ``[None, ..., None, PosteriorMean]`` (zero stage values, posterior
+    mean of the k-times fantasised model at the terminal points), uniform sample weights.  One-shot input
+    ``X [b, q', d]``, ``q' = 1 + f_1 + f_1 f_2 + ...``; stage i's points are ``X_i [f_i, .., f_1, b, 1, d]``.
+    Fantasies use ``observation_noise=True`` and the fantasy caches keep their gradients (SURVEY A.4, A.8 [3P])."""
+
+    def __init__(self, model, batch_sizes, num_fantasies=None, samplers=None, **kw):
+        super().__init__(model, None)
+        self.batch_sizes = list(batch_sizes)
+        if samplers is None:
+            samplers = [SobolQMCNormalSampler(torch.Size([nf])) for nf in num_fantasies]
+        self.num_fantasies = [int(smp.sample_shape[0]) for smp in samplers]
+        self.samplers = nn.ModuleList(samplers)
+
+    def get_split_shapes(self, X):
+        batch_shape, (q_aug, d) = X.shape[:-2], X.shape[-2:]
+        rest = sum(math.prod(self.num_fantasies[:i + 1]) * q for i, q in enumerate(self.batch_sizes))
+        batch_sizes = [q_aug - rest] + self.batch_sizes
+        shapes = [torch.Size(self.num_fantasies[:i][::-1] + [*batch_shape, q_i, d])
+                  for i, q_i in enumerate(batch_sizes)]
+        sizes = [s[: (-2 - len(batch_shape))].numel() * s[-2] for s in shapes]
+        return batch_shape, shapes, sizes
+
+    def get_multi_step_tree_input_representation(self, X):
+        batch_shape, shapes, sizes = self.get_split_shapes(X)
+        Xsplit = torch.split(X, sizes, dim=-2)
+        perm = [-2] + list(range(len(batch_shape))) + [-1]
+        X0 = Xsplit[0].reshape(shapes[0])
+        return [X0] + [Xi.permute(*perm).reshape(shape) for Xi, shape in zip(Xsplit[1:], shapes[1:])]
+
+    def forward(self, X):
+        Xs = self.get_multi_step_tree_input_representation(X)
+        model = self.model
+        for i, Xi in enumerate(Xs[:-1]):
+            model = model.fantasize(X=Xi, sampler=self.samplers[i], observation_noise=True)
+        with propagate_grads(True):
+            mean, _ = model.dense().posterior(Xs[-1])                # [f_k, .., f_1, b, 1]
+        val = mean.squeeze(-1)
+        b = X.shape[:-2]
+        return val.reshape(-1, *b).mean(dim=0)
+
+
+class qNegIntegratedPosteriorVariance(MCAcquisitionFunction):
+    """The reference constructs it with ``mc_points=0`` (acqfs.py:101-104); BoTorch's constructor hands that to
+    ``register_buffer``, which accepts only tensors: the name cannot be instantiated upstream."""
+
+    def __init__(self, model, mc_points, sampler=None, **kw):
+        super().__init__(model, sampler)
+        self.register_buffer("mc_points", mc_points)
 
 
 # --------------------------------------------------------------------------
@@ -594,7 +639,7 @@ def install() -> None:
     if getattr(sys.modules.get("botorch"), "_is_oracle_shim", False):
         return
     acq = dict(qExpectedImprovement=qExpectedImprovement, qKnowledgeGradient=qKnowledgeGradient,
-               qMultiStepLookahead=_Unsupported, qNegIntegratedPosteriorVariance=_Unsupported,
+               qMultiStepLookahead=qMultiStepLookahead, qNegIntegratedPosteriorVariance=qNegIntegratedPosteriorVariance,
                qProbabilityOfImprovement=qProbabilityOfImprovement, qSimpleRegret=qSimpleRegret,
                qUpperConfidenceBound=qUpperConfidenceBound)
     settings = _mod("botorch.settings", propagate_grads=propagate_grads)

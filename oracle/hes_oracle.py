@@ -288,6 +288,33 @@ def baseline_forward(name: str, gp: DenseGP, prev_X: Tensor, maps: List[Tensor],
             return None
         return noises.pop(0)
 
+    if name == "qMSL":
+        # acqfs.py:94-99,137-145: k-step lookahead tree over the one-shot representation; ``base`` = list of the k
+        # stages' Sobol base samples, ``num_fantasies`` = [f_1..f_k]
+        nf = list(num_fantasies)
+        sizes = [math.prod(nf[:i]) for i in range(len(nf) + 1)]
+        assert actions.shape[1] == sum(sizes), (actions.shape, sizes)
+        Xs, off = [], 0
+        for i, qt in enumerate(sizes):
+            Xi = actions[:, off:off + qt, :].permute(1, 0, 2).reshape(*nf[:i][::-1], n_r, 1, d)
+            Xs.append(Xi)
+            off += qt
+        model = gp
+        for i, Xi in enumerate(Xs[:-1]):
+            mean, cov = model.posterior(Xi, observation_noise=True)
+            ys = gp_math.sample_from_posterior(mean, cov, base[i].reshape(nf[i], *([1] * (mean.dim() - 1)), 1))
+            model = model.condition_on_observations(Xi, ys)
+        fmean, _ = model.posterior(Xs[-1])
+        value = fmean.squeeze(-1).reshape(-1, n_r).mean(0)
+        loss = -value
+        pX, cost = prev_X[:, None, :], 0
+        for cX in Xs:
+            cost = cost + spotlight_cost(pX.expand_as(cX), cX, cost_spec, nz(cX), cost + prev_cost)
+            pX = cX[None, ...]
+        cost = cost.squeeze(-1).sum(-1)
+        while cost.dim() > 1:
+            cost = cost.mean(0)
+        return {"acqf_loss": loss, "acqf_cost": cost, "actions": actions, "X": Xs}
     if name == "qKG":
         Xa = actions[:, :-num_fantasies, :]                     # [n_r, 1, d]
         Xf = actions[:, -num_fantasies:, :].permute(1, 0, 2).unsqueeze(-2)   # [nf, n_r, 1, d]

@@ -271,6 +271,48 @@ def case_baselines(ref, name, env, n, n_r, seed, cost):
     print(f"[golden] {name}: ok")
 
 
+def case_msl(ref, name, env, n, n_r, nf, seed, cost):
+    """qMSL (acqfs.py:94-99,137-145): reference qBOAcqf over the shim's qMultiStepLookahead vs the oracle tree."""
+    import math
+    prob = make_problem(env, seed=2)
+    model, X, Y = _shim_model(prob, n)
+    d, L = prob.d, len(nf)
+    prev_X = X[-1:].expand(n_r, -1).clone()
+    prev_y = Y[-1:].expand(n_r, -1).clone()
+    torch.manual_seed(seed)
+    acq = ref.acqfs.qBOAcqf(
+        name="qMSL", model=model, lookahead_steps=L, n_actions=1, n_fantasy_at_design_pts=list(nf),
+        loss_function_class=ref.acqfs.qLossFunctionTopK, loss_func_hypers=dict(dist_weight=1, dist_threshold=0.5),
+        cost_function_class=ref.acqfs.qCostFunction, cost_func_hypers=_cost_hypers(cost), sampler=None, best_f=None)
+    seeds = [int(smp.seed) for smp in acq.bo_acqf.samplers]
+    cnt = [n_r * math.prod(nf[:i]) for i in range(L + 1)]
+    maps = [torch.rand(c, d, dtype=F64) for c in cnt]           # the level tensors reset_parameters would hold
+    ma = [m.clone().requires_grad_(True) for m in maps]
+    mb = [m.clone().requires_grad_(True) for m in maps]
+    torch.manual_seed(seed + 17)
+    r = acq.forward(prev_X, prev_y, ma)
+    g_ref = torch.autograd.grad((r["acqf_loss"] + r["acqf_cost"]).mean(), ma)
+    bases = [smp.base_samples.reshape(-1).clone() for smp in acq.bo_acqf.samplers]
+    torch.manual_seed(seed + 17)
+    o = ho.baseline_forward("qMSL", model.dense(), prev_X, mb, base=bases, cost_spec=cost, num_fantasies=list(nf))
+    g_or = torch.autograd.grad((o["acqf_loss"] + o["acqf_cost"]).mean(), mb)
+    _close(o["acqf_loss"], r["acqf_loss"], 1e-12, f"{name} loss")
+    _close(o["acqf_cost"], r["acqf_cost"], 1e-12, f"{name} cost")
+    for a, b in zip(g_or, g_ref):
+        _close(a, b, 1e-10, f"{name} grad")
+    for a, b in zip(o["X"], r["X"]):
+        assert torch.equal(a, b)
+    torch.manual_seed(seed + 17)
+    nz = [torch.randn(c, dtype=F64) for c in cnt]
+    fx = dict(kind="msl", gp=_gp_inputs(prob, X, Y), d=d, n_r=n_r, nf=list(nf), L=L, cost=_cost_hypers(cost),
+              maps=maps, bases=bases, seeds=seeds, prev_X=prev_X, cost_noise=nz,
+              out=dict(acqf_loss=r["acqf_loss"].detach(), acqf_cost=r["acqf_cost"].detach(),
+                       grads=[g.detach() for g in g_ref], X_shapes=[tuple(x.shape) for x in r["X"]],
+                       actions_shape=tuple(r["actions"].shape)))
+    torch.save(fx, os.path.join(GOLDEN_DIR, name + ".pt"))
+    print(f"[golden] {name}: ok (sampler seeds {seeds})")
+
+
 def case_query(ref, name, env, n, L, n_r, H, seed, cost, n_iter):
     """Whole ``Actor.query`` (HES-TS-AM) verbatim vs ``hes_oracle.query_loop``."""
     prob = make_problem(env, seed=2)
@@ -542,9 +584,9 @@ def main():
                 return
             return fn(ref_, name, *a, **k)
         return run
-    case_ts_am, case_ts_free, case_mc, case_baselines, case_query, case_query_seeded, case_eval, case_pretrain = (
+    case_ts_am, case_ts_free, case_mc, case_baselines, case_query, case_query_seeded, case_eval, case_pretrain, case_msl = (
         _filtered(g[n]) for n in ("case_ts_am", "case_ts_free", "case_mc", "case_baselines", "case_query",
-                                  "case_query_seeded", "case_eval", "case_pretrain"))
+                                  "case_query_seeded", "case_eval", "case_pretrain", "case_msl"))
     euclid = lambda r: ho.CostSpec(radius=r, k=1, max_noise=1e-5, p_norm=2.0)
     # TS-AM: cfg-2a shape (Ackley 2D, n=50, L=3) at 8 restarts; H=64
     case_ts_am(ref, "ts_am_ackley_L3", "Ackley", 50, 3, 8, 64, 11, euclid(0.075))
@@ -566,6 +608,9 @@ def main():
     case_mc(ref, "mc_ackley_L4_m12", "Ackley", 25, [4, 2, 2, 1], 2, 8, 33, euclid(0.075),
             kernel="matern12", ard=False)
     case_baselines(ref, "baselines_ackley", "Ackley", 30, 5, 41, euclid(0.075))
+    # qMSL: the reference's widths [32, 2, 1, 1] and a smaller tree
+    case_msl(ref, "msl_ackley_k4", "Ackley", 30, 4, [32, 2, 1, 1], 43, euclid(0.075))
+    case_msl(ref, "msl_hartmann_k2", "Hartmann", 40, 3, [4, 3], 44, euclid(0.125))
     case_query(ref, "query_ts_am_ackley_L1", "Ackley", 50, 1, 8, 32, 51, euclid(0.075), n_iter=12)
     # BASELINE configs[0] at full size: 64 restarts, H = 64, <= 500 iterations, early stop active (seed-pinned)
     case_query_seeded(ref, "query_ts_am_ackley_L1_full", "Ackley", 50, 1, 64, 64, 2, euclid(0.075), n_iter=500)

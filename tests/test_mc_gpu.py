@@ -289,3 +289,95 @@ def test_whiten_large_n_arbitrated_in_extended_precision(n, d, kernel):
     assert eq_kernel < max(2 * eq_oracle, 1e-10)
     # and against the truth itself the kernel meets north_star's 1e-8 on the posterior variance os - q
     assert eq_kernel / 1.3 < 1e-8
+
+
+def _msl_acqf(fx, dtype):
+    from nonmyopia_b200 import acqfs
+    gp = product_gp(fx["gp"])
+    torch.manual_seed(0)
+    acqf = acqfs.qBOAcqf(name="qMSL", model=gp, lookahead_steps=fx["L"], n_actions=1, n_fantasy_at_design_pts=fx["nf"],
+                         loss_function_class=acqfs.qLossFunctionTopK, loss_func_hypers=dict(dist_weight=1, dist_threshold=0.5),
+                         cost_function_class=acqfs.qCostFunction, cost_func_hypers=fx["cost"], sampler=None, best_f=None)
+    for smp, seed, base in zip(acqf.msl_samplers, fx["seeds"], fx["bases"]):
+        smp.seed = seed
+        assert H.rel_err(smp.base(torch.float64, "cpu"), base) < 1e-12      # same Sobol draw as BoTorch's sampler
+        smp.base_samples = base.clone().to(dtype)
+    return acqf
+
+
+@pytest.mark.parametrize("name", ["msl_ackley_k4", "msl_hartmann_k2"])
+def test_msl_matches_reference_golden(name):
+    """qMSL: the reference's qBOAcqf over BoTorch's qMultiStepLookahead (restated in the shim,
+    widths [32, 2, 1, 1] as main.py:73-77 / actor.py:104) vs the MC-tree kernels: loss, cost, every level's gradient,
+    the tree representation returned in "X"."""
+    fx = H.load(name)
+    acqf = _msl_acqf(fx, F64)
+    maps = [m.clone().cuda().requires_grad_(True) for m in fx["maps"]]
+    acqf._given_draws = torch.cat([z.reshape(-1) for z in fx["cost_noise"]]).cuda()
+    out = acqf.forward(fx["prev_X"].cuda(), None, maps)
+    ref = fx["out"]
+    assert H.rel_err(out["acqf_loss"], ref["acqf_loss"], atol=1e-3) < 1e-8
+    assert H.rel_err(out["acqf_cost"], ref["acqf_cost"], atol=1e-3) < 1e-8
+    assert [tuple(x.shape) for x in out["X"]] == ref["X_shapes"] and tuple(out["actions"].shape) == ref["actions_shape"]
+    assert out["hidden_state"] is None
+    grads = torch.autograd.grad((out["acqf_loss"] + out["acqf_cost"]).mean(), maps)
+    for gd, gr in zip(grads, ref["grads"]):
+        scale = max(float(gr.abs().max()), 1e-6)
+        assert float((gd.cpu() - gr).abs().max()) / scale < 1e-8
+
+
+def test_msl_float32_variant_within_1e3():
+    """The reference runs qMSL in float32 (main.py:77): the FP32 kernels against the FP64 golden, north_star's 1e-3."""
+    fx = H.load("msl_ackley_k4")
+    from nonmyopia_b200 import acqfs
+    from nonmyopia_b200.gp import SurrogateGP
+    g = fx["gp"]
+    F32 = torch.float32
+    acqf = _msl_acqf(fx, F32)
+    maps = [m.clone().to(F32).cuda().requires_grad_(True) for m in fx["maps"]]
+    acqf._given_draws = torch.cat([z.reshape(-1) for z in fx["cost_noise"]]).to(F32).cuda()
+    out = acqf.forward(fx["prev_X"].to(F32).cuda(), None, maps)
+    assert out["acqf_loss"].dtype == F32
+    assert H.rel_err(out["acqf_loss"], fx["out"]["acqf_loss"], atol=1e-1) < 1e-3
+    assert H.rel_err(out["acqf_cost"], fx["out"]["acqf_cost"], atol=1e-1) < 1e-3
+    grads = torch.autograd.grad((out["acqf_loss"] + out["acqf_cost"]).mean(), maps)
+    for gd, gr in zip(grads, fx["out"]["grads"]):
+        assert float((gd.double().cpu() - gr).abs().max()) / max(float(gr.abs().max()), 1e-6) < 5e-3
+
+
+def test_qnipv_mirrors_the_upstream_constructor_error():
+    from nonmyopia_b200 import acqfs
+    fx = H.load("msl_hartmann_k2")
+    with pytest.raises(TypeError):
+        acqfs.qBOAcqf(name="qNIPV", model=product_gp(fx["gp"]), lookahead_steps=0, n_actions=1,
+                      loss_function_class=acqfs.qLossFunctionTopK, loss_func_hypers=dict(dist_weight=1, dist_threshold=0.5),
+                      cost_function_class=acqfs.qCostFunction, cost_func_hypers=fx["cost"], sampler=None)
+
+
+def test_actor_query_msl_runs_in_float32():
+    """Actor end to end with algo = qMSL at the reference's settings (float32, widths [32, 2, 1, 1], lookahead 4):
+    reset_parameters (random ball tree), graph-replayed free loop, selection."""
+    import tempfile
+    import types
+    from nonmyopia_b200 import acqfs, actor as A
+    fx = H.load("msl_ackley_k4")
+    g, d = fx["gp"], fx["d"]
+    F32 = torch.float32
+    n = g["train_X"].shape[0]
+    parms = types.SimpleNamespace(
+        algo="qMSL", algo_ts=False, amortized=False, algo_lookahead_steps=4, x_dim=d, y_dim=1, hidden_dim=8, n_actions=1,
+        n_restarts=4, n_samples=32, env_discretized=False, num_categories=None,
+        bounds=torch.tensor([[0.0, 1.0]] * d, dtype=F32), torch_dtype=F32, device="cuda", acq_opt_lr=1e-2, acq_opt_iter=30,
+        n_initial_points=n, save_dir=tempfile.mkdtemp(), budget=2 * d ** 0.5, plot=False,
+        loss_function_class=acqfs.qLossFunctionTopK, loss_func_hypers=dict(dist_weight=1, dist_threshold=0.5),
+        cost_function_class=acqfs.qCostFunction, cost_func_hypers=fx["cost"], rng_mode="host")
+    torch.manual_seed(1)
+    act = A.Actor(parms)
+    buffer = dict(x=g["train_X"].to(F32).cuda(), y=g["train_Y"].to(F32).cuda(), h=torch.zeros(n, 8, dtype=F32, device="cuda"),
+                  cost=torch.zeros(n, dtype=F32, device="cuda"))
+    act.construct_acqf(product_gp(g), buffer)
+    act.reset_parameters(buffer)
+    assert [m.shape[0] for m in act.maps] == [4, 128, 256, 256, 256]
+    out = act.query(buffer, iteration=n, save_trajectory=False)
+    assert out["next_X"].shape == (1, d) and out["next_X"].dtype == F32
+    assert bool(torch.isfinite(out["all_losses"]).all()) and out["hidden_state"] is None
