@@ -50,6 +50,10 @@ def parse_args():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-selfcheck", action="store_true", help="N > 1: skip the sharded parity self-check")
+    ap.add_argument("--cpu-config", type=int, default=None, choices=[1, 3, 4],
+                    help="run ONLY the cpu_baseline leg of another BASELINE config (oracle port on the host cores): "
+                         "1 = one Ackley HES-TS-AM-1 BO step's Actor.query loop, 3 = Hartmann HES-MC tree, "
+                         "4 = Cosine8 HES-TS-AM (n = 200)")
     ap.add_argument("--sustained-s", type=float, default=2.0,
                     help="seconds of back-to-back graph replays for the sustained-clock number (0 = skip)")
     ap.add_argument("--restarts", type=int, default=N_RESTARTS)
@@ -154,6 +158,105 @@ def cpu_oracle_rate(n_restarts, lookahead, target_s, threads):
     return dict(value=evals / dt, ms_per_step=dt / n_iter * 1e3, n_iter=n_iter, seconds=dt,
                 sample=f"{n_restarts} chains x {lookahead + 1} levels (one Thompson path), {n_iter} Adam iterations "
                        f"({dt:.1f} s) of the same Ackley-2D HES-TS-AM-{lookahead} workload")
+
+
+def cpu_baseline_config(cfg: int):
+    """cpu_baseline leg of BASELINE configs[0], [2] and [3] (SURVEY 8d cfg 1, 3, 4): the oracle port timed on a bounded
+    sample of the workload on all host cores; MC trees are extrapolated per node (the dense fantasy models of the
+    reference need ~4.5 GB of host memory per restart at n = 500)."""
+    from nonmyopia_b200.synthetic import make_problem
+    from oracle import gp_math, hes_oracle as ho
+    F64 = torch.float64
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    if cfg == 1:
+        fx = torch.load(os.path.join(ROOT, "tests", "golden", "query_ts_am_ackley_L1_full.pt"), weights_only=False)
+        g = fx["gp"]
+        d = fx["d"]
+        ls = torch.full((1, d), g["lengthscale"], dtype=F64)
+        gp = gp_math.DenseGP.fit_caches(g["train_X"], g["train_Y"], kind=g["kernel"], lengthscale=ls,
+                                        outputscale=g["outputscale"], noise=g["noise"], mean_const=g["mean_const"])
+        pth = gp_math.MatheronPath(fx["path"]["W"], fx["path"]["w"], fx["path"]["v"], g["train_X"], kind=g["kernel"],
+                                   lengthscale=ls, outputscale=g["outputscale"], mean_const=g["mean_const"])
+        c = fx["cost"]
+        spec = ho.HESSpec(fx["L"], [1] * fx["L"], 1, ho.CostSpec(radius=c["radius"], k=c["k"], max_noise=c["max_noise"],
+                                                                 p_norm=c["p_norm"]), enable_ts=True)
+        torch.set_rng_state(fx["rng_state_in"])
+        from nonmyopia_b200.amortized_network import AmortizedNetwork
+        for _ in range(2):          # the two throw-away networks of actor.py:524-555 consume the generator
+            AmortizedNetwork(d + 1, d, fx["H"], 1, torch.tensor([[0.0, 1.0]] * d, dtype=F64))
+        P = {k: v.clone() for k, v in fx["policy"].items()}
+        t0 = time.perf_counter()
+        o = ho.query_loop(spec, fx["prev_X"], fx["prev_y"], fx["prev_h"], P, budget=fx["budget"], lr=fx["lr"],
+                          n_iter=fx["max_iter"], past_initial=False, path=pth)
+        dt = time.perf_counter() - t0
+        nodes = fx["n_r"] * (fx["L"] + 1) * o["n_iter"]
+        ok = int(o["idx"]) == fx["out"]["chosen_idx"]
+        return dict(config="configs[0]: Ackley 2D HES-TS-AM-1, seed-pinned, 64 restarts, H=64, early stop",
+                    cpu_baseline=dict(value=nodes / dt, unit=UNIT, cores=cores, kind="port",
+                                      sample=f"the whole Actor.query loop of the BO step: {o['n_iter']} Adam iterations x 64 "
+                                             f"restarts x 2 levels in {dt:.1f} s; chosen restart {int(o['idx'])} "
+                                             f"({'=' if ok else '!='} reference {fx['out']['chosen_idx']})"),
+                    seconds=dt, n_iter=o["n_iter"], reference_loop_seconds_in_build_container=fx.get("ref_cpu_seconds"))
+    if cfg == 3:
+        prob = make_problem("Hartmann", seed=2, lengthscale=0.5)
+        d, n = prob.d, prob.train_X.shape[0]
+        ls = torch.full((1, d), prob.lengthscale, dtype=F64)
+        gp = gp_math.DenseGP.fit_caches(prob.train_X, prob.train_Y, kind=prob.kernel, lengthscale=ls,
+                                        outputscale=prob.outputscale, noise=prob.noise, mean_const=prob.mean_const)
+        nf, L, n_r = [64, 4, 2], 3, 1
+        spec = ho.HESSpec(L, nf, 1, ho.CostSpec(radius=prob.radius, k=1, max_noise=1e-5, p_norm=2.0), enable_ts=False)
+        gen = torch.Generator().manual_seed(1)
+        cnt = [n_r * math.prod(nf[:s]) for s in range(L + 1)]
+        maps = [torch.rand(c, d, dtype=F64, generator=gen).requires_grad_(True) for c in cnt]
+        base = [gp_math.sobol_normal_base_samples(f, 1, 0).reshape(-1) for f in nf]
+        abase = gp_math.sobol_normal_base_samples(64, 1, 1).reshape(-1)
+        prev_X, prev_y = prob.train_X[-1:].expand(n_r, -1), prob.train_Y[-1:].expand(n_r, -1)
+        times = []
+        for _ in range(3):
+            t0 = time.perf_counter()
+            o = ho.hes_forward(spec, prev_X, prev_y, None, [torch.sigmoid(m) for m in maps], gp=gp, design_base=base,
+                               action_base=abase, enable_noise=False)
+            tot = (o["acqf_loss"] + (2 * math.sqrt(d) - o["acqf_cost"]).abs()).mean()
+            torch.autograd.grad(tot, maps)
+            times.append(time.perf_counter() - t0)
+        dt = min(times[1:])
+        return dict(config="configs[2]: Hartmann 6D HES-MC tree nf=[64,4,2], n=500",
+                    cpu_baseline=dict(value=sum(cnt) / dt, unit=UNIT, cores=cores, kind="port",
+                                      sample=f"1 restart = {sum(cnt)} tree nodes, forward + autograd backward, best of 2 "
+                                             f"after a warm-up ({dt:.1f} s each); extrapolated per node to 256 restarts "
+                                             "(the dense fantasy models need ~4.5 GB of host memory per restart)"),
+                    seconds=dt)
+    if cfg == 4:
+        prob = make_problem("Cosine8", seed=2)
+        d, n, Hh, L, N = prob.d, prob.train_X.shape[0], 64, 3, 64
+        ls = torch.full((1, d), prob.lengthscale, dtype=F64)
+        gp = gp_math.DenseGP.fit_caches(prob.train_X, prob.train_Y, kind=prob.kernel, lengthscale=ls,
+                                        outputscale=prob.outputscale, noise=prob.noise, mean_const=prob.mean_const)
+        torch.manual_seed(2)
+        pth = gp_math.draw_matheron_path(gp, prob.train_Y, 1)
+        from nonmyopia_b200.amortized_network import AmortizedNetwork
+        net = AmortizedNetwork(d + 1, d, Hh, 1, torch.tensor([[0.0, 1.0]] * d, dtype=F64)).double()
+        spec = ho.HESSpec(L, [1] * L, 1, ho.CostSpec(radius=prob.radius, k=1, max_noise=1e-5, p_norm=2.0), enable_ts=True)
+        prev_x = prob.train_X[-1:].expand(N, -1).contiguous()
+        prev_y = prob.train_Y[-1:].expand(N, -1).contiguous()
+        prev_h = torch.randn(N, Hh, dtype=F64)
+
+        def run(n_iter):
+            P = {k: v.detach().clone() for k, v in net.state_dict().items()}
+            t0 = time.perf_counter()
+            ho.query_loop(spec, prev_x, prev_y, prev_h, P, budget=2 * math.sqrt(d), lr=1e-3, n_iter=n_iter,
+                          past_initial=False, path=pth)
+            return time.perf_counter() - t0
+
+        run(2)
+        n_iter = int(max(4, min(150, 10.0 / max(run(4) / 4, 1e-6))))
+        dt = run(n_iter)
+        return dict(config="configs[3]: Cosine8 8D HES-TS-AM-3, n=200, 64 restarts, FP64",
+                    cpu_baseline=dict(value=N * (L + 1) * n_iter / dt, unit=UNIT, cores=cores, kind="port",
+                                      sample=f"64 restarts x 4 levels, {n_iter} Adam iterations ({dt:.1f} s)"),
+                    seconds=dt)
+    raise ValueError(cfg)
 
 
 def run_reference(args, rank, world):
@@ -576,7 +679,10 @@ def main():
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))
     local_rank = int(os.environ.get("LOCAL_RANK", 0))
-    if args.impl == "reference":
+    if args.cpu_config is not None:
+        if rank == 0:
+            print(json.dumps(cpu_baseline_config(args.cpu_config)), flush=True)
+    elif args.impl == "reference":
         run_reference(args, rank, world)
     else:
         run_b200(args, rank, world, local_rank)

@@ -96,6 +96,40 @@ struct PhaseClk {
 #endif
 
 // ---------------------------------------------------------------- geometry / shared memory
+// Shared-memory copy of the policy's vectors and thin matrices (embedding [d+1][H], output layers [H][d], every bias):
+// the activation epilogues read them right after a GEMM, where a global load - even an L1 hit - sat on the critical
+// path (ncu r02a: 17 % of the forward rollout's stall samples were long-scoreboard waits on these __ldg).
+struct SmallPar {
+    const double* base;
+    int off[S_COUNT];
+    __host__ __device__ static bool small(int seg) {
+        return seg == S_WE || seg == S_BE || seg == S_BP || seg == S_BIH || seg == S_BHH || seg == S_AB0 || seg == S_AB3 ||
+               seg == S_AW6 || seg == S_AB6 || seg == S_XB0 || seg == S_XB3 || seg == S_XW6 || seg == S_XB6;
+    }
+    __host__ __device__ static int elems(const PolicyLayout& lay) {
+        int n = 0;
+        for (int sg = 0; sg < S_COUNT; ++sg)
+            if (small(sg)) n += (lay.off[sg + 1] - lay.off[sg] + 1) & ~1;      // even: double2 loads stay aligned
+        return n;
+    }
+    __device__ void init(const PolicyLayout& lay, const double* smem) {
+        base = smem;
+        int n = 0;
+        for (int sg = 0; sg < S_COUNT; ++sg) {
+            off[sg] = n;
+            if (small(sg)) n += (lay.off[sg + 1] - lay.off[sg] + 1) & ~1;
+        }
+    }
+    __device__ void load(const PolicyLayout& lay, const double* __restrict__ theta_t, double* smem, int tid, int nthr) const {
+        for (int sg = 0; sg < S_COUNT; ++sg) {
+            if (!small(sg)) continue;
+            const int n = lay.off[sg + 1] - lay.off[sg];
+            for (int e = tid; e < n; e += nthr) smem[off[sg] + e] = __ldg(theta_t + lay.off[sg] + e);
+        }
+    }
+    __device__ __forceinline__ const double* at(int seg) const { return base + off[seg]; }
+};
+
 // weight ring as seen by producer and consumers
 struct MmaRing {
     double* stage;
@@ -104,7 +138,7 @@ struct MmaRing {
 };
 
 struct MmaSmem {
-    double *IN, *OUT, *B0, *B1, *HA, *HB, *stage, *cost_acc, *tab;
+    double *IN, *OUT, *B0, *B1, *HA, *HB, *stage, *cost_acc, *tab, *par;
     unsigned full0, empty0;     // shared addresses of the mbarrier arrays
     int rows, KS;
     __device__ void carve(double* base, int d, int H, int rows_) {
@@ -113,6 +147,7 @@ struct MmaSmem {
         double* p = base;
         stage = p; p += kStages * kStageElems;                 // 16-byte aligned bulk-copy destinations first
         tab = p; p += NMB_FAST_TAB_LEN;
+        par = nullptr;
         B0 = p; p += rows * KS;
         B1 = p; p += rows * KS;
         HA = p; p += rows * KS;
@@ -125,13 +160,14 @@ struct MmaSmem {
     }
     // Row group [row_off, row_off + rows_g) of a CTA of rows_total rows: the groups' buffers lie one after the other
     // behind the shared weight ring, the mbarriers behind the last group (same footprint as carve(rows_total)).
-    __device__ void carve_group(double* base, int d, int H, int rows_total, int row_off, int rows_g) {
+    __device__ void carve_group(double* base, int d, int H, int rows_total, int row_off, int rows_g, int n_par) {
         rows = rows_g;
         KS = H + 4;
         const int per_row = 4 * KS + 2 * d + 2;
         stage = base;
         tab = base + kStages * kStageElems;
-        double* p = tab + NMB_FAST_TAB_LEN + (size_t)row_off * per_row;
+        par = tab + NMB_FAST_TAB_LEN;
+        double* p = par + n_par + (size_t)row_off * per_row;
         B0 = p; p += rows * KS;
         B1 = p; p += rows * KS;
         HA = p; p += rows * KS;
@@ -139,12 +175,14 @@ struct MmaSmem {
         IN = p; p += (d + 1) * rows;
         OUT = p; p += d * rows;
         cost_acc = p;
-        full0 = smem_u32(tab + NMB_FAST_TAB_LEN + (size_t)rows_total * per_row);
+        full0 = smem_u32(par + n_par + (size_t)rows_total * per_row);
         empty0 = full0 + 8 * kStages;
     }
     static size_t bytes(int d, int H, int rows) {
-        return ((size_t)kStages * kStageElems + NMB_FAST_TAB_LEN + (size_t)4 * rows * (H + 4) + (size_t)(2 * d + 2) * rows +
-                2 * kStages) * 8;
+        PolicyLayout lay;
+        lay.init(d, H, 1);
+        return ((size_t)kStages * kStageElems + NMB_FAST_TAB_LEN + SmallPar::elems(lay) + (size_t)4 * rows * (H + 4) +
+                (size_t)(2 * d + 2) * rows + 2 * kStages) * 8;
     }
     __device__ MmaRing ring() const { return MmaRing{stage, full0, empty0, KS}; }
 };
@@ -292,7 +330,7 @@ __device__ __forceinline__ void zero_acc4(double (&acc)[4][2]) {
 __device__ __forceinline__ void mma_policy_forward(const PolicyLayout& lay, const double* __restrict__ theta_t, bool head_a,
                                                    const MmaSmem& sm, MmaWarp& w, double* hprev, double* hnew,
                                                    const SaveAreas<double>* save, long long node0, int nvalid,
-                                                   double* __restrict__ hs_out, PhaseClk& pc) {
+                                                   double* __restrict__ hs_out, PhaseClk& pc, const SmallPar& sp) {
     const int d = lay.d, H = lay.H, rows = sm.rows, KS = sm.KS;
     const int tid = w.tid, nthr = w.nthr;
     const MmaRing ring = sm.ring();
@@ -302,13 +340,13 @@ __device__ __forceinline__ void mma_policy_forward(const PolicyLayout& lay, cons
     auto nmb_tanh_tab_ = [tab](double x) { return nmb_tanh_tab(x, tab); };
     // ---- embedding (K = d+1): B0 = elu(We [x;y] + be)
     {
-        const double* Wt = theta_t + lay.off[S_WE];      // [d+1][H]
-        const double* b = theta_t + lay.off[S_BE];
+        const double* Wt = sp.at(S_WE);                  // [d+1][H]
+        const double* b = sp.at(S_BE);
 #pragma unroll 4
         for (int e = tid; e < rows * H; e += nthr) {
             const int r = e / H, o = e - r * H;
-            double a = __ldg(b + o);
-            for (int k = 0; k <= d; ++k) a = fma(sm.IN[k * rows + r], __ldg(Wt + k * H + o), a);
+            double a = b[o];
+            for (int k = 0; k <= d; ++k) a = fma(sm.IN[k * rows + r], Wt[k * H + o], a);
             const double v = nmb_elu_tab_(a);
             sm.B0[r * KS + o] = v;
             if (save && r < nvalid) save->EA[(node0 + r) * H + o] = v;
@@ -336,7 +374,7 @@ __device__ __forceinline__ void mma_policy_forward(const PolicyLayout& lay, cons
     for (int t = 0; t < 4; ++t) {
         const int o = w.col0 + 8 * t + 2 * w.fk;
         if (o < H) {
-            const double2 bb = __ldg(reinterpret_cast<const double2*>(theta_t + lay.off[S_BP] + o));
+            const double2 bb = *reinterpret_cast<const double2*>(sp.at(S_BP) + o);
             const double2 v = make_double2(nmb_elu_tab_(acc[t][0] + bb.x), nmb_elu_tab_(acc[t][1] + bb.y));
             *reinterpret_cast<double2*>(sm.B1 + row * KS + o) = v;
             if (save && rv) *reinterpret_cast<double2*>(save->P + nrow + o) = v;
@@ -348,8 +386,8 @@ __device__ __forceinline__ void mma_policy_forward(const PolicyLayout& lay, cons
     // ---- GRU cell (gates r, z, n of the same (row, col) stay in registers)
     {
         double rg[4][2], zg[4][2], gh[4][2];
-        const double* bih = theta_t + lay.off[S_BIH];
-        const double* bhh = theta_t + lay.off[S_BHH];
+        const double* bih = sp.at(S_BIH);
+        const double* bhh = sp.at(S_BHH);
         pc.mark(2);
         zero_acc4(acc);
         mma_gemm<kStages>(ring, w, sm.B1, H, acc);
@@ -359,7 +397,7 @@ __device__ __forceinline__ void mma_policy_forward(const PolicyLayout& lay, cons
         for (int t = 0; t < 4; ++t) {
             const int o = min(w.col0 + 8 * t + 2 * w.fk, H - 2);
 #pragma unroll
-            for (int j = 0; j < 2; ++j) rg[t][j] = nmb_sigmoid_tab_(acc[t][j] + __ldg(bih + o + j) + __ldg(bhh + o + j));
+            for (int j = 0; j < 2; ++j) rg[t][j] = nmb_sigmoid_tab_(acc[t][j] + bih[o + j] + bhh[o + j]);
         }
         pc.mark(2);
         zero_acc4(acc);
@@ -370,7 +408,7 @@ __device__ __forceinline__ void mma_policy_forward(const PolicyLayout& lay, cons
         for (int t = 0; t < 4; ++t) {
             const int o = min(w.col0 + 8 * t + 2 * w.fk, H - 2);
 #pragma unroll
-            for (int j = 0; j < 2; ++j) zg[t][j] = nmb_sigmoid_tab_(acc[t][j] + __ldg(bih + H + o + j) + __ldg(bhh + H + o + j));
+            for (int j = 0; j < 2; ++j) zg[t][j] = nmb_sigmoid_tab_(acc[t][j] + bih[H + o + j] + bhh[H + o + j]);
         }
         pc.mark(2);
         zero_acc4(acc);
@@ -385,8 +423,8 @@ __device__ __forceinline__ void mma_policy_forward(const PolicyLayout& lay, cons
                 double hn[2], ng[2], hv[2];
 #pragma unroll
                 for (int j = 0; j < 2; ++j) {
-                    hn[j] = gh[t][j] + __ldg(bhh + 2 * H + o + j);
-                    ng[j] = nmb_tanh_tab_(acc[t][j] + __ldg(bih + 2 * H + o + j) + rg[t][j] * hn[j]);
+                    hn[j] = gh[t][j] + bhh[2 * H + o + j];
+                    ng[j] = nmb_tanh_tab_(acc[t][j] + bih[2 * H + o + j] + rg[t][j] * hn[j]);
                     const double hp = hprev[row * KS + o + j];
                     hv[j] = (1.0 - zg[t][j]) * ng[j] + zg[t][j] * hp;
                 }
@@ -418,7 +456,7 @@ __device__ __forceinline__ void mma_policy_forward(const PolicyLayout& lay, cons
     for (int t = 0; t < 4; ++t) {
         const int o = w.col0 + 8 * t + 2 * w.fk;
         if (o < H) {
-            const double2 bb = __ldg(reinterpret_cast<const double2*>(theta_t + lay.off[sB0] + o));
+            const double2 bb = *reinterpret_cast<const double2*>(sp.at(sB0) + o);
             const double2 v = make_double2(nmb_elu_tab_(acc[t][0] + bb.x), nmb_elu_tab_(acc[t][1] + bb.y));
             *reinterpret_cast<double2*>(sm.B0 + row * KS + o) = v;
             if (save && rv) *reinterpret_cast<double2*>(save->U1 + nrow + o) = v;
@@ -436,7 +474,7 @@ __device__ __forceinline__ void mma_policy_forward(const PolicyLayout& lay, cons
     for (int t = 0; t < 4; ++t) {
         const int o = w.col0 + 8 * t + 2 * w.fk;
         if (o < H) {
-            const double2 bb = __ldg(reinterpret_cast<const double2*>(theta_t + lay.off[sB3] + o));
+            const double2 bb = *reinterpret_cast<const double2*>(sp.at(sB3) + o);
             const double2 v = make_double2(nmb_elu_tab_(acc[t][0] + bb.x), nmb_elu_tab_(acc[t][1] + bb.y));
             *reinterpret_cast<double2*>(hprev + row * KS + o) = v;
             if (save && rv) *reinterpret_cast<double2*>(save->U2 + nrow + o) = v;
@@ -447,8 +485,8 @@ __device__ __forceinline__ void mma_policy_forward(const PolicyLayout& lay, cons
     pc.mark(3);
     // ---- output layer (O = d): out = sigmoid(W6 u2 + b6); 4 threads per output, 2 interleaved chains each
     {
-        const double* Wt = theta_t + lay.off[sW6];       // [H][d]
-        const double* b = theta_t + lay.off[sB6];
+        const double* Wt = sp.at(sW6);                   // [H][d]
+        const double* b = sp.at(sB6);
         const int sub = tid & 3;
         for (int e = tid >> 2; e < ((rows * d + 7) & ~7); e += nthr >> 2) {
             const bool ok = e < rows * d;
@@ -456,14 +494,14 @@ __device__ __forceinline__ void mma_policy_forward(const PolicyLayout& lay, cons
             double a0 = 0.0, a1 = 0.0;
             const double* u = hprev + r * KS;
             for (int k = sub; k < H; k += 8) {
-                a0 = fma(u[k], __ldg(Wt + k * d + o), a0);
-                if (k + 4 < H) a1 = fma(u[k + 4], __ldg(Wt + (k + 4) * d + o), a1);
+                a0 = fma(u[k], Wt[k * d + o], a0);
+                if (k + 4 < H) a1 = fma(u[k + 4], Wt[(k + 4) * d + o], a1);
             }
             double a = a0 + a1;
             a += __shfl_xor_sync(0xffffffffu, a, 1);
             a += __shfl_xor_sync(0xffffffffu, a, 2);
             if (ok && sub == 0) {
-                const double v = nmb_sigmoid_tab_(a + __ldg(b + o));
+                const double v = nmb_sigmoid_tab_(a + b[o]);
                 sm.OUT[o * rows + r] = v;
                 if (save && r < nvalid) save->OUT[(node0 + r) * d + o] = v;
             }

@@ -246,7 +246,9 @@ __global__ void __launch_bounds__(kMaxRowsMma * 8 + 32, 1)
     const int nvalid = (int)max(0LL, min((long long)rows, N - chain0));
 
     MmaSmem sm;
-    sm.carve_group(reinterpret_cast<T*>(nmb_smem_raw), d, H, rows_cta, grp ? rowsA : 0, rows);
+    SmallPar sp;
+    sm.carve_group(reinterpret_cast<T*>(nmb_smem_raw), d, H, rows_cta, grp ? rowsA : 0, rows, SmallPar::elems(pb.lay));
+    sp.init(pb.lay, sm.par);
     if (threadIdx.x == 0) {
         for (int s = 0; s < kStages; ++s) {
             mbar_init(sm.full0 + 8 * s, 1);
@@ -255,6 +257,7 @@ __global__ void __launch_bounds__(kMaxRowsMma * 8 + 32, 1)
         fence_barrier_init();
     }
     load_fast_tab(sm.tab, (int)threadIdx.x, (int)blockDim.x);
+    sp.load(pb.lay, ro.theta_t, sm.par, (int)threadIdx.x, (int)blockDim.x);
     __syncthreads();
     if ((int)threadIdx.x >= nthr_all) {      // producer warp
         mma_producer<kStages, false>(pb.lay, ro.theta_t, L, sm.ring(), ro.level_begin, ro.level_end);
@@ -302,7 +305,7 @@ __global__ void __launch_bounds__(kMaxRowsMma * 8 + 32, 1)
         T* hs_out = ro.has_save ? ro.sv.HS + ((size_t)(l + 1) * N + chain0) * H : nullptr;
         T* hprev = (l & 1) ? sm.HB : sm.HA;
         T* hnew = (l & 1) ? sm.HA : sm.HB;
-        mma_policy_forward(pb.lay, ro.theta_t, head_a, sm, w, hprev, hnew, sv, node0, nvalid, hs_out, pc);
+        mma_policy_forward(pb.lay, ro.theta_t, head_a, sm, w, hprev, hnew, sv, node0, nvalid, hs_out, pc, sp);
 
         // ---- output point, Thompson path, cost: 8 threads per chain (nthr = 8 rows)
         const int r = tid >> 3, lane = tid & 7;

@@ -160,7 +160,7 @@ def free_restart_loop(objective: Callable[[List[Tensor]], Dict], params: List[Te
                       opt_step: Callable[[Sequence[Optional[Tensor]]], None], *, budget: float, n_iter: int,
                       past_initial: bool, n_global: Optional[int] = None, group=None, save_trajectory: bool = False,
                       log: Optional[Callable[[str], None]] = print, use_graph: bool = False,
-                      pre_iteration: Optional[Callable[[], None]] = None) -> Dict:
+                      pre_iteration: Optional[Callable[[], None]] = None, timing: Optional[dict] = None) -> Dict:
     """The reference's AdamW loop for free-parameter algorithms (actor.py:558-656; HES-TS, HES-MC, qEI ... qKG)
     over this rank's restarts.
 
@@ -174,7 +174,8 @@ def free_restart_loop(objective: Callable[[List[Tensor]], Dict], params: List[Te
     the minima every iteration for the reference's snapshot / early-stop rule (one synchronisation per iteration
     instead of ~100 eager launches).  Requires an objective without per-call host randomness: host-stream draws
     are made resident by ``pre_iteration()`` (called before every iteration, eager or replayed) in a static device
-    buffer the objective reads."""
+    buffer the objective reads.  ``timing`` (a dict, optional) receives ``ms_per_iter``: CUDA-event time of the
+    replayed iterations (everything after the capture), host reads included."""
     best = dict(loss=None, cost=None, KL=0)
     best_min = float("inf")
     snap, stall = {}, 0
@@ -214,6 +215,10 @@ def free_restart_loop(objective: Callable[[List[Tensor]], Dict], params: List[Te
                     torch.cuda.synchronize()
                     graph, keep = False, (lambda t: t.detach())
             if graph:
+                if timing is not None and "t0" not in timing and ep > warm:
+                    timing["t0"] = torch.cuda.Event(enable_timing=True)
+                    timing["t0"].record()
+                    timing["ep0"] = ep
                 graph.replay()
                 local_maps, rd, cand = static
             else:
@@ -227,9 +232,12 @@ def free_restart_loop(objective: Callable[[List[Tensor]], Dict], params: List[Te
             local_maps, rd, cand = iteration()
         acqf_loss, acqf_cost = rd["acqf_loss"], rd["acqf_cost"]
         if save_trajectory:
-            saved_trajectory.append([x.cpu().detach().tolist() for x in local_maps])
-            saved_loss.append(acqf_loss.tolist())
-            saved_cost.append(acqf_cost.tolist())
+            # history stays on the device (one small copy per level); it is converted once after the loop - the
+            # reference's per-iteration .cpu().tolist() (actor.py:561-564) would put a host sync and, at the
+            # Hartmann tree's size, 1.28 M doubles of list building into every iteration
+            saved_trajectory.append([x.detach().clone() for x in local_maps])
+            saved_loss.append(acqf_loss.detach().clone())
+            saved_cost.append(acqf_cost.detach().clone())
         cand = allreduce_min(cand.clone() if group is not None else cand, group).tolist()
         if ep == 0 or cand[0] < best_min:
             best = dict(loss=keep(acqf_loss), cost=keep(acqf_cost), KL=0)
@@ -246,6 +254,15 @@ def free_restart_loop(objective: Callable[[List[Tensor]], Dict], params: List[Te
             break
     if use_graph:
         torch.cuda.current_stream().wait_stream(side)
+    if timing is not None and "t0" in timing:
+        t1 = torch.cuda.Event(enable_timing=True)
+        t1.record()
+        torch.cuda.synchronize()
+        timing["ms_per_iter"] = timing["t0"].elapsed_time(t1) / max(n_done - timing["ep0"], 1)
+    if save_trajectory:
+        saved_trajectory = [[x.cpu().tolist() for x in lv] for lv in saved_trajectory]
+        saved_loss = [x.tolist() for x in saved_loss]
+        saved_cost = [x.tolist() for x in saved_cost]
     return dict(best_loss=best["loss"], best_cost=best["cost"], best_KL=0, best_next_X=snap["X"],
                 best_actions=snap["actions"], best_hidden_state=None, saved_trajectory=saved_trajectory,
                 saved_loss=saved_loss, saved_cost=saved_cost, n_iter=n_done)
