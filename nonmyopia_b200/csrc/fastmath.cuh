@@ -221,6 +221,7 @@ NMB_HD void nmb_sincospi_tab(double x, const double* __restrict__ tab, double* s
     *cs = fma(tc, dc, fma(-ts, s, tc));
 }
 
+
 NMB_HD double nmb_rcp2(double a) {      // 1 / a, a in [2^-500, 2^500]: rcp.approx (2^-23) + 2 Newton steps
 #ifdef __CUDA_ARCH__
     double r;
@@ -234,17 +235,41 @@ NMB_HD double nmb_rcp2(double a) {      // 1 / a, a in [2^-500, 2^500]: rcp.appr
 #endif
 }
 
+// |x| <= lim for a limit whose low word is zero (40, 20, 60 ...), decided on the high word alone: five integer
+// instructions instead of the fourteen of fmin(fmax()) with its NaN handling (a NaN comes out as +-lim)
+NMB_HD double nmb_clamp_abs(double x, double lim) {
+#ifdef __CUDA_ARCH__
+    const int hi = __double2hiint(x), lhi = __double2hiint(lim);
+    const bool over = (hi & 0x7fffffff) >= lhi;
+    return __hiloint2double(over ? ((hi & 0x80000000) | lhi) : hi, over ? 0 : __double2loint(x));
+#else
+    return fmin(fmax(x, -lim), lim);
+#endif
+}
+// min(x, 0) clamped at -60 (the ELU's exponential argument)
+NMB_HD double nmb_neg_part_clamped(double x) {
+#ifdef __CUDA_ARCH__
+    const int hi = __double2hiint(x);
+    const bool pos = hi >= 0, big = (hi & 0x7fffffff) >= 0x404E0000;
+    return __hiloint2double(pos ? 0 : (big ? (int)0xC04E0000 : hi), (pos || big) ? 0 : __double2loint(x));
+#else
+    return fmax(fmin(x, 0.0), -60.0);
+#endif
+}
+
+// rcp.approx.f64 works on the upper 32 bits (20 mantissa bits): two Newton steps reach 2^-80, i.e. full double
+// precision (measured on the device: identical worst-case error to three steps, tests/test_fastmath.py)
 NMB_HD double nmb_sigmoid_tab(double x, const double* __restrict__ tab) {
-    x = fmin(fmax(x, -40.0), 40.0);
-    return nmb_rcp(1.0 + nmb_exp_tab_nc(-x, tab));
+    x = nmb_clamp_abs(x, 40.0);
+    return nmb_rcp2(1.0 + nmb_exp_tab_nc(-x, tab));
 }
 NMB_HD double nmb_tanh_tab(double x, const double* __restrict__ tab) {
-    x = fmin(fmax(x, -20.0), 20.0);
+    x = nmb_clamp_abs(x, 20.0);
     const double em = nmb_expm1_tab_nc(2.0 * x, tab);
-    return em * nmb_rcp(em + 2.0);
+    return em * nmb_rcp2(em + 2.0);
 }
 NMB_HD double nmb_elu_tab(double x, const double* __restrict__ tab) {
-    const double e = nmb_expm1_tab_nc(fmax(fmin(x, 0.0), -60.0), tab);
+    const double e = nmb_expm1_tab_nc(nmb_neg_part_clamped(x), tab);
     return x > 0.0 ? x : e;
 }
 

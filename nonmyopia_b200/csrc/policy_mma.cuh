@@ -276,10 +276,12 @@ struct MmaWarp {
     bool active;           // this warp's 32 columns intersect [0, H)
     unsigned chunk;        // running chunk counter (same order as the producer)
     int fr, fk;            // fragment coordinates: lane >> 2, lane & 3
-    __device__ void init(int warp, int nthr_, int H) {
+    // nt = 8-column tiles per warp: 4 (two warps per 8-row block) or 2 (four warps per block)
+    __device__ void init(int warp, int nthr_, int H, int nt = 4) {
         lane = threadIdx.x & 31;
-        row0 = (warp >> 1) * 8;
-        col0 = (warp & 1) * 32;
+        const int wpr = 8 / nt;
+        row0 = (warp / wpr) * 8;
+        col0 = (warp % wpr) * (8 * nt);
         nthr = nthr_;
         active = col0 < H;
         chunk = 0;
@@ -292,9 +294,9 @@ struct MmaWarp {
 
 // acc[t] (t = 0..3: 8-column tiles of the warp's 32 columns) += A[row0.., 0..H) . W chunk stream
 // A: shared, row-major with stride KS, pointing at the first contraction column.
-template <int NST>
+template <int NST, int NT = 4>
 __device__ __forceinline__ void mma_gemm(const MmaRing& sm, MmaWarp& w, const double* __restrict__ A, int H,
-                                         double (&acc)[4][2]) {
+                                         double (&acc)[NT][2]) {
     const double* arow = A + (size_t)(w.row0 + w.fr) * sm.KS + w.fk;
     for (int k0 = 0; k0 < H; k0 += kKC) {
         const unsigned slot = w.chunk % NST, fill = w.chunk / NST;
@@ -305,11 +307,11 @@ __device__ __forceinline__ void mma_gemm(const MmaRing& sm, MmaWarp& w, const do
 #pragma unroll 4
             for (int kk = 0; kk < kn; kk += 4) {
                 const double a = arow[k0 + kk];
-                const double b0 = st[kk * kSW], b1 = st[kk * kSW + 8], b2 = st[kk * kSW + 16], b3 = st[kk * kSW + 24];
-                dmma884(acc[0], a, b0);
-                dmma884(acc[1], a, b1);
-                dmma884(acc[2], a, b2);
-                dmma884(acc[3], a, b3);
+                double b[NT];
+#pragma unroll
+                for (int t = 0; t < NT; ++t) b[t] = st[kk * kSW + 8 * t];
+#pragma unroll
+                for (int t = 0; t < NT; ++t) dmma884(acc[t], a, b[t]);
             }
         }
         __syncwarp();
@@ -318,9 +320,9 @@ __device__ __forceinline__ void mma_gemm(const MmaRing& sm, MmaWarp& w, const do
     }
 }
 
-__device__ __forceinline__ void zero_acc4(double (&acc)[4][2]) {
+template <int NT> __device__ __forceinline__ void zero_acc4(double (&acc)[NT][2]) {
 #pragma unroll
-    for (int t = 0; t < 4; ++t) { acc[t][0] = 0.0; acc[t][1] = 0.0; }
+    for (int t = 0; t < NT; ++t) { acc[t][0] = 0.0; acc[t][1] = 0.0; }
 }
 
 // One policy step, forward, for the CTA's `rows` chains (consumer warps only).
@@ -514,6 +516,11 @@ __device__ __forceinline__ void mma_policy_forward(const PolicyLayout& lay, cons
 
 // ================================================================== backward step
 constexpr int kStagesBwd = 5;          // 8 consumer warps drain a chunk in ~0.5 us: the ring must cover the L2 latency
+// 8-row x 16-col warp tiles in the reverse rollout: 16 consumer warps for 32 rows instead of 8.  Two independent DMMA
+// chains per warp already saturate the tensor pipe (dmma_chain micro-benchmark: 16.4 cycles per DMMA with 2 tiles); the
+// reverse kernel was starved at 2.25 warps per scheduler (ncu r02a: DMMA 37 % active, `wait` + scoreboard stalls
+// around the prefetched activations and the epilogues), not short of ILP inside a warp.
+constexpr int kNTB = 2;
 constexpr int kMaxRowsMmaBwd = 32;    // 7 row-major adjoint buffers (122 KB) + 5 weight stages (92 KB) in 227 KB
 
 struct MmaBwdSmem {
@@ -547,10 +554,11 @@ struct MmaBwdSmem {
 
 // the lane's 4 x double2 slice of a node-major [node][H] save area (issued BEFORE the GEMM whose epilogue uses it,
 // so the HBM/L2 latency overlaps the tensor-pipe work)
-__device__ __forceinline__ void prefetch_tile(double2 (&dst)[4], const double* __restrict__ area, size_t nrow,
+template <int NT>
+__device__ __forceinline__ void prefetch_tile(double2 (&dst)[NT], const double* __restrict__ area, size_t nrow,
                                               const MmaWarp& w, int H, bool rv) {
 #pragma unroll
-    for (int t = 0; t < 4; ++t) {
+    for (int t = 0; t < NT; ++t) {
         const int k = w.col0 + 8 * t + 2 * w.fk;
         dst[t] = (rv && k < H) ? *reinterpret_cast<const double2*>(area + nrow + k) : make_double2(0.0, 0.0);
     }
@@ -612,14 +620,14 @@ __device__ __forceinline__ void mma_policy_backward(const PolicyLayout& lay, con
     const int row = w.row0 + w.fr;
     const bool rv = row < nvalid;
     const size_t nrow = (size_t)(node0 + row) * H;
-    double acc[4][2];
+    double acc[kNTB][2];
     // ---- du1_pre = (du2_pre . W3) * elu'(u1) -> X1
-    double2 pf[4];
+    double2 pf[kNTB];
     prefetch_tile(pf, sv.U1, nrow, w, H, rv);
     zero_acc4(acc);
-    mma_gemm<kStagesBwd>(ring, w, sm.X0, H, acc);
+    mma_gemm<kStagesBwd, kNTB>(ring, w, sm.X0, H, acc);
 #pragma unroll
-    for (int t = 0; t < 4; ++t) {
+    for (int t = 0; t < kNTB; ++t) {
         const int k = w.col0 + 8 * t + 2 * w.fk;
         if (k < H) {
             double2 v = make_double2(0.0, 0.0);
@@ -633,24 +641,24 @@ __device__ __forceinline__ void mma_policy_backward(const PolicyLayout& lay, con
     }
     consumer_sync(nthr);
     // ---- d[p; h'] = du1_pre . W0 : first H columns -> raw dp (X2), second H columns -> GRU backward
-    double2 prg[4], pzg[4], png[4], phn[4], php[4];
+    double2 prg[kNTB], pzg[kNTB], png[kNTB], phn[kNTB], php[kNTB];
     prefetch_tile(prg, sv.RG, nrow, w, H, rv);
     prefetch_tile(pzg, sv.ZG, nrow, w, H, rv);
     prefetch_tile(png, sv.NG, nrow, w, H, rv);
     prefetch_tile(phn, sv.HN, nrow, w, H, rv);
     prefetch_tile(php, sv.HS, nrow, w, H, rv);      // HS[level] = h before the step
     zero_acc4(acc);
-    mma_gemm<kStagesBwd>(ring, w, sm.X1, H, acc);
+    mma_gemm<kStagesBwd, kNTB>(ring, w, sm.X1, H, acc);
 #pragma unroll
-    for (int t = 0; t < 4; ++t) {
+    for (int t = 0; t < kNTB; ++t) {
         const int k = w.col0 + 8 * t + 2 * w.fk;
         if (k < H) *reinterpret_cast<double2*>(sm.X2 + row * KS + k) = make_double2(acc[t][0], acc[t][1]);
     }
     zero_acc4(acc);
-    mma_gemm<kStagesBwd>(ring, w, sm.X1, H, acc);
+    mma_gemm<kStagesBwd, kNTB>(ring, w, sm.X1, H, acc);
     // X0 (du2_pre), X3..X5 are dead for every warp here (barriers above / end of the previous step)
 #pragma unroll
-    for (int t = 0; t < 4; ++t) {
+    for (int t = 0; t < kNTB; ++t) {
         const int k = w.col0 + 8 * t + 2 * w.fk;
         if (k < H) {
             double dr[2] = {0, 0}, dz[2] = {0, 0}, dn[2] = {0, 0}, dnh[2] = {0, 0}, dhp[2] = {0, 0};
@@ -684,14 +692,14 @@ __device__ __forceinline__ void mma_policy_backward(const PolicyLayout& lay, con
     consumer_sync(nthr);
     // ---- dp_pre = (raw dp + dgi . Wih) * elu'(p) -> X2
     prefetch_tile(pf, sv.P, nrow, w, H, rv);
-    double2 pea[4];
+    double2 pea[kNTB];
     prefetch_tile(pea, sv.EA, nrow, w, H, rv);
     zero_acc4(acc);
-    mma_gemm<kStagesBwd>(ring, w, sm.X0, H, acc);
-    mma_gemm<kStagesBwd>(ring, w, sm.X3, H, acc);
-    mma_gemm<kStagesBwd>(ring, w, sm.X4, H, acc);
+    mma_gemm<kStagesBwd, kNTB>(ring, w, sm.X0, H, acc);
+    mma_gemm<kStagesBwd, kNTB>(ring, w, sm.X3, H, acc);
+    mma_gemm<kStagesBwd, kNTB>(ring, w, sm.X4, H, acc);
 #pragma unroll
-    for (int t = 0; t < 4; ++t) {
+    for (int t = 0; t < kNTB; ++t) {
         const int k = w.col0 + 8 * t + 2 * w.fk;
         if (k < H) {
             double2 v = make_double2(0.0, 0.0);
@@ -706,11 +714,11 @@ __device__ __forceinline__ void mma_policy_backward(const PolicyLayout& lay, con
     }
     // ---- dh_prev += dr . Whh_r + dz . Whh_z + dnh . Whh_n
     zero_acc4(acc);
-    mma_gemm<kStagesBwd>(ring, w, sm.X0, H, acc);
-    mma_gemm<kStagesBwd>(ring, w, sm.X3, H, acc);
-    mma_gemm<kStagesBwd>(ring, w, sm.X5, H, acc);
+    mma_gemm<kStagesBwd, kNTB>(ring, w, sm.X0, H, acc);
+    mma_gemm<kStagesBwd, kNTB>(ring, w, sm.X3, H, acc);
+    mma_gemm<kStagesBwd, kNTB>(ring, w, sm.X5, H, acc);
 #pragma unroll
-    for (int t = 0; t < 4; ++t) {
+    for (int t = 0; t < kNTB; ++t) {
         const int k = w.col0 + 8 * t + 2 * w.fk;
         if (k < H) {
             double2* g = reinterpret_cast<double2*>(sm.GH + row * KS + k);
@@ -721,9 +729,9 @@ __device__ __forceinline__ void mma_policy_backward(const PolicyLayout& lay, con
     consumer_sync(nthr);
     // ---- de_pre = (dp_pre . Wp) * elu'(ea) -> X1
     zero_acc4(acc);
-    mma_gemm<kStagesBwd>(ring, w, sm.X2, H, acc);
+    mma_gemm<kStagesBwd, kNTB>(ring, w, sm.X2, H, acc);
 #pragma unroll
-    for (int t = 0; t < 4; ++t) {
+    for (int t = 0; t < kNTB; ++t) {
         const int k = w.col0 + 8 * t + 2 * w.fk;
         if (k < H) {
             double2 v = make_double2(0.0, 0.0);

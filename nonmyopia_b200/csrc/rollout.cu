@@ -527,7 +527,7 @@ __global__ void __launch_bounds__(kNT, 1) ts_rollout_bwd_kernel(ProblemDev<T> pb
 
 // ================================================================== backward, FP64 tensor pipe + TMA weight stream
 template <int DMAX>
-__global__ void __launch_bounds__(kMaxRowsMmaBwd * 8 + 32, 1)
+__global__ void __launch_bounds__(kMaxRowsMmaBwd * (32 / kNTB) + 32, 1)
     ts_rollout_bwd_mma_kernel(ProblemDev<double> pb, RolloutDev<double> ro, const double* __restrict__ g_loss,
                               const double* __restrict__ g_cost, const double* __restrict__ g_X,
                               const double* __restrict__ g_A, double* __restrict__ g_prev, int rows) {
@@ -538,7 +538,7 @@ __global__ void __launch_bounds__(kMaxRowsMmaBwd * 8 + 32, 1)
     const long long chain0 = (long long)blockIdx.x * rows;
     const int nvalid = (int)min((long long)rows, N - chain0);
     const int tid = threadIdx.x;
-    const int ncw = rows >> 2, nthr = ncw * 32;
+    const int ncw = (rows >> 3) * (8 / kNTB), nthr = ncw * 32;
     const long long step = pb.step_ptr ? *pb.step_ptr : 0;
 
     MmaBwdSmem sm;
@@ -556,7 +556,7 @@ __global__ void __launch_bounds__(kMaxRowsMmaBwd * 8 + 32, 1)
         return;
     }
     MmaWarp w;
-    w.init(tid >> 5, nthr, H);
+    w.init(tid >> 5, nthr, H, kNTB);
     const int KS = sm.KS;
     T* carry = sm.carry;      // [(DMAX+1)][rows]: adjoint of (x_{l+1}, y_{l+1}) from the level above
 
@@ -762,8 +762,8 @@ static int launch_bwd_mma(const nmb_ts_problem_t* p, const nmb_ts_rollout_t* r, 
     auto kern = ts_rollout_bwd_mma_kernel<DMAX>;
     NMB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     dim3 grid((unsigned)((p->n_chains + rows - 1) / rows));
-    kern<<<grid, rows * 8 + 32, smem, st>>>(pb, r0, (const double*)gl, (const double*)gc, (const double*)gX,
-                                            (const double*)gA, (double*)gprev, rows);
+    kern<<<grid, rows * (32 / kNTB) + 32, smem, st>>>(pb, r0, (const double*)gl, (const double*)gc, (const double*)gX,
+                                                       (const double*)gA, (double*)gprev, rows);
     NMB_LAUNCH_CHECK();
     return 0;
 }
