@@ -286,6 +286,21 @@ int nmb_cholesky_root(int dtype, int n, int batch, void* A, int64_t lda, int64_t
                       int64_t stride_i, int32_t* info, void* stream);
 
 /* ------------------------------------------------------------------------
+ * Exact marginal log-likelihood of the surrogate and its hyper-parameter gradient: the arithmetic of
+ * `fit_gpytorch_mll(ExactMarginalLogLikelihood(likelihood, SingleTaskGP(...)))` in the reference's BO loop
+ * (main.py:472-486; BoTorch / GPyTorch restated).  FP64.  Inputs: the training data,
+ * 1 / lengthscale [d], the mean constant, and L / L^-1 of K + s2 I from nmb_kernel_matrix + nmb_cholesky_root.
+ * out [5 + d] (device): 0 quad = (y-c)^T Khat^-1 (y-c), 1 log det Khat, 2 sum(alpha), 3 tr G, 4 tr(G kappa),
+ * 5 + k tr(G dkappa / dlengthscale_k), with alpha = Khat^-1 (y-c), G = alpha alpha^T - Khat^-1, kappa the unit-amplitude
+ * kernel, so that d(-log p)/d theta = -1/2 tr(G dKhat/d theta) and d(-log p)/dc = -sum(alpha).  Deterministic.
+ * work: nmb_gp_mll_workspace_elems doubles.  n <= 800.
+ * ---------------------------------------------------------------------- */
+int64_t nmb_gp_mll_workspace_elems(int n, int d);
+int nmb_gp_mll_value_grad(int kernel_id, int d, int n, const double* X, const double* inv_ls, const double* y,
+                          double mean_const, const double* L, int64_t ldl, const double* Linv, int64_t ldi, double* work,
+                          double* out, void* stream);
+
+/* ------------------------------------------------------------------------
  * Restart shards over NVLink peer memory (one process per GPU; SURVEY 8e C2 + C3): the per-iteration exchange of
  * the sharded Actor.query loop - policy-gradient SUM and the MIN of the two snapshot-decision candidates
  * (actor.py:622-639, 641-648) - written against peer-mapped buffers, fused with the AdamW update, instead of two
