@@ -12,6 +12,8 @@
 // Inverse, block row by block row: X_ij = -L_ii^-1 sum_{j <= k < i} L_ik X_kj with the L row panel staged in shared
 // memory, a warp per 32 x 32 tile.  Fixed summation order: results do not depend on the launch.
 // info[b] follows LAPACK potrf: 0, or k > 0 if the leading minor of order k is not positive definite.
+#include <stdlib.h>
+#include <algorithm>
 #include "common.cuh"
 
 namespace nmb {
@@ -20,6 +22,7 @@ constexpr int kCB = 32;        // block size
 constexpr int kCD = 33;        // row stride of the diagonal-block buffers
 constexpr int kCP = 34;        // row stride of the panel buffer
 constexpr int kCholMaxN = 800; // GPyTorch's max_cholesky_size
+constexpr int kCholMultiMinN = 128;   // one matrix of at least this order runs on the multi-CTA path
 
 template <typename T>
 __global__ void __launch_bounds__(256) chol_root_kernel(int n, T* __restrict__ A_all, long long lda, long long strideA,
@@ -174,9 +177,218 @@ __global__ void __launch_bounds__(256) chol_root_kernel(int n, T* __restrict__ A
     }
 }
 
+// ------------------------------------------------------------------ one matrix over many CTAs
+// The same blocked algorithm with the three phases of a block step as separate launches, so that the panel rows and the
+// trailing tiles of ONE matrix spread over the SMs (the single-CTA kernel above takes 5 ms at n = 500; it stays the
+// batched / small-n path).  Every element goes through the same FMA sequence as above: bit-identical results.
+//   chol_diag_kernel   (1 warp)            factor + invert the diagonal block: L_jj -> A, L_jj^-1 -> X
+//   chol_panel_kernel  (CTA per 128 rows)  P = A[below, block] L_jj^-T in place
+//   chol_update_kernel (CTA per tile)      A[tile] -= P_i P_k^T on the lower triangle
+//   chol_inverse_kernel (CTA per block column) off-diagonal blocks of L^-1, block row by block row
+template <typename T>
+__global__ void __launch_bounds__(32) chol_diag_kernel(int n, int j0, T* __restrict__ A, long long lda, T* __restrict__ X,
+                                                       long long ldx, int* __restrict__ info) {
+    // register-resident: lane = row of the block during the factorisation (column k travels by shuffle), lane =
+    // column of the inverse during the forward substitution (row r of L travels by shuffle); the arithmetic per
+    // element is the single-CTA kernel's (terms added for t < c are exact zeros)
+    if (*info) return;
+    const int lane = threadIdx.x, nb = min(kCB, n - j0);
+    T row[kCB];
+#pragma unroll
+    for (int c = 0; c < kCB; ++c) row[c] = (lane < nb && c <= lane && c < nb) ? A[(size_t)(j0 + lane) * lda + j0 + c] : T(0);
+    int fail = 0;
+#pragma unroll
+    for (int k = 0; k < kCB; ++k) {
+        if (k < nb && !fail) {
+            const T dkk = __shfl_sync(0xffffffffu, row[k], k);
+            if (!(dkk > T(0)) || !(dkk < T(INFINITY))) {
+                fail = j0 + k + 1;
+            } else {
+                const T s = Num<T>::sqrt(dkk);
+                T lrk = T(0);
+                if (lane == k) row[k] = s;
+                if (lane > k && lane < nb) { lrk = row[k] / s; row[k] = lrk; }
+#pragma unroll
+                for (int c = k + 1; c < kCB; ++c) {
+                    const T lck = __shfl_sync(0xffffffffu, lrk, c);      // D[c][k]
+                    if (c <= lane && lane < nb && c < nb) row[c] -= lrk * lck;
+                }
+            }
+        }
+    }
+    if (fail) { if (lane == 0) *info = fail; return; }
+    // inverse, lane = column c: x[r] = -(sum_{c <= t < r} L[r][t] x[t]) / L[r][r], x[c] = 1 / L[c][c]
+    T x[kCB];
+#pragma unroll
+    for (int r = 0; r < kCB; ++r) {
+        T acc = T(0);
+#pragma unroll
+        for (int t = 0; t < r; ++t) {
+            const T lrt = __shfl_sync(0xffffffffu, row[t], r);          // L[r][t]
+            if (t >= lane) acc = fma(lrt, x[t], acc);
+        }
+        const T lrr = __shfl_sync(0xffffffffu, row[r], r);
+        T v = T(0);
+        if (r < nb && lane < nb) {
+            if (r == lane) v = T(1) / lrr;
+            else if (r > lane) v = -acc / lrr;
+        }
+        x[r] = v;
+    }
+#pragma unroll
+    for (int c = 0; c < kCB; ++c)
+        if (lane < nb && c < nb) A[(size_t)(j0 + lane) * lda + j0 + c] = c <= lane ? row[c] : T(0);
+    // X block: element (r, c = lane) = x[r]; store row-wise (strided by lane: 32 x 32 block, once per step)
+#pragma unroll
+    for (int r = 0; r < kCB; ++r)
+        if (lane < nb && r < nb) X[(size_t)(j0 + r) * ldx + j0 + lane] = lane <= r ? x[r] : T(0);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(128) chol_panel_kernel(int n, int j0, T* __restrict__ A, long long lda,
+                                                         const T* __restrict__ X, long long ldx, const int* __restrict__ info) {
+    __shared__ T Di[kCB * kCD];
+    if (*info) return;
+    const int nb = min(kCB, n - j0), m = n - j0 - nb;
+    for (int e = threadIdx.x; e < kCB * kCB; e += 128) {
+        const int r = e >> 5, c = e & 31;
+        Di[r * kCD + c] = (r < nb && c <= r) ? X[(size_t)(j0 + r) * ldx + j0 + c] : T(0);
+    }
+    __syncthreads();
+    const int r = blockIdx.x * 128 + threadIdx.x;
+    if (r >= m) return;
+    T* arow = A + (size_t)(j0 + nb + r) * lda + j0;
+    T a[kCB];
+#pragma unroll
+    for (int k = 0; k < kCB; ++k) a[k] = k < nb ? arow[k] : T(0);
+#pragma unroll
+    for (int c = 0; c < kCB; ++c) {
+        T p = T(0);
+#pragma unroll
+        for (int k = 0; k <= c; ++k) p = fma(Di[c * kCD + k], a[k], p);
+        if (c < nb) arow[c] = p;
+    }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) chol_update_kernel(int n, int j0, T* __restrict__ A, long long lda,
+                                                          const int* __restrict__ info) {
+    __shared__ T Pi[kCB * kCD], Pk[kCB * kCD];
+    if (*info) return;
+    const int nb = min(kCB, n - j0), m = n - j0 - nb;
+    int ti = 0;
+    const int tile = blockIdx.x;
+    while ((ti + 1) * (ti + 2) / 2 <= tile) ++ti;
+    const int tk = tile - ti * (ti + 1) / 2;
+    const T* base = A + (size_t)(j0 + nb) * lda + j0;
+    for (int e = threadIdx.x; e < kCB * kCB; e += 256) {
+        const int r = e >> 5, c = e & 31;
+        const int ri = ti * kCB + r, rk = tk * kCB + r;
+        Pi[r * kCD + c] = (ri < m && c < nb) ? base[(size_t)ri * lda + c] : T(0);
+        Pk[r * kCD + c] = (rk < m && c < nb) ? base[(size_t)rk * lda + c] : T(0);
+    }
+    __syncthreads();
+    const int lane = threadIdx.x & 31, wy = threadIdx.x >> 5;
+    const int col = tk * kCB + lane;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        const int i = wy * 4 + q, row = ti * kCB + i;
+        if (row >= m) break;
+        T dot = T(0);
+#pragma unroll
+        for (int c = 0; c < kCB; ++c) dot = fma(Pi[i * kCD + c], Pk[lane * kCD + c], dot);
+        if (col <= row) A[(size_t)(j0 + nb + row) * lda + j0 + nb + col] -= dot;
+    }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) chol_inverse_kernel(int n, const T* __restrict__ A, long long lda, T* __restrict__ X,
+                                                           long long ldx, const int* __restrict__ info) {
+    extern __shared__ __align__(16) unsigned char chol_inv_smem[];
+    T* Di = reinterpret_cast<T*>(chol_inv_smem);     // [32][33]
+    T* ACC = Di + kCB * kCD;                         // [32][33] column sums of the tile before the diagonal solve
+    T* P = ACC + kCB * kCD + 2;                      // L row panel [32][ldp]
+    if (*info) return;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int bj = blockIdx.x, k_lo = bj * kCB, nblk = (n + kCB - 1) / kCB;
+    const int col = k_lo + lane;
+    for (int bi = bj + 1; bi < nblk; ++bi) {
+        const int i0 = bi * kCB, nbi = min(kCB, n - i0), w = i0 - k_lo, ldp = w + 2;
+        for (int e = tid; e < kCB * w; e += 256) {
+            const int r = e / w, k = e - r * w;
+            P[(size_t)r * ldp + k] = r < nbi ? A[(size_t)(i0 + r) * lda + k_lo + k] : T(0);
+        }
+        for (int e = tid; e < kCB * kCB; e += 256) {
+            const int r = e >> 5, c = e & 31;
+            Di[r * kCD + c] = (r < nbi && c <= r) ? X[(size_t)(i0 + r) * ldx + i0 + c] : T(0);
+        }
+        __syncthreads();
+        // warp w owns rows 4w..4w+3 of the tile; every element sums over k in the single-CTA kernel's order
+        T acc[4] = {T(0), T(0), T(0), T(0)};
+        for (int k8 = 0; k8 < w; k8 += 8) {          // w is a multiple of 32; 8 independent L2 loads in flight
+            T x[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) x[u] = (col < n) ? X[(size_t)(k_lo + k8 + u) * ldx + col] : T(0);
+#pragma unroll
+            for (int u = 0; u < 8; ++u)
+#pragma unroll
+                for (int q = 0; q < 4; ++q) acc[q] = fma(P[(size_t)(warp * 4 + q) * ldp + k8 + u], x[u], acc[q]);
+        }
+#pragma unroll
+        for (int q = 0; q < 4; ++q) ACC[(warp * 4 + q) * kCD + lane] = acc[q];
+        __syncthreads();
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const int r = warp * 4 + q;
+            T o = T(0);
+            for (int t = 0; t <= r; ++t) o = fma(Di[r * kCD + t], ACC[t * kCD + lane], o);
+            if (r < nbi && col < n) X[(size_t)(i0 + r) * ldx + col] = -o;
+        }
+        __syncthreads();          // the block row just written is read (from global) by the next bi of this CTA
+    }
+}
+
+template <typename T>
+__global__ void chol_zero_upper_kernel(int n, T* __restrict__ A, long long lda, T* __restrict__ X, long long ldx,
+                                       const int* __restrict__ info) {
+    if (*info) return;
+    for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < (long long)n * n;
+         e += (long long)gridDim.x * blockDim.x) {
+        const int r = (int)(e / n), c = (int)(e - (long long)r * n);
+        if (c > r && (c / kCB) > (r / kCB)) { A[(size_t)r * lda + c] = T(0); X[(size_t)r * ldx + c] = T(0); }
+    }
+}
+
+template <typename T>
+static int launch_chol_multi(int n, void* A_, int64_t lda, void* X_, int64_t ldx, int32_t* info, cudaStream_t st) {
+    T* A = (T*)A_;
+    T* X = (T*)X_;
+    NMB_CUDA(cudaMemsetAsync(info, 0, sizeof(int32_t), st));
+    for (int j0 = 0; j0 < n; j0 += kCB) {
+        const int nb = std::min(kCB, n - j0), m = n - j0 - nb;
+        chol_diag_kernel<T><<<1, 32, 0, st>>>(n, j0, A, lda, X, ldx, info);
+        if (m <= 0) break;
+        chol_panel_kernel<T><<<(m + 127) / 128, 128, 0, st>>>(n, j0, A, lda, X, ldx, info);
+        const int nt = (m + kCB - 1) / kCB;
+        chol_update_kernel<T><<<nt * (nt + 1) / 2, 256, 0, st>>>(n, j0, A, lda, info);
+    }
+    const int nblk = (n + kCB - 1) / kCB;
+    if (nblk > 1) {
+        const size_t smem = ((size_t)2 * kCB * kCD + 2 + (size_t)kCB * (n + 2)) * sizeof(T);
+        NMB_CUDA(cudaFuncSetAttribute(chol_inverse_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        chol_inverse_kernel<T><<<nblk - 1, 256, smem, st>>>(n, A, lda, X, ldx, info);
+    }
+    chol_zero_upper_kernel<T><<<64, 256, 0, st>>>(n, A, lda, X, ldx, info);
+    NMB_LAUNCH_CHECK();
+    return 0;
+}
+
 template <typename T>
 static int launch_chol(int n, int batch, void* A, int64_t lda, int64_t strideA, void* X, int64_t ldx, int64_t strideX,
                        int32_t* info, cudaStream_t st) {
+    // one large matrix with its inverse: spread over the SMs (bit-identical to the single-CTA kernel)
+    if (batch == 1 && n >= kCholMultiMinN && X && info && !getenv("NMB_CHOL_SINGLE_CTA"))
+        return launch_chol_multi<T>(n, A, lda, X, ldx, info, st);
     const int mpad = n > kCB ? (n - 1) / kCB * kCB : 0;                      // panel rows, rounded up to tiles
     const size_t panel = std::max<size_t>((size_t)mpad * kCP, (size_t)kCB * (n + 2));
     const size_t smem = ((size_t)2 * kCB * kCD + 2 + panel) * sizeof(T);

@@ -68,3 +68,27 @@ def test_gp_caches_match_oracle_and_jitter_rule():
     L, _ = _psd_safe_cholesky(S.cuda())
     Lr = gp_math.psd_safe_cholesky(S)
     assert float((L.cpu() @ L.cpu().T - Lr @ Lr.T).abs().max()) < 1e-6
+
+
+@pytest.mark.parametrize("n", [128, 161, 333, 500, 800])
+def test_multi_cta_path_is_bit_identical_to_the_single_cta_kernel(n, monkeypatch):
+    """One large matrix runs as diag / panel / update launches over many CTAs (chol.cu): every element goes through the
+    same FMA sequence as the single-CTA kernel, so L and L^-1 agree bit for bit; a non-PD minor is reported alike."""
+    import time
+    from nonmyopia_b200.gp import cholesky_root
+    A = _spd(1, n, 100 + n).cuda()
+    monkeypatch.setenv("NMB_CHOL_SINGLE_CTA", "1")
+    L1, X1, i1 = cholesky_root(A)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter(); cholesky_root(A); torch.cuda.synchronize(); t_single = time.perf_counter() - t0
+    monkeypatch.delenv("NMB_CHOL_SINGLE_CTA")
+    Lm, Xm, im = cholesky_root(A)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter(); cholesky_root(A); torch.cuda.synchronize(); t_multi = time.perf_counter() - t0
+    print(f"n={n}: single CTA {1e3 * t_single:.2f} ms, multi CTA {1e3 * t_multi:.2f} ms")
+    assert int(i1) == int(im) == 0
+    assert torch.equal(L1, Lm) and torch.equal(X1, Xm)
+    B = A.clone()
+    B[0, n - 7, n - 7] = -3.0
+    _, _, ib = cholesky_root(B)
+    assert int(ib) == n - 6
