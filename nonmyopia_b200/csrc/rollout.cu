@@ -8,6 +8,7 @@
 // The backward kernel walks the same chain in reverse (BPTT through the GRU and through
 // f's input gradient) and leaves every layer's pre-activation adjoint in the save
 // workspace for the split-K weight-gradient kernel (wgrad.cu).
+#include <stdlib.h>
 #include "cost.cuh"
 #include "path.cuh"
 #include "policy_dev.cuh"
@@ -768,6 +769,10 @@ static int launch_bwd_mma(const nmb_ts_problem_t* p, const nmb_ts_rollout_t* r, 
     return 0;
 }
 
+}  // namespace nmb
+#include "rollout_tf32.cuh"
+namespace nmb {
+
 // the in-kernel draws of (step, call, chain) exactly as the rollout kernels make them (same device functions)
 __global__ void ts_device_draws_kernel(ProblemDev<double> pb, RolloutDev<double> ro, long long step, int n_calls,
                                        double* cs, int* dims, double* noise) {
@@ -861,6 +866,13 @@ extern "C" int nmb_ts_rollout_fwd(const nmb_ts_problem_t* prob, const nmb_ts_rol
                         : launch_fwd_mma<16>(prob, rollouts, n_rollouts, st);
     }
     if (prob->dtype == NMB_F64) return NMB_DISPATCH_D(launch_fwd, double, prob->d, prob, rollouts, n_rollouts, st);
+    if (tf32_fwd_ok(prob, rollouts, n_rollouts)) {
+        const int d = prob->d;
+        return d <= 2 ? launch_fwd_tf32<2>(prob, rollouts, n_rollouts, st)
+               : d <= 4 ? launch_fwd_tf32<4>(prob, rollouts, n_rollouts, st)
+               : d <= 8 ? launch_fwd_tf32<8>(prob, rollouts, n_rollouts, st)
+                        : launch_fwd_tf32<16>(prob, rollouts, n_rollouts, st);
+    }
     return NMB_DISPATCH_D(launch_fwd, float, prob->d, prob, rollouts, n_rollouts, st);
 }
 
