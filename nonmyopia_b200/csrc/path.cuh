@@ -10,6 +10,21 @@
 
 namespace nmb {
 
+// sin(pi x), cos(pi x) in FP32: x = q/2 + r with |r| <= 1/4 exactly (magic-number rounding), then the MUFU sine /
+// cosine on pi r in [-pi/4, pi/4] (absolute error ~2^-21) and the quadrant swap - the FP32 / TF32 variant's path
+// features (tolerance 1e-3); libm's sincospif costs ~3x the instructions.  Overloads keep the template code generic.
+__device__ __forceinline__ void nmb_sincospi_fast(float x, float* sn, float* cs) {
+    const float kd = fmaf(x, 2.0f, 12582912.0f);                 // 1.5 * 2^23
+    const int q = __float_as_int(kd);
+    const float r = fmaf(kd - 12582912.0f, -0.5f, x);
+    const float a = 3.14159265358979f * r;
+    const float s = __sinf(a), c = __cosf(a);
+    const float u = (q & 1) ? c : s, v = (q & 1) ? s : c;
+    *sn = (q & 2) ? -u : u;
+    *cs = ((q + 1) & 2) ? -v : v;
+}
+__device__ __forceinline__ void nmb_sincospi_fast(double x, double* sn, double* cs) { nmb_sincospi(x, sn, cs); }
+
 template <typename T> struct PathDev {
     int d, n_freq, n_train, n_paths, kernel_id;
     T feat_scale, amplitude, mean_const;
@@ -56,7 +71,8 @@ __device__ __forceinline__ void path_partial(const PathDev<T>& P, const T (&x)[D
             u = fma(wk[k], x[k], u);
         }
         T sn, cs;
-        if constexpr (TAB) nmb_sincospi_tab(u, tab, &sn, &cs);
+        if constexpr (TAB && sizeof(T) == 8) nmb_sincospi_tab(u, tab, &sn, &cs);
+        else if constexpr (TAB) nmb_sincospi_fast(u, &sn, &cs);          // float: exact reduction + MUFU
         else Num<T>::sincospi(u, &sn, &cs);
         const T ws = __ldg(wsin + m), wc = __ldg(wcos + m);
         acc = fma(sn, ws, fma(cs, wc, acc));
@@ -90,7 +106,7 @@ __device__ __forceinline__ void path_partial(const PathDev<T>& P, const T (&x)[D
             r2 = fma(sd[k], sd[k], r2);
         }
         T kap, gc;
-        if constexpr (TAB) kernel_profile_tab(P.kernel_id, r2, tab, kap, gc);
+        if constexpr (TAB && sizeof(T) == 8) kernel_profile_tab(P.kernel_id, r2, tab, kap, gc);
         else kernel_profile<T>(P.kernel_id, r2, kap, gc);
         const T vj = __ldg(vv + j);
         kacc = fma(kap, vj, kacc);

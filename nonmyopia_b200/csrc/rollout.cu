@@ -893,5 +893,12 @@ extern "C" int nmb_ts_rollout_bwd(const nmb_ts_problem_t* prob, const nmb_ts_rol
     }
     if (prob->dtype == NMB_F64)
         return NMB_DISPATCH_D(launch_bwd, double, prob->d, prob, rollout, g_loss, g_cost, g_X, g_A, g_prev, st);
+    if (tf32_bwd_ok(prob, rollout)) {
+        const int d = prob->d;
+        return d <= 2 ? launch_bwd_tf32<2>(prob, rollout, g_loss, g_cost, g_X, g_A, g_prev, st)
+               : d <= 4 ? launch_bwd_tf32<4>(prob, rollout, g_loss, g_cost, g_X, g_A, g_prev, st)
+               : d <= 8 ? launch_bwd_tf32<8>(prob, rollout, g_loss, g_cost, g_X, g_A, g_prev, st)
+                        : launch_bwd_tf32<16>(prob, rollout, g_loss, g_cost, g_X, g_A, g_prev, st);
+    }
     return NMB_DISPATCH_D(launch_bwd, float, prob->d, prob, rollout, g_loss, g_cost, g_X, g_A, g_prev, st);
 }
