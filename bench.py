@@ -400,6 +400,7 @@ def run_b200(args, rank, world, local_rank):
         # ---- e2e: the public class API with HOST buffers, copies inside the timed region
         e2e = run_e2e_loop(args, loop, prev_x, prev_y, prev_h, stream, barrier)
         e2e_api = run_e2e(args, gp, path, net, prev_x, prev_y, prev_h, budget, dev, stream, barrier)
+        aq = run_actor_query(args, gp, path, net, prob, n_r, S, Lk, dev, group) if world == 1 else None
     t = torch.tensor([ms_total, e2e["ms_total"], e2e_api["ms_total"], sustained["ms_total"] if sustained else 0.0],
                      dtype=torch.float64, device=dev)
     if world > 1:
@@ -453,6 +454,13 @@ def run_b200(args, rank, world, local_rank):
                        "prev_X/prev_y/prev_hid_state from pinned memory (each step's copy is issued on a side stream "
                        "during the previous step's kernels, two input-buffer sets), one iteration (same launches as "
                        "`value`), D2H of the per-restart loss/cost, stream synchronise",
+                "actor_query": None if aq is None else {
+                    "value": nodes_per_step * aq["iterations"] / aq["seconds"], "unit": UNIT,
+                    "seconds": aq["seconds"], "iterations": aq["iterations"], "ms_per_iteration": 1e3 * aq["seconds"] / aq["iterations"],
+                    "h2d_bytes_per_step": aq["h2d"],
+                    "api": "Actor.query (reference actor.py:439-734) in the default seed-stream mode on the same workload: "
+                           "wall time of the whole call (graph capture, host-RNG ring uploads from pinned memory every 16 "
+                           "iterations, state polls, final selection) / iterations"},
                 "class_api_eager": {
                     "value": nodes_per_step * world * e2e_api["steps"] / (api_ms * 1e-3), "unit": UNIT,
                     "ms_per_step": api_ms / e2e_api["steps"],
@@ -598,6 +606,49 @@ def time_kernels(loop, stream, n_steps):
     flops = {"ts_rollout_fwd": nodes * (2 * f_net + 1.5 * f_ts), "ts_rollout_bwd": nodes * f_net,
              "policy_wgrad": nodes * f_net, "objective+snapshot": 0.0, "adamw": 0.0}
     return {k: {"ms": sum(v) / len(v), "flops": flops.get(k, 0.0)} for k, v in acc.items()}
+
+
+def run_actor_query(args, gp, path, net, prob, n_r, S, Lk, dev, group):
+    """The call a user of the reference makes - ``Actor.query`` (actor.py:439-734) - on the bench workload, in the
+    default seed-stream mode: the CUDA-graph loop fed by the host-RNG ring (every chunk of iterations: H2D of the
+    reference-order draws from pinned memory, D2H poll of the loop state), final selection.  Wall time around the call
+    (second call; 120 iterations, early stop closed by ``past_initial = False`` and < 200 iterations)."""
+    import contextlib
+    import io
+    import tempfile
+    import types
+    from nonmyopia_b200 import acqfs, actor as A
+    F64 = torch.float64
+    N, n_it = n_r * S, 120
+    world = 1 if group is None else torch.distributed.get_world_size(group)
+    n = prob.train_X.shape[0]
+    parms = types.SimpleNamespace(
+        algo="HES", algo_ts=True, amortized=True, algo_lookahead_steps=Lk, x_dim=D, y_dim=1, hidden_dim=H, n_actions=1,
+        n_restarts=N * world, n_samples=64, env_discretized=False, num_categories=None,
+        bounds=torch.tensor([[0.0, 1.0]] * D, dtype=F64), torch_dtype=F64, device=dev, acq_opt_lr=1e-3, acq_opt_iter=n_it,
+        n_initial_points=n, save_dir=tempfile.mkdtemp(), budget=2 * math.sqrt(D), plot=False,
+        loss_function_class=acqfs.qLossFunctionTopK, loss_func_hypers=dict(dist_weight=1, dist_threshold=0.5),
+        cost_function_class=acqfs.qCostFunction, cost_func_hypers=cost_hypers(), rng_mode="host", process_group=group,
+        exchange=args.exchange)
+    with contextlib.redirect_stdout(io.StringIO()):
+        act = A.Actor(parms)
+        act.maps.load_state_dict(net.state_dict())
+        buffer = dict(x=prob.train_X.to(dev), y=prob.train_Y.to(dev), h=torch.zeros(n, H, dtype=F64, device=dev),
+                      cost=torch.zeros(n, dtype=F64, device=dev))
+        act.construct_acqf(gp, buffer)
+        g = torch.Generator().manual_seed(1000)
+        act.hidden_noise = torch.randn(N * world, H, generator=g).to(F64).to(dev)
+        secs = []
+        for _ in range(2):
+            torch.manual_seed(5)
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            out = act.query(buffer, iteration=n, f_posterior=path, save_trajectory=False)
+            torch.cuda.synchronize()
+            secs.append(time.perf_counter() - t0)
+    assert bool(torch.isfinite(out["next_X"]).all())
+    ring = N * (Lk + 1) * (2 * 16 + 2 * 8)          # bytes of draws per iteration and rank (cs, dims, noise x 2 rollouts)
+    return dict(seconds=secs[-1], iterations=n_it, h2d=ring, d2h=72 // 16)
 
 
 def run_e2e_loop(args, loop, prev_x, prev_y, prev_h, stream, barrier):

@@ -2,6 +2,8 @@
 import ctypes as C
 import json
 import os
+import sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 from nonmyopia_b200 import _lib
 
