@@ -301,6 +301,21 @@ int nmb_gp_mll_value_grad(int kernel_id, int d, int n, const double* X, const do
                           double* out, void* stream);
 
 /* ------------------------------------------------------------------------
+ * Allocation-free variant of nmb_gp_mll_value_grad.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Same inputs, same `out`, same kernels; the workspace is a file-scope
+ * `static __device__` array inside the library (523 KB, held by every GPU that loads the library until exit) whose
+ * device address is looked up once per device with cudaGetSymbolAddress.  Calls no cudaMalloc / cudaFree / allocating
+ * library routine.  Limit: n <= 256 (NMB_ELIMIT beyond, with a message naming the limit); d <= NMB_MAX_DIM.
+ * Every call on a device shares the one array, which keeps the last call's contents: each call overwrites everything it
+ * reads, so nothing needs clearing, but two calls that overlap on the GPU (different streams, or threads without
+ * ordering) RACE - serialise them, or use nmb_gp_mll_value_grad with separate caller workspaces.
+ * ---------------------------------------------------------------------- */
+int nmb_gp_mll_value_grad_static(int kernel_id, int d, int n, const double* X, const double* inv_ls, const double* y,
+                                 double mean_const, const double* L, int64_t ldl, const double* Linv, int64_t ldi,
+                                 double* out, void* stream);
+
+/* ------------------------------------------------------------------------
  * Restart shards over NVLink peer memory (one process per GPU; SURVEY 8e C2 + C3): the per-iteration exchange of
  * the sharded Actor.query loop - policy-gradient SUM and the MIN of the two snapshot-decision candidates
  * (actor.py:622-639, 641-648) - written against peer-mapped buffers, fused with the AdamW update, instead of two

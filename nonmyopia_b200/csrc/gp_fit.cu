@@ -7,6 +7,7 @@
 //   G = alpha alpha^T - Kinv and the traces  tr(G), tr(G kappa), tr(G dK/dl_k)                   (mll_grad_kernel)
 // so that  d(-log p)/d theta = -1/2 tr(G dKhat/d theta),  d(-log p)/dc = -sum(alpha).
 // The host (nonmyopia_b200/gp_fit.py) adds the priors and the softplus chain rule and drives L-BFGS-B.
+#include <mutex>
 #include "common.cuh"
 
 namespace nmb {
@@ -189,4 +190,56 @@ extern "C" int nmb_gp_mll_value_grad(int kernel_id, int d, int n, const double* 
     mll_grad_reduce_kernel<<<1, 32, 0, st>>>((int)(t * t), stride, d, part, out);
     NMB_LAUNCH_CHECK();
     return 0;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Allocation-free variant (no counterpart in the reference): the same
+// launches as nmb_gp_mll_value_grad with the workspace in a file-scope device array instead of caller memory, for
+// callers that may not call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).
+// n <= kStaticMaxN keeps the array at 523 KB per GPU that loads the library (held until exit).
+// ---------------------------------------------------------------------------------------------------------------
+namespace nmb {
+namespace {
+constexpr int kStaticMaxN = 256;
+constexpr int kStaticTiles = (kStaticMaxN + 31) / 32;
+constexpr size_t kStaticElems = (size_t)kStaticMaxN * kStaticMaxN + kStaticMaxN + (size_t)kStaticTiles * kStaticTiles * (NMB_MAX_DIM + 2);
+static __device__ __align__(256) double g_mll_static_work[kStaticElems];
+
+// In host code `g_mll_static_work` is only a handle for the runtime, not a device address: the address is looked up
+// once per device (with that device current) and cached.
+constexpr int kMaxDevices = 64;
+double* g_mll_static_ptr[kMaxDevices] = {};
+std::mutex g_mll_static_mu;
+
+int mll_static_workspace(double** out) {
+    int dev = -1;
+    NMB_CUDA(cudaGetDevice(&dev));
+    NMB_REQUIRE(dev >= 0 && dev < kMaxDevices, NMB_ELIMIT, "nmb_gp_mll_value_grad_static: device ordinal %d outside [0,%d)", dev,
+                kMaxDevices);
+    std::lock_guard<std::mutex> lk(g_mll_static_mu);
+    if (!g_mll_static_ptr[dev]) {
+        void* p = nullptr;
+        NMB_CUDA(cudaGetSymbolAddress(&p, g_mll_static_work));
+        NMB_REQUIRE(p != nullptr, NMB_ENODEV, "nmb_gp_mll_value_grad_static: cudaGetSymbolAddress returned a null address");
+        g_mll_static_ptr[dev] = static_cast<double*>(p);
+    }
+    *out = g_mll_static_ptr[dev];
+    return 0;
+}
+}  // namespace
+}  // namespace nmb
+
+extern "C" int nmb_gp_mll_value_grad_static(int kernel_id, int d, int n, const double* X, const double* inv_ls,
+                                            const double* y, double mean_const, const double* L, int64_t ldl,
+                                            const double* Linv, int64_t ldi, double* out, void* stream) {
+    NMB_REQUIRE(n >= 1 && n <= kStaticMaxN, NMB_ELIMIT,
+                "nmb_gp_mll_value_grad_static: n=%d outside [1,%d] (the built-in workspace is sized for %d points; use "
+                "nmb_gp_mll_value_grad with caller memory beyond that)", n, kStaticMaxN, kStaticMaxN);
+    NMB_REQUIRE(d >= 1 && d <= NMB_MAX_DIM, NMB_ELIMIT, "nmb_gp_mll_value_grad_static: d=%d outside [1,%d]", d, NMB_MAX_DIM);
+    double* work = nullptr;
+    if (int rc = mll_static_workspace(&work)) return rc;
+    // Every element the kernels read from the workspace (Kinv [n, n], alpha [n], per-tile partials) is written earlier
+    // in the same call, so nothing has to be cleared between calls; stale contents of a previous (larger) call lie
+    // outside what this call reads.
+    return nmb_gp_mll_value_grad(kernel_id, d, n, X, inv_ls, y, mean_const, L, ldl, Linv, ldi, work, out, stream);
 }
