@@ -12,7 +12,8 @@ import threading
 
 import torch
 
-LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "lib", "libnonmyopia_b200.so")
+LIB_PATH = os.environ.get("NMB_LIB_PATH") or os.path.join(os.path.dirname(os.path.abspath(__file__)), "lib",
+                                                          "libnonmyopia_b200.so")   # NMB_LIB_PATH: A/B builds (tools/)
 
 NMB_F64, NMB_F32 = 0, 1
 KERNEL_IDS = {"rbf": 0, "matern12": 1, "matern32": 2, "matern52": 3}

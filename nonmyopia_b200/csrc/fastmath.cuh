@@ -166,7 +166,13 @@ NMB_HD double exp_reduce_tab(double x, const double* __restrict__ tab, double& s
     q = fma(q, r, 0.5);
     const double p = fma(q, z, r);
     // s = 2^(ki/64) = tab[ki & 63] * 2^(ki >> 6): the exponent is added to the table entry's bits
+#ifdef __CUDA_ARCH__
+    // the exponent goes into the HIGH word only (the 64-bit form costs an add-with-carry pair and two wide shifts)
+    const double t = tab[ki & 63];
+    s = __hiloint2double(__double2hiint(t) + ((ki >> 6) << 20), __double2loint(t));
+#else
     s = bits_f64(f64_bits(tab[ki & 63]) + ((int64_t)(ki >> 6) << 52));
+#endif
     return p;
 }
 
@@ -235,23 +241,25 @@ NMB_HD double nmb_rcp2(double a) {      // 1 / a, a in [2^-500, 2^500]: rcp.appr
 #endif
 }
 
-// |x| <= lim for a limit whose low word is zero (40, 20, 60 ...), decided on the high word alone: five integer
-// instructions instead of the fourteen of fmin(fmax()) with its NaN handling (a NaN comes out as +-lim)
+// |x| <= lim (+ at most 2^-20 relative: the low word is kept) for a limit whose low word is zero (40, 20, ...),
+// decided on the high word alone: three integer instructions (and, unsigned min, or) instead of the fourteen of
+// fmin(fmax()) with its NaN handling (a NaN comes out as +-lim).  The callers only need "no overflow past lim".
 NMB_HD double nmb_clamp_abs(double x, double lim) {
 #ifdef __CUDA_ARCH__
-    const int hi = __double2hiint(x), lhi = __double2hiint(lim);
-    const bool over = (hi & 0x7fffffff) >= lhi;
-    return __hiloint2double(over ? ((hi & 0x80000000) | lhi) : hi, over ? 0 : __double2loint(x));
+    const int hi = __double2hiint(x);
+    const unsigned a = min((unsigned)(hi & 0x7fffffff), (unsigned)__double2hiint(lim));
+    return __hiloint2double((int)((unsigned)(hi & 0x80000000) | a), __double2loint(x));
 #else
     return fmin(fmax(x, -lim), lim);
 #endif
 }
-// min(x, 0) clamped at -60 (the ELU's exponential argument)
+// The ELU's exponential argument: negative x with the magnitude clamped at 60 (-60.00..: low word kept).  Negative
+// doubles order like their high words read as unsigned, so ONE unsigned min does it; x >= 0 passes through
+// unchanged - the ELU selects x itself there and discards the exponential (whatever it evaluates to).
 NMB_HD double nmb_neg_part_clamped(double x) {
 #ifdef __CUDA_ARCH__
-    const int hi = __double2hiint(x);
-    const bool pos = hi >= 0, big = (hi & 0x7fffffff) >= 0x404E0000;
-    return __hiloint2double(pos ? 0 : (big ? (int)0xC04E0000 : hi), (pos || big) ? 0 : __double2loint(x));
+    const unsigned hi = (unsigned)__double2hiint(x);
+    return __hiloint2double((int)min(hi, 0xC04E0000u), __double2loint(x));
 #else
     return fmax(fmin(x, 0.0), -60.0);
 #endif

@@ -38,12 +38,38 @@ __global__ void transpose_kernel(SegTab tb, const T* __restrict__ theta, T* __re
 
 // torch.optim.AdamW (single-tensor path): p *= 1 - lr*wd; m.lerp_(g, 1-b1); v = b2 v + (1-b2) g^2;
 // denom = sqrt(v)/sqrt(1-b2^t) + eps; p -= (lr/(1-b1^t)) * m/denom
+// bias corrections of step t, computed by one thread per CTA (two FP64 pow calls) and broadcast through shared memory
+__device__ __forceinline__ void adamw_bias_corrections(const nmb_adamw_t& hp, long long t, double* s_bc) {
+    if (threadIdx.x == 0) {
+        s_bc[0] = 1.0 - ::pow(hp.beta1, (double)t);
+        s_bc[1] = ::sqrt(1.0 - ::pow(hp.beta2, (double)t));
+    }
+    __syncthreads();
+}
+
+// Second CTA counter of the scratch area behind the loop state (the first belongs to objective_kernel): the last CTA
+// of an optimiser launch advances the loop state, after every CTA has read step / done (each CTA takes its ticket
+// after its last read of the state), so no separate one-thread kernel is needed.
+__device__ __forceinline__ unsigned int* advance_ticket(nmb_loop_state_t* state) {
+    return reinterpret_cast<unsigned int*>(reinterpret_cast<char*>(state) + 128) + 1;
+}
+__device__ __forceinline__ bool last_cta_of_launch(unsigned int* ticket) {
+    __shared__ int s_last;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        const unsigned prev = atomicAdd(ticket, 1u);
+        s_last = prev + 1 == gridDim.x;
+        if (s_last) *ticket = 0;                         // ready for the next launch
+    }
+    __syncthreads();
+    return s_last != 0;
+}
+
 template <typename T>
-__device__ __forceinline__ void adamw_apply(const nmb_adamw_t& hp, T g, long long t, long long i, int ti,
+__device__ __forceinline__ void adamw_apply(const nmb_adamw_t& hp, T g, double bc1, double bc2s, long long i, int ti,
                                             T* __restrict__ theta, T* __restrict__ theta_t, T* __restrict__ m,
                                             T* __restrict__ v) {
-    const double bc1 = 1.0 - ::pow(hp.beta1, (double)t);
-    const double bc2s = ::sqrt(1.0 - ::pow(hp.beta2, (double)t));
     T p = theta[i] * (T)(1.0 - hp.lr * hp.weight_decay);
     T mi = m[i], vi = v[i];
     mi = mi + (g - mi) * (T)(1.0 - hp.beta1);
@@ -59,8 +85,11 @@ __global__ void adamw_kernel(SegTab tb, int use_tab, nmb_adamw_t hp, T* __restri
                              T* __restrict__ m, T* __restrict__ v, const T* __restrict__ partials, long long n,
                              nmb_loop_state_t* state, int advance) {
     const bool stopped = state && state->done;
+    if (stopped) return;                                  // uniform over the grid: done only changes in the last CTA's tail
+    __shared__ double s_bc[2];
+    adamw_bias_corrections(hp, (state ? state->step : 0) + 1, s_bc);
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (!stopped && i < n) {
+    if (i < n) {
         int seg = 0, ti = (int)i, nsp = 1;
         if (use_tab) { ti = transposed_index(tb, (int)i, seg); nsp = tb.splits[seg]; }
         if (nsp > 0) {
@@ -73,18 +102,15 @@ __global__ void adamw_kernel(SegTab tb, int use_tab, nmb_adamw_t hp, T* __restri
 #pragma unroll
                 for (int u = 0; u < 32; ++u) g += pv[u];
             }
-            adamw_apply<T>(hp, g, (state ? state->step : 0) + 1, i, ti, theta, theta_t, m, v);
+            adamw_apply<T>(hp, g, s_bc[0], s_bc[1], i, ti, theta, theta_t, m, v);
         }
     }
-    (void)advance;
-}
-
-// latch done / advance the step counter once all optimiser blocks have finished (separate tiny
-// kernel: no inter-block ordering assumptions inside adamw_kernel)
-__global__ void advance_state_kernel(nmb_loop_state_t* state) {
-    if (state->done) return;
-    state->step += 1;
-    state->done = state->done_next;
+    if (advance && state && last_cta_of_launch(advance_ticket(state))) {
+        if (threadIdx.x == 0) {
+            state->step += 1;
+            state->done = state->done_next;
+        }
+    }
 }
 
 // actor.py:622-639: compare this iteration's best total (with |budget - cost|) with the min of
@@ -109,7 +135,7 @@ __device__ __forceinline__ void loop_decide(nmb_loop_state_t* state, int past_in
 // (deterministic) and takes the snapshot / early-stop decision.
 constexpr int kObjMaxCtas = 96;
 struct ObjPartial { double best, lck, sl, sc; long long idx; };
-struct ObjScratch { unsigned int count; unsigned int pad; ObjPartial part[kObjMaxCtas]; };
+struct ObjScratch { unsigned int count; unsigned int count_adv; ObjPartial part[kObjMaxCtas]; };   // count_adv: advance_ticket()
 static_assert(128 + sizeof(ObjScratch) <= NMB_LOOP_STATE_BYTES, "scratch must fit behind the loop state");
 
 template <typename T>
@@ -122,7 +148,8 @@ __global__ void __launch_bounds__(256) objective_kernel(int d, int L, long long 
                                                          T* __restrict__ g_cost, T* __restrict__ g_X,
                                                          T* __restrict__ g_A, T* __restrict__ hist_loss,
                                                          T* __restrict__ hist_cost, T* __restrict__ hist_X,
-                                                         long long hist_cap, int defer_decision, nmb_loop_state_t* state) {
+                                                         long long hist_cap, int defer_decision, int lpc,
+                                                         nmb_loop_state_t* state) {
     if (state->done) return;
     __shared__ double s_val[32];
     __shared__ double s_lck[32];
@@ -135,32 +162,45 @@ __global__ void __launch_bounds__(256) objective_kernel(int d, int L, long long 
     long long best_i = 0x7fffffffffffffffLL;
     double sl = 0.0, sc = 0.0, lck_min = 1.0 / 0.0;
     ObjScratch* scr = reinterpret_cast<ObjScratch*>(reinterpret_cast<char*>(state) + 128);
-    for (long long c = (long long)blockIdx.x * blockDim.x + tid; c < N; c += (long long)gridDim.x * blockDim.x) {
+    // `lpc` lanes per chain (a power of two <= 32): the L + 1 policy outputs of a chain are handled by neighbouring
+    // lanes (the per-level sqrt / divide chains run side by side instead of one after the other), the chain's own
+    // terms by sub-lane 0
+    const int sub = tid & (lpc - 1);
+    const long long cpb = blockDim.x / lpc;
+    const bool hist_on = state->step < hist_cap;
+    const long long hstep = state->step;
+    for (long long base = (long long)blockIdx.x * cpb; base < N; base += (long long)gridDim.x * cpb) {
+        const long long c = base + tid / lpc;
+        const bool valid = c < N;
         T kl = T(0);
-        for (int l = 0; l <= L; ++l) {
-            const T* xm = l < L ? X + ((size_t)l * N + c) * d : A + (size_t)c * d;
-            const T* xo = nullptr;
-            if (Xo) xo = l < L ? Xo + ((size_t)l * N + c) * d : Ao + (size_t)c * d;
-            T* gdst = l < L ? (g_X ? g_X + ((size_t)l * N + c) * d : nullptr) : (g_A ? g_A + (size_t)c * d : nullptr);
-            if (!xo) {
-                if (gdst) for (int k = 0; k < d; ++k) gdst[k] = T(0);
-                continue;
-            }
-            // F.cosine_similarity(dim=-1, eps=1e-6): x.y / (max(|x|, eps) * max(|y|, eps))
-            T dot = T(0), nm = T(0), no = T(0);
-            for (int k = 0; k < d; ++k) { dot = fma(xm[k], xo[k], dot); nm = fma(xm[k], xm[k], nm); no = fma(xo[k], xo[k], no); }
-            const T rm = Num<T>::sqrt(nm), rqo = Num<T>::sqrt(no);
-            const T cm = rm > eps ? rm : eps, co = rqo > eps ? rqo : eps;
-            const T cs = dot / (cm * co);
-            kl += T(1) - cs;
-            if (gdst) {
-                // d(1 - cos)/d xm = -( xo/(cm co) - cos * xm / cm^2 )   (norm clamp inactive: |xm| > eps)
-                for (int k = 0; k < d; ++k) {
-                    const T dcs = xo[k] / (cm * co) - (rm > eps ? cs * xm[k] / (cm * cm) : T(0));
-                    gdst[k] = -inv_n * dcs;
+        if (valid) {
+            for (int l = sub; l <= L; l += lpc) {
+                const T* xm = l < L ? X + ((size_t)l * N + c) * d : A + (size_t)c * d;
+                const T* xo = nullptr;
+                if (Xo) xo = l < L ? Xo + ((size_t)l * N + c) * d : Ao + (size_t)c * d;
+                T* gdst = l < L ? (g_X ? g_X + ((size_t)l * N + c) * d : nullptr) : (g_A ? g_A + (size_t)c * d : nullptr);
+                if (hist_X && hist_on && l < L)
+                    for (int k = 0; k < d; ++k) hist_X[(((size_t)hstep * L + l) * N + c) * d + k] = xm[k];
+                if (!xo) {
+                    if (gdst) for (int k = 0; k < d; ++k) gdst[k] = T(0);
+                    continue;
+                }
+                // F.cosine_similarity(dim=-1, eps=1e-6): x.y / (max(|x|, eps) * max(|y|, eps))
+                T dot = T(0), nm = T(0), no = T(0);
+                for (int k = 0; k < d; ++k) { dot = fma(xm[k], xo[k], dot); nm = fma(xm[k], xm[k], nm); no = fma(xo[k], xo[k], no); }
+                const T rm = Num<T>::sqrt(nm), rqo = Num<T>::sqrt(no);
+                const T cm = rm > eps ? rm : eps, co = rqo > eps ? rqo : eps;
+                const T cs = dot / (cm * co);
+                kl += T(1) - cs;
+                if (gdst) {
+                    // d(1 - cos)/d xm = -( xo/(cm co) - cos * xm / cm^2 )   (norm clamp inactive: |xm| > eps)
+                    const T icc = T(1) / (cm * co), w = rm > eps ? cs / (cm * cm) : T(0);
+                    for (int k = 0; k < d; ++k) gdst[k] = -inv_n * (xo[k] * icc - w * xm[k]);
                 }
             }
         }
+        for (int m = lpc >> 1; m > 0; m >>= 1) kl += __shfl_xor_sync(0xffffffffu, kl, m);   // fixed order: deterministic
+        if (!valid || sub != 0) continue;
         const T lc = loss[c], cc = cost[c];
         const T gap = budget - cc;
         const T tot = lc + Num<T>::fabs(gap) + kl;
@@ -168,17 +208,12 @@ __global__ void __launch_bounds__(256) objective_kernel(int d, int L, long long 
         total[c] = tot;
         g_loss[c] = inv_n;
         g_cost[c] = gap > T(0) ? -inv_n : (gap < T(0) ? inv_n : T(0));
-        if (hist_loss && state->step < hist_cap) {
-            hist_loss[(size_t)state->step * N + c] = lc;
-            hist_cost[(size_t)state->step * N + c] = cc;
-        }
-        if (hist_X && state->step < hist_cap) {
-            for (int l = 0; l < L; ++l)
-                for (int k = 0; k < d; ++k)
-                    hist_X[(((size_t)state->step * L + l) * N + c) * d + k] = X[((size_t)l * N + c) * d + k];
+        if (hist_loss && hist_on) {
+            hist_loss[(size_t)hstep * N + c] = lc;
+            hist_cost[(size_t)hstep * N + c] = cc;
         }
         sl += (double)lc; sc += (double)cc;
-        if ((double)tot < best) { best = (double)tot; best_i = c; }   // strided ascending: first minimum kept
+        if ((double)tot < best) { best = (double)tot; best_i = c; }   // ascending chains per lane: first minimum kept
         const double lck = (double)((lc + cc) + kl);                  // best_loss + best_cost + best_KL of a snapshot
         lck_min = lck < lck_min ? lck : lck_min;
     }
@@ -358,30 +393,33 @@ __global__ void __launch_bounds__(32) peer_wait_decide_kernel(PeerTab pt, nmb_lo
 template <typename T>
 __global__ void __launch_bounds__(256) peer_adamw_kernel(PeerTab pt, SegTab tb, nmb_adamw_t hp, T* __restrict__ theta,
                                                          T* __restrict__ theta_t, T* __restrict__ m, T* __restrict__ v,
-                                                         const nmb_loop_state_t* state) {
+                                                         nmb_loop_state_t* state) {
     if (state->done) return;
-    const unsigned long long e = reinterpret_cast<const PeerHdr*>(pt.base[pt.rank])->epoch;
+    PeerHdr* hdr = reinterpret_cast<PeerHdr*>(pt.base[pt.rank]);
+    const unsigned long long e = hdr->epoch;
+    __shared__ double s_bc[2];
+    adamw_bias_corrections(hp, state->step + 1, s_bc);
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= pt.n) return;
-    const long long off = NMB_PEER_HEADER_BYTES + (long long)(e & 1) * pt.slot_bytes;
-    T pv[NMB_MAX_PEERS];
+    if (i < pt.n) {
+        const long long off = NMB_PEER_HEADER_BYTES + (long long)(e & 1) * pt.slot_bytes;
+        T pv[NMB_MAX_PEERS];
 #pragma unroll
-    for (int r = 0; r < NMB_MAX_PEERS; ++r)
-        pv[r] = r < pt.world ? __ldcv(reinterpret_cast<const T*>(pt.base[r] + off) + i) : T(0);
-    T g = T(0);
+        for (int r = 0; r < NMB_MAX_PEERS; ++r)
+            pv[r] = r < pt.world ? __ldcv(reinterpret_cast<const T*>(pt.base[r] + off) + i) : T(0);
+        T g = T(0);
 #pragma unroll
-    for (int r = 0; r < NMB_MAX_PEERS; ++r) g += pv[r];
-    int seg;
-    const int ti = transposed_index(tb, (int)i, seg);
-    adamw_apply<T>(hp, g, state->step + 1, i, ti, theta, theta_t, m, v);
-}
-
-// end of a sharded iteration: the exchange epoch and the loop state advance together
-__global__ void peer_advance_kernel(PeerTab pt, nmb_loop_state_t* state) {
-    if (state->done) return;
-    reinterpret_cast<PeerHdr*>(pt.base[pt.rank])->epoch += 1;
-    state->step += 1;
-    state->done = state->done_next;
+        for (int r = 0; r < NMB_MAX_PEERS; ++r) g += pv[r];
+        int seg;
+        const int ti = transposed_index(tb, (int)i, seg);
+        adamw_apply<T>(hp, g, s_bc[0], s_bc[1], i, ti, theta, theta_t, m, v);
+    }
+    // end of a sharded iteration: the exchange epoch and the loop state advance together, in the last CTA to finish
+    // (every CTA has read epoch / step / done before it takes its ticket)
+    if (last_cta_of_launch(advance_ticket(state)) && threadIdx.x == 0) {
+        hdr->epoch = e + 1;
+        state->step += 1;
+        state->done = state->done_next;
+    }
 }
 
 struct CopyList { const void* src[8]; void* dst[8]; long long n[8]; int count; };
@@ -424,17 +462,19 @@ extern "C" int nmb_ts_objective(int dtype, int d, int L, int64_t n_chains, int64
     NMB_REQUIRE((X_orig == nullptr) == (A_orig == nullptr), NMB_EINVAL, "nmb_ts_objective: X_orig/A_orig mismatch");
     NMB_REQUIRE(L == 0 || X, NMB_EINVAL, "nmb_ts_objective: X is null");
     cudaStream_t st = (cudaStream_t)stream;
-    const int obj_ctas = (int)std::min<long long>(kObjMaxCtas, (n_chains + 255) / 256);
+    int lpc = 1;
+    while (lpc < 32 && lpc < L + 1) lpc <<= 1;
+    const int obj_ctas = (int)std::min<long long>(kObjMaxCtas, (n_chains * lpc + 255) / 256);
     if (dtype == NMB_F64) {
         objective_kernel<double><<<obj_ctas, 256, 0, st>>>(d, L, n_chains, n_global, budget, past_initial, patience, (const double*)loss,
             (const double*)cost, (const double*)X, (const double*)A, (const double*)X_orig, (const double*)A_orig,
             (double*)KL, (double*)total, (double*)g_loss, (double*)g_cost, (double*)g_X, (double*)g_A,
-            (double*)hist_loss, (double*)hist_cost, (double*)hist_X, hist_capacity, defer_decision, state);
+            (double*)hist_loss, (double*)hist_cost, (double*)hist_X, hist_capacity, defer_decision, lpc, state);
     } else if (dtype == NMB_F32) {
         objective_kernel<float><<<obj_ctas, 256, 0, st>>>(d, L, n_chains, n_global, (float)budget, past_initial, patience, (const float*)loss,
             (const float*)cost, (const float*)X, (const float*)A, (const float*)X_orig, (const float*)A_orig,
             (float*)KL, (float*)total, (float*)g_loss, (float*)g_cost, (float*)g_X, (float*)g_A,
-            (float*)hist_loss, (float*)hist_cost, (float*)hist_X, hist_capacity, defer_decision, state);
+            (float*)hist_loss, (float*)hist_cost, (float*)hist_X, hist_capacity, defer_decision, lpc, state);
     } else { set_error("nmb_ts_objective: dtype %d", dtype); return NMB_EINVAL; }
     NMB_LAUNCH_CHECK();
     return 0;
@@ -467,12 +507,8 @@ template <typename T>
 static int launch_adamw(SegTab tb, int use_tab, const nmb_adamw_t* hp, void* theta, void* theta_t, void* m, void* v,
                         const void* partials, long long n, nmb_loop_state_t* state, int advance, cudaStream_t st) {
     adamw_kernel<T><<<(unsigned)((n + 255) / 256), 256, 0, st>>>(tb, use_tab, *hp, (T*)theta, (T*)theta_t, (T*)m, (T*)v,
-                                                                 (const T*)partials, n, state, 0);
+                                                                 (const T*)partials, n, state, advance);
     NMB_LAUNCH_CHECK();
-    if (advance && state) {
-        advance_state_kernel<<<1, 1, 0, st>>>(state);
-        NMB_LAUNCH_CHECK();
-    }
     return 0;
 }
 
@@ -588,8 +624,6 @@ extern "C" int nmb_peer_adamw_step(const nmb_peer_exchange_t* px, int dtype, int
         peer_adamw_kernel<float><<<grid, 256, 0, st>>>(pt, tb, *hp, (float*)theta, (float*)theta_t, (float*)exp_avg,
                                                         (float*)exp_avg_sq, state);
     } else { set_error("nmb_peer_adamw_step: dtype %d", dtype); return NMB_EINVAL; }
-    NMB_LAUNCH_CHECK();
-    peer_advance_kernel<<<1, 1, 0, st>>>(pt, state);
     NMB_LAUNCH_CHECK();
     return 0;
 }
