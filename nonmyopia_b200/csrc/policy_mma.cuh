@@ -17,7 +17,10 @@
 
 namespace nmb {
 
-constexpr int kStages = 4;        // weight ring depth
+#ifndef NMB_FWD_STAGES
+#define NMB_FWD_STAGES 4
+#endif
+constexpr int kStages = NMB_FWD_STAGES;        // weight ring depth (forward rollout)
 // Stage row stride (doubles).  A 64-bit shared load is served as two half-warp wavefronts (lanes 0-15, 16-31); the
 // B fragment of lane l sits at (l & 3) * kSW + (l >> 2), so a half-warp touches k = 0..3 x n = 0..3 and needs
 // kSW = 4 (mod 16) for 16 distinct 8-byte banks.  (72 = 8 mod 16 looked conflict-free for an arbitrary lane split but
@@ -240,7 +243,7 @@ __device__ __forceinline__ void gemm_src_bwd(const PolicyLayout& lay, bool head_
 
 // Producer warp: stream every weight chunk of all L+1 steps in consumption order (forward: steps 0..L from
 // theta_t; backward: steps L..0 from theta).
-template <int NST, bool BWD>
+template <int NST, bool BWD, int KC = kKC>
 __device__ __forceinline__ void mma_producer(const PolicyLayout& lay, const double* __restrict__ weights, int L,
                                              const MmaRing& rg, int it_begin = 0, int it_end = -1) {
     const int lane = threadIdx.x & 31;
@@ -254,15 +257,15 @@ __device__ __forceinline__ void mma_producer(const PolicyLayout& lay, const doub
             int off, ldw;
             if (BWD) gemm_src_bwd(lay, l == L, g, off, ldw);
             else gemm_src(lay, l == L, g, off, ldw);
-            for (int k0 = 0; k0 < H; k0 += kKC, ++c) {
+            for (int k0 = 0; k0 < H; k0 += KC, ++c) {
                 const unsigned slot = c % NST, fill = c / NST;
                 if (fill > 0) mbar_wait(rg.empty0 + 8 * slot, (fill - 1) & 1);
-                const int kn = min(kKC, H - k0);
+                const int kn = min(KC, H - k0);
                 const unsigned full = rg.full0 + 8 * slot;
                 if (lane == 0) mbar_arrive_expect_tx(full, row_bytes * (unsigned)kn);
                 __syncwarp();
                 if (lane < kn)
-                    bulk_g2s(smem_u32(rg.stage + (size_t)slot * kStageElems + lane * kSW),
+                    bulk_g2s(smem_u32(rg.stage + (size_t)slot * (KC * kSW) + lane * kSW),
                              weights + off + (size_t)(k0 + lane) * ldw, row_bytes, full);
             }
         }
@@ -294,16 +297,16 @@ struct MmaWarp {
 
 // acc[t] (t = 0..3: 8-column tiles of the warp's 32 columns) += A[row0.., 0..H) . W chunk stream
 // A: shared, row-major with stride KS, pointing at the first contraction column.
-template <int NST, int NT = 4>
+template <int NST, int NT = 4, int KC = kKC>
 __device__ __forceinline__ void mma_gemm(const MmaRing& sm, MmaWarp& w, const double* __restrict__ A, int H,
                                          double (&acc)[NT][2]) {
     const double* arow = A + (size_t)(w.row0 + w.fr) * sm.KS + w.fk;
-    for (int k0 = 0; k0 < H; k0 += kKC) {
+    for (int k0 = 0; k0 < H; k0 += KC) {
         const unsigned slot = w.chunk % NST, fill = w.chunk / NST;
         mbar_wait(sm.full0 + 8 * slot, fill & 1);
         if (w.active) {
-            const double* st = sm.stage + (size_t)slot * kStageElems + w.fk * kSW + w.col0 + w.fr;
-            const int kn = min(kKC, H - k0);
+            const double* st = sm.stage + (size_t)slot * (KC * kSW) + w.fk * kSW + w.col0 + w.fr;
+            const int kn = min(KC, H - k0);
 #pragma unroll 4
             for (int kk = 0; kk < kn; kk += 4) {
                 const double a = arow[k0 + kk];
@@ -527,11 +530,11 @@ struct MmaBwdSmem {
     double *X0, *X1, *X2, *X3, *X4, *X5, *GH, *GO, *GXY, *carry, *stage;
     unsigned full0, empty0;
     int rows, KS;
-    __device__ void carve(double* base, int d, int dmax, int H, int rows_) {
+    __device__ void carve(double* base, int d, int dmax, int H, int rows_, int nst = kStagesBwd, int kc = kKC) {
         rows = rows_;
         KS = H + 4;
         double* p = base;
-        stage = p; p += kStagesBwd * kStageElems;
+        stage = p; p += nst * kc * kSW;
         X0 = p; p += rows * KS;
         X1 = p; p += rows * KS;
         X2 = p; p += rows * KS;
@@ -543,11 +546,11 @@ struct MmaBwdSmem {
         GXY = p; p += (d + 1) * rows;
         carry = p; p += (dmax + 1) * rows;
         full0 = smem_u32(p);
-        empty0 = full0 + 8 * kStagesBwd;
+        empty0 = full0 + 8 * nst;
     }
-    static size_t bytes(int d, int dmax, int H, int rows) {
-        return ((size_t)kStagesBwd * kStageElems + (size_t)7 * rows * (H + 4) + (size_t)(2 * d + dmax + 2) * rows +
-                2 * kStagesBwd) * 8;
+    static size_t bytes(int d, int dmax, int H, int rows, int nst = kStagesBwd, int kc = kKC) {
+        return ((size_t)nst * kc * kSW + (size_t)7 * rows * (H + 4) + (size_t)(2 * d + dmax + 2) * rows +
+                2 * nst) * 8;
     }
     __device__ MmaRing ring() const { return MmaRing{stage, full0, empty0, KS}; }
 };
@@ -569,6 +572,7 @@ __device__ __forceinline__ void prefetch_tile(double2 (&dst)[NT], const double* 
 //   out: sm.GXY [(d+1)][rows] adjoint of [x; y];  sm.GH adjoint of the previous hidden state
 // Leaves the pre-activation adjoints (DO, DU2, DU1, DR, DZ, DN, DNH, DP, DE) of the node in the save
 // workspace for the weight-gradient kernel.  theta: torch layout [O][K].
+template <int NST = kStagesBwd, int KC = kKC>
 __device__ __forceinline__ void mma_policy_backward(const PolicyLayout& lay, const double* __restrict__ theta, bool head_a,
                                                     const MmaBwdSmem& sm, MmaWarp& w, const SaveAreas<double>& sv,
                                                     long long node0, int nvalid) {
@@ -625,7 +629,7 @@ __device__ __forceinline__ void mma_policy_backward(const PolicyLayout& lay, con
     double2 pf[kNTB];
     prefetch_tile(pf, sv.U1, nrow, w, H, rv);
     zero_acc4(acc);
-    mma_gemm<kStagesBwd, kNTB>(ring, w, sm.X0, H, acc);
+    mma_gemm<NST, kNTB, KC>(ring, w, sm.X0, H, acc);
 #pragma unroll
     for (int t = 0; t < kNTB; ++t) {
         const int k = w.col0 + 8 * t + 2 * w.fk;
@@ -648,14 +652,14 @@ __device__ __forceinline__ void mma_policy_backward(const PolicyLayout& lay, con
     prefetch_tile(phn, sv.HN, nrow, w, H, rv);
     prefetch_tile(php, sv.HS, nrow, w, H, rv);      // HS[level] = h before the step
     zero_acc4(acc);
-    mma_gemm<kStagesBwd, kNTB>(ring, w, sm.X1, H, acc);
+    mma_gemm<NST, kNTB, KC>(ring, w, sm.X1, H, acc);
 #pragma unroll
     for (int t = 0; t < kNTB; ++t) {
         const int k = w.col0 + 8 * t + 2 * w.fk;
         if (k < H) *reinterpret_cast<double2*>(sm.X2 + row * KS + k) = make_double2(acc[t][0], acc[t][1]);
     }
     zero_acc4(acc);
-    mma_gemm<kStagesBwd, kNTB>(ring, w, sm.X1, H, acc);
+    mma_gemm<NST, kNTB, KC>(ring, w, sm.X1, H, acc);
     // X0 (du2_pre), X3..X5 are dead for every warp here (barriers above / end of the previous step)
 #pragma unroll
     for (int t = 0; t < kNTB; ++t) {
@@ -695,9 +699,9 @@ __device__ __forceinline__ void mma_policy_backward(const PolicyLayout& lay, con
     double2 pea[kNTB];
     prefetch_tile(pea, sv.EA, nrow, w, H, rv);
     zero_acc4(acc);
-    mma_gemm<kStagesBwd, kNTB>(ring, w, sm.X0, H, acc);
-    mma_gemm<kStagesBwd, kNTB>(ring, w, sm.X3, H, acc);
-    mma_gemm<kStagesBwd, kNTB>(ring, w, sm.X4, H, acc);
+    mma_gemm<NST, kNTB, KC>(ring, w, sm.X0, H, acc);
+    mma_gemm<NST, kNTB, KC>(ring, w, sm.X3, H, acc);
+    mma_gemm<NST, kNTB, KC>(ring, w, sm.X4, H, acc);
 #pragma unroll
     for (int t = 0; t < kNTB; ++t) {
         const int k = w.col0 + 8 * t + 2 * w.fk;
@@ -714,9 +718,9 @@ __device__ __forceinline__ void mma_policy_backward(const PolicyLayout& lay, con
     }
     // ---- dh_prev += dr . Whh_r + dz . Whh_z + dnh . Whh_n
     zero_acc4(acc);
-    mma_gemm<kStagesBwd, kNTB>(ring, w, sm.X0, H, acc);
-    mma_gemm<kStagesBwd, kNTB>(ring, w, sm.X3, H, acc);
-    mma_gemm<kStagesBwd, kNTB>(ring, w, sm.X5, H, acc);
+    mma_gemm<NST, kNTB, KC>(ring, w, sm.X0, H, acc);
+    mma_gemm<NST, kNTB, KC>(ring, w, sm.X3, H, acc);
+    mma_gemm<NST, kNTB, KC>(ring, w, sm.X5, H, acc);
 #pragma unroll
     for (int t = 0; t < kNTB; ++t) {
         const int k = w.col0 + 8 * t + 2 * w.fk;
@@ -729,7 +733,7 @@ __device__ __forceinline__ void mma_policy_backward(const PolicyLayout& lay, con
     consumer_sync(nthr);
     // ---- de_pre = (dp_pre . Wp) * elu'(ea) -> X1
     zero_acc4(acc);
-    mma_gemm<kStagesBwd, kNTB>(ring, w, sm.X2, H, acc);
+    mma_gemm<NST, kNTB, KC>(ring, w, sm.X2, H, acc);
 #pragma unroll
     for (int t = 0; t < kNTB; ++t) {
         const int k = w.col0 + 8 * t + 2 * w.fk;

@@ -527,8 +527,8 @@ __global__ void __launch_bounds__(kNT, 1) ts_rollout_bwd_kernel(ProblemDev<T> pb
 }
 
 // ================================================================== backward, FP64 tensor pipe + TMA weight stream
-template <int DMAX>
-__global__ void __launch_bounds__(kMaxRowsMmaBwd * (32 / kNTB) + 32, 1)
+template <int DMAX, int NST = kStagesBwd, int KC = kKC, int MAXROWS = kMaxRowsMmaBwd, int MINB = 1>
+__global__ void __launch_bounds__(MAXROWS * (32 / kNTB) + 32, MINB)
     ts_rollout_bwd_mma_kernel(ProblemDev<double> pb, RolloutDev<double> ro, const double* __restrict__ g_loss,
                               const double* __restrict__ g_cost, const double* __restrict__ g_X,
                               const double* __restrict__ g_A, double* __restrict__ g_prev, int rows) {
@@ -543,9 +543,9 @@ __global__ void __launch_bounds__(kMaxRowsMmaBwd * (32 / kNTB) + 32, 1)
     const long long step = pb.step_ptr ? *pb.step_ptr : 0;
 
     MmaBwdSmem sm;
-    sm.carve(reinterpret_cast<T*>(nmb_smem_raw), d, DMAX, H, rows);
+    sm.carve(reinterpret_cast<T*>(nmb_smem_raw), d, DMAX, H, rows, NST, KC);
     if (tid == 0) {
-        for (int s = 0; s < kStagesBwd; ++s) {
+        for (int s = 0; s < NST; ++s) {
             mbar_init(sm.full0 + 8 * s, 1);
             mbar_init(sm.empty0 + 8 * s, ncw);
         }
@@ -553,7 +553,7 @@ __global__ void __launch_bounds__(kMaxRowsMmaBwd * (32 / kNTB) + 32, 1)
     }
     __syncthreads();
     if (tid >= nthr) {
-        mma_producer<kStagesBwd, true>(pb.lay, ro.theta, L, sm.ring());
+        mma_producer<NST, true, KC>(pb.lay, ro.theta, L, sm.ring());
         return;
     }
     MmaWarp w;
@@ -627,7 +627,7 @@ __global__ void __launch_bounds__(kMaxRowsMmaBwd * (32 / kNTB) + 32, 1)
             }
         }
         consumer_sync(nthr);
-        mma_policy_backward(pb.lay, ro.theta, head_a, sm, w, sv, node0, nvalid);
+        mma_policy_backward<NST, KC>(pb.lay, ro.theta, head_a, sm, w, sv, node0, nvalid);
         if (tid < rows) {
             const int r = tid;
 #pragma unroll
