@@ -345,6 +345,16 @@ int nmb_peer_wait_decide(const nmb_peer_exchange_t* px, int dtype, nmb_loop_stat
 int nmb_peer_adamw_step(const nmb_peer_exchange_t* px, int dtype, int d, int H, int n_actions, const nmb_adamw_t* hp,
                         void* theta, void* theta_t, void* exp_avg, void* exp_avg_sq, nmb_loop_state_t* state,
                         void* stream);
+/* The three calls above as ONE launch (what the sharded Actor.query loop uses): CTA b reduces its 256-element slice of
+ * the nmb_policy_wgrad partials into the rank's slot, raises a per-slice flag in every peer, waits for the same slice
+ * of every peer, sums it in rank order and applies AdamW; the last CTA to finish takes the MIN of the candidates, the
+ * decision of nmb_loop_decide, and advances the exchange epoch and the loop state.  Call nmb_snapshot_if_improved
+ * AFTER it (the snapshot copies rollout outputs, never the weights).  Needs (n + 255) / 256 <= 8 x SM count
+ * (NMB_ELIMIT otherwise: fall back to the three calls).  Same buffer, same epoch counter as the three-call form. */
+int nmb_peer_exchange_adamw_step(const nmb_peer_exchange_t* px, int dtype, const void* partials, int d, int H,
+                                 int n_actions, const int32_t* seg_splits_host, const nmb_adamw_t* hp, void* theta,
+                                 void* theta_t, void* exp_avg, void* exp_avg_sq, nmb_loop_state_t* state,
+                                 int past_initial, int patience, void* stream);
 
 /* ------------------------------------------------------------------------
  * Exact-GP posterior over a fantasy tree (HES-MC and the qEI/qPI/qSR/qUCB/qKG baselines):

@@ -290,7 +290,13 @@ struct PeerHdr {
 };
 static_assert(sizeof(PeerHdr) <= NMB_PEER_HEADER_BYTES, "peer header");
 
-struct PeerTab { unsigned char* base[NMB_MAX_PEERS]; int rank, world; long long n; long long slot_bytes, cand_off; };
+struct PeerTab {
+    unsigned char* base[NMB_MAX_PEERS];
+    int rank, world;
+    long long n;
+    long long slot_bytes, cand_off;
+    long long ll_off;         // LL lines of the fused exchange: [2 parities][NMB_MAX_PEERS][n + 2] x 16 bytes behind the two slots
+};
 
 template <typename T> static PeerTab make_peertab(const nmb_peer_exchange_t* px) {
     PeerTab t;
@@ -298,6 +304,7 @@ template <typename T> static PeerTab make_peertab(const nmb_peer_exchange_t* px)
     t.rank = px->rank; t.world = px->world; t.n = px->n;
     t.cand_off = (px->n * (long long)sizeof(T) + 15) / 16 * 16;
     t.slot_bytes = t.cand_off + 16;
+    t.ll_off = NMB_PEER_HEADER_BYTES + 2 * t.slot_bytes;
     return t;
 }
 
@@ -419,6 +426,189 @@ __global__ void __launch_bounds__(256) peer_adamw_kernel(PeerTab pt, SegTab tb, 
         hdr->epoch = e + 1;
         state->step += 1;
         state->done = state->done_next;
+    }
+}
+
+
+// ---- the whole exchange in ONE kernel (the three-launch form above stays for callers that need the phases apart).
+// Measured on 2 GPUs (tools/peer_clocks.py, -DNMB_PEER_CLOCKS): a flag-per-slice version of this kernel spent 7 us of
+// every CTA's 16 us in `fence.sys` + the release store (213 CTAs fencing at once; whole kernel 31 us against 8.6 us
+// for the single-GPU AdamW kernel).  This version needs no fence and no flag: values travel as self-validating
+// 16-byte lines {lo, seq, hi, seq} (8-byte lines {bits, seq} in FP32) - the LL scheme of NCCL: an 8-byte store is
+// atomic on NVLink, so a line whose sequence words both equal epoch + 1 is complete.
+//   1. thread i reduces element i of the split-K partials and PUSHES it into recv[epoch & 1][rank][i] of every peer
+//      (one NVLink trip instead of flag trip + read round trip); CTA 0 pushes the rank's two decision candidates;
+//   2. it polls its own recv lines of the other ranks (local memory, L1 bypassed) until they carry epoch + 1, sums in
+//      rank order with its own value from the register, applies AdamW: bitwise identical weights on every rank;
+//   3. the last CTA to finish takes the MIN of the candidates, the snapshot / early-stop decision (loop_decide) and
+//      advances the exchange epoch and the loop state.
+// Two parity buffers: a rank can start exchange e + 2 (which overwrites parity e & 1) only after it has received every
+// peer's lines of e + 1, which a peer sends after it finished reading e.  The snapshot copy (rollout outputs only,
+// never the weights) runs AFTER this kernel and reads state->improved.
+__device__ __forceinline__ void ll_store(void* p, double v, unsigned seq) {
+    const unsigned lo = (unsigned)__double2loint(v), hi = (unsigned)__double2hiint(v);
+    asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(lo), "r"(seq), "r"(hi), "r"(seq) : "memory");
+}
+__device__ __forceinline__ void ll_store(void* p, float v, unsigned seq) {
+    asm volatile("st.volatile.global.v2.u32 [%0], {%1, %2};" ::"l"(p), "r"(__float_as_uint(v)), "r"(seq) : "memory");
+}
+__device__ __forceinline__ bool ll_try_load(const void* p, unsigned seq, double& v) {
+    unsigned lo, f0, hi, f1;
+    asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(lo), "=r"(f0), "=r"(hi), "=r"(f1) : "l"(p) : "memory");
+    v = __hiloint2double((int)hi, (int)lo);
+    return f0 == seq && f1 == seq;
+}
+__device__ __forceinline__ bool ll_try_load(const void* p, unsigned seq, float& v) {
+    unsigned b, f;
+    asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(b), "=r"(f) : "l"(p) : "memory");
+    v = __uint_as_float(b);
+    return f == seq;
+}
+// line (of_rank, i) of parity `par` in rank `in_rank`'s buffer; lines are 16 bytes apart in both precisions;
+// i = n, n + 1: the two decision candidates (always doubles)
+__device__ __forceinline__ unsigned char* ll_line(const PeerTab& pt, int in_rank, int par, int of_rank, long long i) {
+    return pt.base[in_rank] + pt.ll_off + (((size_t)par * NMB_MAX_PEERS + of_rank) * (size_t)(pt.n + 2) + (size_t)i) * 16;
+}
+
+#ifdef NMB_PEER_CLOCKS
+static __device__ unsigned long long g_peer_clk[12];
+static __device__ unsigned long long g_peer_span[2] = {~0ULL, 0ULL};
+__device__ __forceinline__ unsigned long long gtime() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
+#define NMB_PCLK(expr) do { if (threadIdx.x == 0) { expr; } } while (0)
+extern "C" int nmb_debug_peer_clocks(unsigned long long* out12) {
+    return cudaMemcpyFromSymbol(out12, g_peer_clk, sizeof(g_peer_clk)) == cudaSuccess ? 0 : -1;
+}
+#else
+#define NMB_PCLK(expr) do { } while (0)
+#endif
+
+template <typename T>
+__global__ void __launch_bounds__(256) peer_exchange_adamw_kernel(PeerTab pt, SegTab tb, const T* __restrict__ partials,
+                                                                  nmb_adamw_t hp, T* __restrict__ theta,
+                                                                  T* __restrict__ theta_t, T* __restrict__ m,
+                                                                  T* __restrict__ v, nmb_loop_state_t* state,
+                                                                  int past_initial, int patience, long long timeout_cycles) {
+    if (state->done) return;
+    PeerHdr* hdr = reinterpret_cast<PeerHdr*>(pt.base[pt.rank]);
+    const unsigned long long e = hdr->epoch;
+    const unsigned seq = (unsigned)(e + 1);
+    const int par = (int)(e & 1);
+    const int tid = threadIdx.x;
+    const long long i = (long long)blockIdx.x * blockDim.x + tid;
+    __shared__ double s_bc[2];
+#ifdef NMB_PEER_CLOCKS
+    unsigned long long tk0 = 0, tk1 = 0, tk2 = 0, tk3 = 0;
+#endif
+    NMB_PCLK(tk0 = gtime());
+    // ---- 1. reduce + push
+    T g = T(0);
+    int ti = 0, nsp = 0;
+    if (i < pt.n) {
+        int seg;
+        ti = transposed_index(tb, (int)i, seg);
+        nsp = tb.splits[seg];
+        for (int q0 = 0; q0 < nsp; q0 += 32) {
+            T pv[32];
+#pragma unroll
+            for (int u = 0; u < 32; ++u) pv[u] = q0 + u < nsp ? partials[(size_t)(q0 + u) * pt.n + i] : T(0);
+#pragma unroll
+            for (int u = 0; u < 32; ++u) g += pv[u];
+        }
+        for (int r = 0; r < pt.world; ++r)
+            if (r != pt.rank) ll_store(ll_line(pt, r, par, pt.rank, i), g, seq);
+    }
+    if (blockIdx.x == 0 && tid < 2) {
+        const double c = tid == 0 ? state->cand_total : state->cand_lck;
+        for (int r = 0; r < pt.world; ++r) ll_store(ll_line(pt, r, par, pt.rank, pt.n + tid), c, seq);
+    }
+    NMB_PCLK(tk1 = gtime());
+    adamw_bias_corrections(hp, state->step + 1, s_bc);
+    // ---- 2. receive, sum in rank order, update
+    bool timed_out = false;
+    if (i < pt.n && nsp > 0) {
+        T pv[NMB_MAX_PEERS];
+        unsigned pending = 0;
+#pragma unroll
+        for (int r = 0; r < NMB_MAX_PEERS; ++r) {
+            pv[r] = T(0);
+            if (r < pt.world) {
+                if (r == pt.rank) pv[r] = g;
+                else if (!ll_try_load(ll_line(pt, pt.rank, par, r, i), seq, pv[r])) pending |= 1u << r;
+            }
+        }
+        if (pending) {
+            const long long t0 = clock64();
+            while (pending) {
+#pragma unroll
+                for (int r = 0; r < NMB_MAX_PEERS; ++r)
+                    if ((pending >> r) & 1u)
+                        if (ll_try_load(ll_line(pt, pt.rank, par, r, i), seq, pv[r])) pending &= ~(1u << r);
+                if (pending && clock64() - t0 > timeout_cycles) { timed_out = true; break; }
+            }
+        }
+        NMB_PCLK(tk2 = gtime());
+        if (!timed_out) {
+            T gs = T(0);
+#pragma unroll
+            for (int r = 0; r < NMB_MAX_PEERS; ++r) gs += pv[r];          // rank order; absent ranks hold exact zeros
+            adamw_apply<T>(hp, gs, s_bc[0], s_bc[1], i, ti, theta, theta_t, m, v);
+        }
+    }
+    if (__syncthreads_or(timed_out)) {
+        // a dead peer: stop the loop and do NOT take a ticket (no CTA becomes the last one, the state is not advanced)
+        if (tid == 0) { state->stall = NMB_PEER_TIMEOUT_STALL; state->done_next = 1; state->done = 1; }
+        return;
+    }
+#ifdef NMB_PEER_CLOCKS
+    if (tid == 0) {
+        tk3 = gtime();
+        atomicMin(&g_peer_span[0], tk0);
+        atomicMax(&g_peer_span[1], tk3);
+        if (blockIdx.x == 100) {
+            atomicAdd(&g_peer_clk[0], tk1 - tk0); atomicAdd(&g_peer_clk[1], tk2 - tk1); atomicAdd(&g_peer_clk[2], tk3 - tk2);
+            atomicAdd(&g_peer_clk[3], 1ULL);
+        }
+    }
+#endif
+    // ---- 3. decision + advance, once per launch
+    if (!last_cta_of_launch(advance_ticket(state))) return;
+    if (tid < 32) {
+        double c0 = INFINITY, c1 = INFINITY;
+        bool to = false;
+        if (tid < pt.world) {
+            const long long t0 = clock64();
+            bool ok0 = false, ok1 = false;
+            while (!(ok0 && ok1)) {
+                if (!ok0) ok0 = ll_try_load(ll_line(pt, pt.rank, par, tid, pt.n), seq, c0);
+                if (!ok1) ok1 = ll_try_load(ll_line(pt, pt.rank, par, tid, pt.n + 1), seq, c1);
+                if (!(ok0 && ok1) && clock64() - t0 > timeout_cycles) { to = true; break; }
+            }
+        }
+        to = __any_sync(0xffffffffu, to);
+        double ct = to ? INFINITY : c0, cl = to ? INFINITY : c1;
+        for (int q = 16; q > 0; q >>= 1) {
+            ct = fmin(ct, __shfl_xor_sync(0xffffffffu, ct, q));
+            cl = fmin(cl, __shfl_xor_sync(0xffffffffu, cl, q));
+        }
+        if (tid == 0) {
+            if (to) {
+                state->stall = NMB_PEER_TIMEOUT_STALL; state->done_next = 1; state->done = 1;
+            } else {
+                state->cand_total = ct;
+                state->cand_lck = cl;
+                loop_decide(state, past_initial, patience);
+                hdr->epoch = e + 1;
+                state->step += 1;
+                state->done = state->done_next;
+            }
+#ifdef NMB_PEER_CLOCKS
+            const unsigned long long cend = gtime();
+            g_peer_clk[7] += cend - g_peer_span[0];
+            g_peer_clk[8] += g_peer_span[1] - g_peer_span[0];
+            g_peer_clk[10] += 1;
+            g_peer_span[0] = ~0ULL; g_peer_span[1] = 0;
+#endif
+        }
     }
 }
 
@@ -558,7 +748,9 @@ static int validate_peers(const nmb_peer_exchange_t* px, const char* who) {
 
 extern "C" int64_t nmb_peer_exchange_bytes(int dtype, int64_t n) {
     const int64_t esz = dtype == NMB_F32 ? 4 : 8;
-    return NMB_PEER_HEADER_BYTES + 2 * ((n * esz + 15) / 16 * 16 + 16);
+    // header + two gradient slots (each followed by the two decision candidates) + the LL receive lines of the fused
+    // exchange: [2 parities][NMB_MAX_PEERS][n + 2] x 16 bytes
+    return NMB_PEER_HEADER_BYTES + 2 * ((n * esz + 15) / 16 * 16 + 16) + (int64_t)2 * NMB_MAX_PEERS * (n + 2) * 16;
 }
 
 extern "C" int nmb_peer_publish(const nmb_peer_exchange_t* px, int dtype, const void* grad, int d, int H, int n_actions,
@@ -583,21 +775,15 @@ extern "C" int nmb_peer_publish(const nmb_peer_exchange_t* px, int dtype, const 
     return 0;
 }
 
+static long long peer_timeout_cycles();
+
 extern "C" int nmb_peer_wait_decide(const nmb_peer_exchange_t* px, int dtype, nmb_loop_state_t* state, int past_initial,
                                     int patience, void* stream) {
     int rc = validate_peers(px, "nmb_peer_wait_decide");
     if (rc) return rc;
     NMB_REQUIRE(state && (dtype == NMB_F64 || dtype == NMB_F32), NMB_EINVAL, "nmb_peer_wait_decide: bad argument");
     const PeerTab pt = dtype == NMB_F64 ? make_peertab<double>(px) : make_peertab<float>(px);
-    static long long timeout_cycles = 0;
-    if (timeout_cycles == 0) {
-        int dev = 0, khz = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, dev);
-        const char* env = getenv("NMB_PEER_TIMEOUT_MS");
-        const double ms = env && atof(env) > 0 ? atof(env) : 10000.0;
-        timeout_cycles = (long long)(ms * (khz > 0 ? (double)khz : 2.0e6));
-    }
+    const long long timeout_cycles = peer_timeout_cycles();
     peer_wait_decide_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(pt, state, past_initial, patience, timeout_cycles);
     NMB_LAUNCH_CHECK();
     return 0;
@@ -624,6 +810,50 @@ extern "C" int nmb_peer_adamw_step(const nmb_peer_exchange_t* px, int dtype, int
         peer_adamw_kernel<float><<<grid, 256, 0, st>>>(pt, tb, *hp, (float*)theta, (float*)theta_t, (float*)exp_avg,
                                                         (float*)exp_avg_sq, state);
     } else { set_error("nmb_peer_adamw_step: dtype %d", dtype); return NMB_EINVAL; }
+    NMB_LAUNCH_CHECK();
+    return 0;
+}
+
+static long long peer_timeout_cycles() {
+    static long long timeout_cycles = 0;
+    if (timeout_cycles == 0) {
+        int dev = 0, khz = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, dev);
+        const char* env = getenv("NMB_PEER_TIMEOUT_MS");
+        const double ms = env && atof(env) > 0 ? atof(env) : 10000.0;
+        timeout_cycles = (long long)(ms * (khz > 0 ? (double)khz : 2.0e6));
+    }
+    return timeout_cycles;
+}
+
+extern "C" int nmb_peer_exchange_adamw_step(const nmb_peer_exchange_t* px, int dtype, const void* partials, int d, int H,
+                                            int n_actions, const int32_t* seg_splits_host, const nmb_adamw_t* hp,
+                                            void* theta, void* theta_t, void* exp_avg, void* exp_avg_sq,
+                                            nmb_loop_state_t* state, int past_initial, int patience, void* stream) {
+    int rc = validate_peers(px, "nmb_peer_exchange_adamw_step");
+    if (rc) return rc;
+    NMB_REQUIRE(partials && seg_splits_host && hp && theta && exp_avg && exp_avg_sq && state, NMB_EINVAL,
+                "nmb_peer_exchange_adamw_step: null argument");
+    SegTab tb = make_segtab(d, H, n_actions, seg_splits_host);
+    NMB_REQUIRE(tb.off[S_COUNT] == px->n, NMB_EINVAL, "nmb_peer_exchange_adamw_step: exchange holds %lld elements, policy has %d",
+                (long long)px->n, tb.off[S_COUNT]);
+    const long long grid = (px->n + 255) / 256;
+    // every CTA spins on its peers' flags: the whole grid has to be resident (8 CTAs of 256 threads per SM)
+    NMB_REQUIRE(grid <= 8LL * sm_count(), NMB_ELIMIT,
+                "nmb_peer_exchange_adamw_step: %lld slices do not fit the GPU at once (use publish / wait_decide / adamw_step)",
+                grid);
+    cudaStream_t st = (cudaStream_t)stream;
+    const long long tmo = peer_timeout_cycles();
+    if (dtype == NMB_F64) {
+        peer_exchange_adamw_kernel<double><<<(unsigned)grid, 256, 0, st>>>(
+            make_peertab<double>(px), tb, (const double*)partials, *hp, (double*)theta, (double*)theta_t, (double*)exp_avg,
+            (double*)exp_avg_sq, state, past_initial, patience, tmo);
+    } else if (dtype == NMB_F32) {
+        peer_exchange_adamw_kernel<float><<<(unsigned)grid, 256, 0, st>>>(
+            make_peertab<float>(px), tb, (const float*)partials, *hp, (float*)theta, (float*)theta_t, (float*)exp_avg,
+            (float*)exp_avg_sq, state, past_initial, patience, tmo);
+    } else { set_error("nmb_peer_exchange_adamw_step: dtype %d", dtype); return NMB_EINVAL; }
     NMB_LAUNCH_CHECK();
     return 0;
 }

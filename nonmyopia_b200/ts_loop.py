@@ -30,6 +30,7 @@ call (``rand`` + per-sample ``randperm``, amortized_network.py:136,156) and insi
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import List, Optional
 
 import torch
@@ -225,7 +226,9 @@ class TSAMLoop:
                     self.exchange_note = why
         # rollout_fwd, objective, snapshot, rollout_bwd, wgrad, adamw (the last CTA advances the state); sharded:
         # + decide, reduce (NCCL) or + publish, wait/decide (peer memory)
-        self.n_launches_per_iter = 6 if group is None else 8
+        # the peer exchange as one kernel (NMB_PEER_UNFUSED=1: publish / wait_decide / adamw_step as three launches)
+        self.fused_exchange = self.px is not None and os.environ.get("NMB_PEER_UNFUSED") is None
+        self.n_launches_per_iter = 6 if (group is None or self.fused_exchange) else 8
 
     # ------------------------------------------------------------------ one iteration
     def _iteration(self, draws=None, mark=None) -> None:
@@ -295,6 +298,16 @@ class TSAMLoop:
         mark("ts_rollout_bwd")
         partials = eng.weight_grad_partials(self.prob, self.main)
         mark("policy_wgrad")
+        if self.fused_exchange:
+            # publish -> per-slice rendezvous -> rank-ordered sum + AdamW -> decision + advance: one launch
+            _lib.check(lib.nmb_peer_exchange_adamw_step(
+                px, eng.dt, _lib.ptr(partials), eng.d, eng.H, 1, eng.seg_splits, C.byref(self.hp), _lib.ptr(self.theta),
+                _lib.ptr(self.theta_t), _lib.ptr(self.m), _lib.ptr(self.v), state_p, int(self.past_initial),
+                self.patience, st), "nmb_peer_exchange_adamw_step")
+            _lib.check(lib.nmb_snapshot_if_improved(eng.dt, 6, self._src, self._dst, self._cnt, state_p, st),
+                       "nmb_snapshot_if_improved")
+            mark("adamw")
+            return
         _lib.check(lib.nmb_peer_publish(px, eng.dt, _lib.ptr(partials), eng.d, eng.H, 1, eng.seg_splits, state_p, st),
                    "nmb_peer_publish")
         _lib.check(lib.nmb_peer_wait_decide(px, eng.dt, state_p, int(self.past_initial), self.patience, st),
