@@ -450,7 +450,7 @@ def run_b200(args, rank, world, local_rank):
         "roofline": roof, "cpu_baseline": cpu,
         "e2e": {"value": nodes_per_step * world * e2e["steps"] / (e2e_ms * 1e-3), "unit": UNIT,
                 "h2d_bytes_per_step": e2e["h2d"], "d2h_bytes_per_step": e2e["d2h"], "ms_per_step": e2e_ms / e2e["steps"],
-                "api": "TSAMLoop.step_host - the per-iteration engine of Actor.query (HES-TS-AM): per-step H2D of "
+                "api": "TSAMLoop.step_host (the following step, whose inputs the caller has already handed over, is launched behind this step's result copies) - the per-iteration engine of Actor.query (HES-TS-AM): per-step H2D of "
                        "prev_X/prev_y/prev_hid_state from pinned memory (each step's copy is issued on a side stream "
                        "during the previous step's kernels, two input-buffer sets), one iteration (same launches as "
                        "`value`), D2H of the per-restart loss/cost, stream synchronise",
@@ -657,13 +657,14 @@ def run_e2e_loop(args, loop, prev_x, prev_y, prev_h, stream, barrier):
     N = hx.shape[0]
     out_host = torch.empty(2, N, dtype=torch.float64).pin_memory()
     nxt = (hx, hy, hh)                      # inputs of the following step: copied under this step's kernels
-    for _ in range(3):
-        loop.step_host(hx, hy, hh, out_host, next_inputs=nxt)
+    for k in range(3):
+        loop.step_host(hx, hy, hh, out_host, next_inputs=nxt if k < 2 else None)
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(stream)
-    for _ in range(args.steps):
-        loop.step_host(hx, hy, hh, out_host, next_inputs=nxt)
+    for k in range(args.steps):
+        # (the last call promises no following step: step_host launches a promised step ahead)
+        loop.step_host(hx, hy, hh, out_host, next_inputs=nxt if k + 1 < args.steps else None)
     e1.record(stream)
     barrier()
     assert torch.isfinite(out_host).all()

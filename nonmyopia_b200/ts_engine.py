@@ -114,8 +114,8 @@ class RolloutBuffers:
         self.X = torch.empty(max(L, 1), N, d, dtype=dtype, device=device)
         self.A = torch.empty(N, d, dtype=dtype, device=device)
         self.Y = torch.empty(L + 1, N, dtype=dtype, device=device)
-        self.loss = torch.empty(N, dtype=dtype, device=device)
-        self.cost = torch.empty(N, dtype=dtype, device=device)
+        self.loss_cost = torch.empty(2, N, dtype=dtype, device=device)     # one buffer: one D2H copy reads both
+        self.loss, self.cost = self.loss_cost[0], self.loss_cost[1]
         self.save = None
         self.HS = None
         if with_save:

@@ -181,6 +181,8 @@ class TSAMLoop:
         self.prob = eng.problem(*self.prev, prev_cost=prev_cost)
         self._prev_cost = prev_cost
         self._alt = None          # second input buffer set + graph (step_host with prefetch)
+        self._host_done = None    # event behind a step_host call's result copies
+        self._host_stage = None   # device staging buffers of step_host's loss / cost read-back
         self.main = te.RolloutBuffers(d, H, L, N, dt, dev, with_save=True)
         self.orig = te.RolloutBuffers(d, H, L, N, dt, dev, with_save=False)
         z = lambda *s: torch.zeros(*s, dtype=dt, device=dev)
@@ -397,7 +399,7 @@ class TSAMLoop:
             self._iteration()
         self.prob = prob1
         self._alt = dict(prev=prev2, prob=prob2, graph=g, side=torch.cuda.Stream(device=self.state.device),
-                         ready=torch.cuda.Event(), which=0, staged=False)
+                         ready=torch.cuda.Event(), which=0, staged=False, ahead=False, staged_ptrs=None)
 
     def step_host(self, host_x: Tensor, host_y: Tensor, host_h: Tensor, host_out: Tensor, next_inputs=None) -> None:
         """One Adam iteration driven from HOST buffers (the reference reads loss / cost on the host every
@@ -406,7 +408,10 @@ class TSAMLoop:
         then a stream synchronise.  The graph reads the inputs through fixed device buffers, so the copies
         land in place.  ``next_inputs = (host_x, host_y, host_h)`` of the FOLLOWING call may be passed: they are copied
         on a side stream into the other input-buffer set while this iteration runs (every step's copy still happens,
-        it just no longer sits in front of the kernels)."""
+        it just no longer sits in front of the kernels), and - with the in-kernel random stream - the following iteration
+        is launched right behind this step's result copies, so the GPU does not idle while the host returns and calls
+        again.  Passing ``next_inputs`` therefore COMMITS the caller to that next call (with those very tensors); the
+        last call of a sequence passes ``None``."""
         main = torch.cuda.current_stream()
         if self.ring is not None:
             ep = self._host_steps = getattr(self, "_host_steps", -1) + 1
@@ -415,23 +420,53 @@ class TSAMLoop:
         if next_inputs is not None and alt is None and self.graph is not None:
             self._enable_alt_inputs()
             alt = self._alt
-        if alt is not None and alt["staged"]:
-            main.wait_event(alt["ready"])               # this step's inputs were prefetched into set `which`
+        if alt is not None and alt.get("ahead"):
+            # this step's iteration is already in the stream: the previous call launched it behind its own result
+            # copies, as soon as the prefetched inputs had landed (the GPU never waits for the host between steps)
+            if alt["staged_ptrs"] != (host_x.data_ptr(), host_y.data_ptr(), host_h.data_ptr()):
+                raise _lib.NmbError("step_host: the inputs differ from the next_inputs promised by the previous call "
+                                    "(their iteration has already been launched)")
             which = alt["which"]
+            alt["ahead"] = False
         else:
-            which = alt["which"] if alt is not None else 0
-            px, py, ph = self.prev if which == 0 else alt["prev"]
-            px.copy_(host_x.view_as(px), non_blocking=True)
-            py.copy_(host_y.view_as(py), non_blocking=True)
-            ph.copy_(host_h.view_as(ph), non_blocking=True)
-        if self.graph is not None:
-            (self.graph if which == 0 else alt["graph"]).replay()
-        else:
-            self._iteration()
+            if alt is not None and alt["staged"]:
+                main.wait_event(alt["ready"])               # this step's inputs were prefetched into set `which`
+                which = alt["which"]
+            else:
+                which = alt["which"] if alt is not None else 0
+                px, py, ph = self.prev if which == 0 else alt["prev"]
+                px.copy_(host_x.view_as(px), non_blocking=True)
+                py.copy_(host_y.view_as(py), non_blocking=True)
+                ph.copy_(host_h.view_as(ph), non_blocking=True)
+            if self.graph is not None:
+                (self.graph if which == 0 else alt["graph"]).replay()
+            else:
+                self._iteration()
+        # this step's per-restart loss and cost -> host (in stream order behind the iteration)
+        # Staged through a device buffer (one small device-to-device copy on this stream) and read back on the COPY
+        # stream: a device-to-host copy in the compute stream would put two compute <-> copy-engine hand-overs (~18 us
+        # measured) between this iteration and the next one.  Two staging buffers: buffer `which` is rewritten two
+        # calls later, after this call has waited for its read-back.
+        if self._host_stage is None:
+            self._host_stage = [torch.empty_like(self.main.loss_cost) for _ in range(2)]
+            self._host_iter_done = torch.cuda.Event()
+            self._host_done = torch.cuda.Event()
+            self._host_copy_stream = torch.cuda.Stream(device=self.state.device)
+        stage = self._host_stage[which]
+        stage.copy_(self.main.loss_cost, non_blocking=True)
+        self._host_iter_done.record(main)
+        with torch.cuda.stream(self._host_copy_stream):
+            self._host_copy_stream.wait_event(self._host_iter_done)
+            if host_out.is_contiguous() and tuple(host_out.shape) == tuple(stage.shape):
+                host_out.copy_(stage, non_blocking=True)
+            else:
+                host_out[0].copy_(stage[0], non_blocking=True)
+                host_out[1].copy_(stage[1], non_blocking=True)
+            self._host_done.record(self._host_copy_stream)
         if alt is not None:
             alt["staged"] = False
             if next_inputs is not None:
-                # the other set was last read by the previous call, which ended with a synchronise
+                # the other set was last read by the previous step's iteration, whose results the previous call waited for
                 nx, ny, nh = next_inputs
                 dx, dy, dh = alt["prev"] if which == 0 else self.prev
                 with torch.cuda.stream(alt["side"]):
@@ -440,11 +475,16 @@ class TSAMLoop:
                     dh.copy_(nh.view_as(dh), non_blocking=True)
                     alt["ready"].record(alt["side"])
                 alt["which"], alt["staged"] = 1 - which, True
-        host_out[0].copy_(self.main.loss, non_blocking=True)
-        host_out[1].copy_(self.main.cost, non_blocking=True)
+                alt["staged_ptrs"] = (nx.data_ptr(), ny.data_ptr(), nh.data_ptr())
+                if self.ring is None and self.graph is not None:
+                    # launch the FOLLOWING iteration now (behind the result copies above and the input prefetch):
+                    # passing next_inputs commits the caller to that step
+                    main.wait_event(alt["ready"])
+                    (alt["graph"] if which == 0 else self.graph).replay()
+                    alt["ahead"] = True
         if self.ring is not None and (self._host_steps + 1) % self.ring.K == 0:
             self.ring.chunk_enqueued(self._host_steps)
-        main.synchronize()
+        self._host_done.synchronize()                       # results of THIS step are on the host
 
     # ------------------------------------------------------------------ results (actor.py:661-733)
     def result(self):

@@ -66,3 +66,39 @@ def test_graph_replay_equals_eager_and_early_stop_freezes_state():
     a.graph.replay(); a.graph.replay()
     torch.cuda.synchronize()
     assert torch.equal(th, a.theta) and a.read_state().step == 24
+
+
+def test_step_host_launch_ahead_equals_plain_replays():
+    """``step_host`` with ``next_inputs`` (prefetch on a side stream + the following iteration launched behind this
+    step's result copies) walks exactly the trajectory of plain graph replays, returns every step's own loss / cost,
+    and refuses inputs other than the promised ones."""
+    from nonmyopia_b200 import _lib
+    fx = H.load("query_ts_am_ackley_L1")
+    n = 12
+    ref = _make_loop(fx, max_iter=40, record_history=True)
+    ref.run(n, use_graph=True, poll_every=4)
+    hx, hy, hh = (t.to(torch.float64).contiguous().pin_memory() for t in (fx["prev_X"], fx["prev_y"].reshape(-1), fx["prev_h"]))
+    N = hx.shape[0]
+    for promise in (False, True):
+        loop = _make_loop(fx, max_iter=40)
+        loop.capture()
+        out = torch.empty(2, N, dtype=torch.float64).pin_memory()
+        losses = []
+        for k in range(n):
+            nxt = (hx, hy, hh) if (promise and k + 1 < n) else None
+            loop.step_host(hx, hy, hh, out, next_inputs=nxt)
+            losses.append(out[0].clone())
+        torch.cuda.synchronize()
+        assert loop.read_state().step == n
+        assert torch.equal(loop.theta, ref.theta), promise
+        assert torch.equal(loop.best_loss, ref.best_loss), promise
+        got = torch.stack(losses)
+        assert torch.equal(got, ref.hist_loss[:n].cpu()), promise       # each call returned ITS step's losses
+    # a promised step must be called with the promised tensors
+    loop = _make_loop(fx, max_iter=40)
+    loop.capture()
+    out = torch.empty(2, N, dtype=torch.float64).pin_memory()
+    loop.step_host(hx, hy, hh, out, next_inputs=(hx, hy, hh))
+    other = hx.clone().pin_memory()
+    with pytest.raises(_lib.NmbError):
+        loop.step_host(other, hy, hh, out)
