@@ -718,8 +718,17 @@ def run_e2e(args, gp, path, net, prev_x, prev_y, prev_h, budget, dev, stream, ba
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(stream)
+    prof = None
+    if os.environ.get("NMB_PROFILE_CLASS_API"):          # host profile of the eager class-API step (stderr)
+        import cProfile
+        prof = cProfile.Profile()
+        prof.enable()
     for _ in range(steps):
         step()
+    if prof is not None:
+        import pstats
+        prof.disable()
+        pstats.Stats(prof, stream=sys.stderr).sort_stats("cumulative").print_stats(45)
     e1.record(stream)
     barrier()
     h2d = (hx.numel() + hy.numel() + hh.numel()) * 8
