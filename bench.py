@@ -423,7 +423,7 @@ def run_b200(args, rank, world, local_rank):
         ach = flops / (kern[dom]["ms"] * 1e-3) / 1e12
         roof = {"bound": "fp64", "kernel": dom, "achieved": ach, "peak": fp64_peak, "unit": "TFLOP/s",
                 "frac": ach / fp64_peak, "traffic": ncu_dram_traffic(dom),
-                "traffic_note": "DRAM read + write bytes per launch from profiles/ncu_full_r02b_rollout_wgrad.csv (the backward "
+                "traffic_note": "DRAM read + write bytes per launch from profiles/ncu_full_r02c_rollout_wgrad.csv (the backward "
                                 "workspace, not algorithmic bytes: the kernel is FP64-pipe bound)",
                 "peak_source": "own-measured FP64 DFMA peak on this pool's B200 (profiles/pipe_peaks_r01.json); "
                                "MEASURED_PEAKS.json has no FP64 entry",
@@ -480,9 +480,9 @@ def run_b200(args, rank, world, local_rank):
 
 def ncu_dram_traffic(kernel_substr):
     """DRAM bytes per launch (read + write) of the named kernel from the committed `ncu --set full` capture
-    (profiles/ncu_full_r02b_rollout_wgrad.csv, raw page); None when the file or the kernel is missing."""
+    (profiles/ncu_full_r02c_rollout_wgrad.csv, raw page); None when the file or the kernel is missing."""
     import csv
-    path = os.path.join(ROOT, "profiles", "ncu_full_r02b_rollout_wgrad.csv")
+    path = os.path.join(ROOT, "profiles", "ncu_full_r02c_rollout_wgrad.csv")
     scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
     try:
         rows = list(csv.reader(open(path)))
