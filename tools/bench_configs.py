@@ -350,6 +350,11 @@ def run_cfg1(args, rank, world):
                 act.construct_acqf(model, buffer)
                 torch.set_rng_state(fx["rng_state_in"])
                 torch.cuda.synchronize()
+                prof = None
+                if rep == 2 and os.environ.get("NMB_PROFILE_CFG1"):       # host profile of the two calls (stderr)
+                    import cProfile
+                    prof = cProfile.Profile()
+                    prof.enable()
                 t0 = time.perf_counter()
                 if tag == "reset_parameters":
                     act.reset_parameters(buffer)
@@ -369,6 +374,11 @@ def run_cfg1(args, rank, world):
                     info = dict(chosen_idx=int(out["chosen_idx"]), chosen_idx_reference=fx["out"]["chosen_idx"],
                                 next_X=out["next_X"].tolist(), next_X_reference=fx["out"]["next_X"].tolist(),
                                 iterations=fx["n_iter"])
+            if prof is not None:
+                import pstats
+                prof.disable()
+                sys.stderr.write(f"==== host profile of {tag}\n")
+                pstats.Stats(prof, stream=sys.stderr).sort_stats("cumulative").print_stats(28)
             res[tag] = dict(seconds=dt, reference_cpu_seconds_build_container=fx.get("ref_cpu_seconds"), **info)
     out = dict(case="cfg1_bo_step_ackley_hes_ts_am_1", note="third repetition (the first two pay library load, CUDA "
                "context and pinned-memory set-up)", **res)
