@@ -78,11 +78,14 @@ template <typename T, int DMAX>
 __global__ void __launch_bounds__(256) tree_cost_bwd_kernel(const __grid_constant__ TreeShape ts, int d, CostDev<T> c,
                                                             const T* __restrict__ root, const T* __restrict__ pts,
                                                             const T* __restrict__ mult, const T* __restrict__ g_acc,
-                                                            T* __restrict__ g_pts, T* __restrict__ g_root) {
+                                                            T* __restrict__ g_pts, T* __restrict__ g_root,
+                                                            long long first_node, int skip_root) {
     const int nl = ts.n_levels;
     const long long n_nodes = ts.off[nl];
-    // nodes [0, n_nodes) = tree nodes; [n_nodes, n_nodes + n_root) = root points
-    for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < n_nodes + ts.n_root;
+    // nodes [first_node, n_nodes) = tree nodes of the lower levels; [n_nodes, n_nodes + n_root) = root points (the
+    // upper levels and - when they have many leaves below them - the root points go to tree_cost_bwd_heavy_kernel)
+    const long long t_end = n_nodes + (skip_root ? 0 : ts.n_root);
+    for (long long t = first_node + (long long)blockIdx.x * blockDim.x + threadIdx.x; t < t_end;
          t += (long long)gridDim.x * blockDim.x) {
         int s = -1;
         long long j = t - n_nodes;
@@ -123,6 +126,98 @@ __global__ void __launch_bounds__(256) tree_cost_bwd_kernel(const __grid_constan
         }
         T* dst = s < 0 ? (g_root ? g_root + j * d : nullptr) : g_pts + (ts.off[s] + j) * d;
         if (dst) {
+#pragma unroll
+            for (int k = 0; k < DMAX; ++k) if (k < d) dst[k] = g[k];
+        }
+    }
+}
+
+
+// Upper levels of the tree (and the root points): a node there has hundreds of leaves below it, and the thread-per-node
+// kernel above walks them one after the other (level-0 node of the [64, 4, 2] tree: 512 + 64 x 8 dependent-latency
+// loads: 0.2 - 0.3 ms for a trivial amount of arithmetic, and no faster with fewer restarts).  Here a WARP owns a node:
+// the leaf adjoints below it are summed lane-strided + shuffle tree (fixed order: deterministic), the moves that start
+// from it are spread over the lanes when there are >= 32 children, otherwise walked one by one with lane-parallel leaf
+// sums.  Items: nodes [0, off[h_levels]) then (root_heavy) the n_root root points.
+template <typename T, int DMAX>
+__global__ void __launch_bounds__(256) tree_cost_bwd_heavy_kernel(const __grid_constant__ TreeShape ts, int d, CostDev<T> c,
+                                                                  const T* __restrict__ root, const T* __restrict__ pts,
+                                                                  const T* __restrict__ mult, const T* __restrict__ g_acc,
+                                                                  T* __restrict__ g_pts, T* __restrict__ g_root,
+                                                                  int h_levels, int root_heavy) {
+    const int nl = ts.n_levels;
+    const int lane = threadIdx.x & 31;
+    const long long warp0 = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
+    const long long n_heavy = ts.off[h_levels];
+    const long long n_items = n_heavy + (root_heavy ? ts.n_root : 0);
+    const long long n_leaf = ts.cnt[nl - 1];
+    for (long long item = warp0; item < n_items; item += nwarps) {
+        int s = -1;
+        long long j = item - n_heavy;
+        if (item < n_heavy) {
+            s = 0;
+            while (item >= ts.off[s + 1]) ++s;
+            j = item - ts.off[s];
+        }
+        T me[DMAX], other[DMAX], dir[DMAX], g[DMAX];
+#pragma unroll
+        for (int k = 0; k < DMAX; ++k) g[k] = T(0);
+        load_pt<T, DMAX>(s < 0 ? root + j * d : pts + (ts.off[s] + j) * d, d, me);
+        // the move that ends in this node
+        if (s >= 0) {
+            T G = T(0);
+            for (long long l = j + (long long)lane * ts.cnt[s]; l < n_leaf; l += 32 * ts.cnt[s]) G += g_acc[l];
+            G = warp_sum(G);
+            if (lane == 0) {
+                const T* pp = s == 0 ? root + (j % ts.n_root) * d : pts + (ts.off[s - 1] + j % ts.cnt[s - 1]) * d;
+                load_pt<T, DMAX>(pp, d, other);
+                const T dist = move_dist<T, DMAX>(c, d, me, other, dir);
+                if (c.k * (dist - c.radius) > T(0)) {
+                    const T w = G * c.k * mult[ts.off[s] + j];
+#pragma unroll
+                    for (int k = 0; k < DMAX; ++k) g[k] = fma(w, dir[k], g[k]);
+                }
+            }
+        }
+        // the moves that start from this node
+        if (s + 1 < nl) {
+            const long long step = s < 0 ? ts.n_root : ts.cnt[s];
+            const long long nch = ts.cnt[s + 1] / step;
+            if (nch >= 32) {
+                for (long long q = lane; q < nch; q += 32) {
+                    const long long ch = j + q * step;
+                    const T G = leaf_sum<T>(ts, s + 1, ch, g_acc);
+                    load_pt<T, DMAX>(pts + (ts.off[s + 1] + ch) * d, d, other);
+                    const T dist = move_dist<T, DMAX>(c, d, other, me, dir);
+                    if (c.k * (dist - c.radius) > T(0)) {
+                        const T w = G * c.k * mult[ts.off[s + 1] + ch];
+#pragma unroll
+                        for (int k = 0; k < DMAX; ++k) g[k] = fma(-w, dir[k], g[k]);
+                    }
+                }
+            } else {
+                for (long long q = 0; q < nch; ++q) {
+                    const long long ch = j + q * step;
+                    T G = T(0);
+                    for (long long l = ch + (long long)lane * ts.cnt[s + 1]; l < n_leaf; l += 32 * ts.cnt[s + 1]) G += g_acc[l];
+                    G = warp_sum(G);
+                    if (lane == 0) {
+                        load_pt<T, DMAX>(pts + (ts.off[s + 1] + ch) * d, d, other);
+                        const T dist = move_dist<T, DMAX>(c, d, other, me, dir);
+                        if (c.k * (dist - c.radius) > T(0)) {
+                            const T w = G * c.k * mult[ts.off[s + 1] + ch];
+#pragma unroll
+                            for (int k = 0; k < DMAX; ++k) g[k] = fma(-w, dir[k], g[k]);
+                        }
+                    }
+                }
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < DMAX; ++k) g[k] = warp_sum(g[k]);
+        T* dst = s < 0 ? (g_root ? g_root + j * d : nullptr) : g_pts + (ts.off[s] + j) * d;
+        if (dst && lane == 0) {
 #pragma unroll
             for (int k = 0; k < DMAX; ++k) if (k < d) dst[k] = g[k];
         }
@@ -193,14 +288,35 @@ extern "C" int nmb_tree_cost_bwd(int dtype, int d, int n_levels, const int64_t* 
     int rc = make_shape(n_levels, counts_host, n_root, ts);
     if (rc) return rc;
     cudaStream_t st = (cudaStream_t)stream;
-    const unsigned grid = grid_for(ts.off[n_levels] + n_root);
-    if (dtype == NMB_F64)
-        NMB_TC_DISPATCH(tree_cost_bwd_kernel, double, d, grid, st, ts, d, to_dev<double>(*cost), (const double*)root,
-                        (const double*)pts, (const double*)mult, (const double*)g_acc, (double*)g_pts,
-                        (double*)g_root);
-    else if (dtype == NMB_F32)
-        NMB_TC_DISPATCH(tree_cost_bwd_kernel, float, d, grid, st, ts, d, to_dev<float>(*cost), (const float*)root,
-                        (const float*)pts, (const float*)mult, (const float*)g_acc, (float*)g_pts, (float*)g_root);
+    // upper levels (>= 64 leaves below a node) and, with as many leaves per root point, the roots: warp per node
+    const long long n_leaf = ts.cnt[n_levels - 1];
+    int h_levels = 0;
+    while (h_levels < n_levels - 1 && n_leaf / ts.cnt[h_levels] >= 64) ++h_levels;
+    const int root_heavy = n_leaf / n_root >= 64 ? 1 : 0;
+    const long long first_light = ts.off[h_levels];
+    const long long n_heavy = first_light + (root_heavy ? n_root : 0);
+    const long long n_light = ts.off[n_levels] - first_light + (root_heavy ? 0 : n_root);
+    const unsigned grid = grid_for(n_light);
+    const unsigned grid_h = grid_for(n_heavy * 32);
+    if (dtype == NMB_F64) {
+        if (n_heavy > 0)
+            NMB_TC_DISPATCH(tree_cost_bwd_heavy_kernel, double, d, grid_h, st, ts, d, to_dev<double>(*cost), (const double*)root,
+                            (const double*)pts, (const double*)mult, (const double*)g_acc, (double*)g_pts,
+                            (double*)g_root, h_levels, root_heavy);
+        if (n_light > 0)
+            NMB_TC_DISPATCH(tree_cost_bwd_kernel, double, d, grid, st, ts, d, to_dev<double>(*cost), (const double*)root,
+                            (const double*)pts, (const double*)mult, (const double*)g_acc, (double*)g_pts,
+                            (double*)g_root, first_light, root_heavy);
+    } else if (dtype == NMB_F32) {
+        if (n_heavy > 0)
+            NMB_TC_DISPATCH(tree_cost_bwd_heavy_kernel, float, d, grid_h, st, ts, d, to_dev<float>(*cost), (const float*)root,
+                            (const float*)pts, (const float*)mult, (const float*)g_acc, (float*)g_pts, (float*)g_root,
+                            h_levels, root_heavy);
+        if (n_light > 0)
+            NMB_TC_DISPATCH(tree_cost_bwd_kernel, float, d, grid, st, ts, d, to_dev<float>(*cost), (const float*)root,
+                            (const float*)pts, (const float*)mult, (const float*)g_acc, (float*)g_pts, (float*)g_root,
+                            first_light, root_heavy);
+    }
     else { set_error("nmb_tree_cost_bwd: dtype %d", dtype); return NMB_EINVAL; }
     NMB_LAUNCH_CHECK();
     return 0;
