@@ -538,7 +538,11 @@ __global__ void __launch_bounds__(256) gather_gu_kernel(GpDev<T> g, const __grid
     const int NL = tr.n_levels;
     const long long unit0 = CTA_PER_NODE ? blockIdx.x : (((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
     const long long nunits = CTA_PER_NODE ? gridDim.x : (((long long)gridDim.x * blockDim.x) >> 5);
-    for (long long item = unit0; item < n_items; item += nunits) {
+    // CTA per node: a work unit is (node, block of 128 columns) - the columns are independent, and with few restarts
+    // the upper-level nodes alone (one per restart, 832 descendant rows each at nf = [64, 4, 2]) left most SMs idle
+    const int nkb = CTA_PER_NODE ? (g.n + 127) / 128 : 1;
+    for (long long unit = unit0; unit < n_items * nkb; unit += nunits) {
+        const long long item = unit / nkb;
         int s;
         long long i;
         restart_major(tr, s_lo, s_hi, item, s, i);
@@ -547,7 +551,9 @@ __global__ void __launch_bounds__(256) gather_gu_kernel(GpDev<T> g, const __grid
         T* out = st.gU + (size_t)node * g.ldu;
         const T gq2 = T(2) * st.Gq[node];
         const long long D = DescIter<T>(tr, s, i).count();
-        for (int k0 = 0; k0 < g.n; k0 += 128) {
+        const int k_lo = CTA_PER_NODE ? (int)(unit - item * nkb) * 128 : 0;
+        const int k_hi = CTA_PER_NODE ? min(g.n, k_lo + 128) : g.n;
+        for (int k0 = k_lo; k0 < k_hi; k0 += 128) {
             T a[4] = {T(0), T(0), T(0), T(0)};
             if (CTA_PER_NODE) {
                 gather_desc<T>(g, tr, st, s, i, warp, D, 8, k0, lane, a);
@@ -846,7 +852,7 @@ extern "C" int nmb_mc_gather_gu(const nmb_gp_t* gp, const nmb_tree_t* tree, cons
 #define NMB_GG(T)                                                                                                       \
     do {                                                                                                                \
         if (n_heavy > 0) {                                                                                              \
-            const unsigned grid = (unsigned)std::min<long long>(n_heavy, 16LL * sm_count());                            \
+            const unsigned grid = (unsigned)std::min<long long>(n_heavy * ((gp->n + 127) / 128), 16LL * sm_count());    \
             gather_gu_kernel<T, true><<<grid, 256, 0, s>>>(to_dev<T>(*gp), tr, to_dev<T>(*st), 0, s_heavy, n_heavy);    \
         }                                                                                                               \
         if (n_light > 0)                                                                                                \
