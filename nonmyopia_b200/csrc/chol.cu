@@ -188,60 +188,54 @@ __global__ void __launch_bounds__(256) chol_root_kernel(int n, T* __restrict__ A
 template <typename T>
 __global__ void __launch_bounds__(32) chol_diag_kernel(int n, int j0, T* __restrict__ A, long long lda, T* __restrict__ X,
                                                        long long ldx, int* __restrict__ info) {
-    // register-resident: lane = row of the block during the factorisation (column k travels by shuffle), lane =
-    // column of the inverse during the forward substitution (row r of L travels by shuffle); the arithmetic per
-    // element is the single-CTA kernel's (terms added for t < c are exact zeros)
+    // One warp, the block and its inverse in shared memory: literally step 1 of the single-CTA kernel above (same
+    // loops, same expressions: bit-identical).  A register-resident variant of this kernel (rows in registers, columns
+    // travelling by shuffle, fully unrolled) took 110 us per block - 1.8 of the 2.7 ms of a factorisation at n = 500;
+    // this one is bound by ~500 dependent shared-memory FMAs of the forward substitution.
+    __shared__ T D[kCB * kCD];
+    __shared__ T Di[kCB * kCD];
     if (*info) return;
     const int lane = threadIdx.x, nb = min(kCB, n - j0);
-    T row[kCB];
-#pragma unroll
-    for (int c = 0; c < kCB; ++c) row[c] = (lane < nb && c <= lane && c < nb) ? A[(size_t)(j0 + lane) * lda + j0 + c] : T(0);
+    for (int e = lane; e < kCB * kCB; e += 32) {
+        const int r = e >> 5, c = e & 31;
+        D[r * kCD + c] = (r < nb && c <= r) ? A[(size_t)(j0 + r) * lda + j0 + c] : T(0);
+        Di[r * kCD + c] = T(0);
+    }
+    __syncwarp();
     int fail = 0;
-#pragma unroll
-    for (int k = 0; k < kCB; ++k) {
-        if (k < nb && !fail) {
-            const T dkk = __shfl_sync(0xffffffffu, row[k], k);
-            if (!(dkk > T(0)) || !(dkk < T(INFINITY))) {
-                fail = j0 + k + 1;
-            } else {
-                const T s = Num<T>::sqrt(dkk);
-                T lrk = T(0);
-                if (lane == k) row[k] = s;
-                if (lane > k && lane < nb) { lrk = row[k] / s; row[k] = lrk; }
-#pragma unroll
-                for (int c = k + 1; c < kCB; ++c) {
-                    const T lck = __shfl_sync(0xffffffffu, lrk, c);      // D[c][k]
-                    if (c <= lane && lane < nb && c < nb) row[c] -= lrk * lck;
-                }
-            }
+    for (int k = 0; k < nb; ++k) {
+        const T dkk = D[k * kCD + k];
+        if (!(dkk > T(0)) || !(dkk < T(INFINITY))) {      // also catches NaN (uniform over the warp)
+            fail = j0 + k + 1;
+            break;
         }
+        const T s = Num<T>::sqrt(dkk);
+        T lrk = T(0);
+        __syncwarp();
+        if (lane == k) D[k * kCD + k] = s;
+        if (lane > k && lane < nb) { lrk = D[lane * kCD + k] / s; D[lane * kCD + k] = lrk; }
+        __syncwarp();
+        for (int c = k + 1; c < nb; ++c)
+            if (c <= lane && lane < nb) D[lane * kCD + c] -= lrk * D[c * kCD + k];
+        __syncwarp();
     }
     if (fail) { if (lane == 0) *info = fail; return; }
-    // inverse, lane = column c: x[r] = -(sum_{c <= t < r} L[r][t] x[t]) / L[r][r], x[c] = 1 / L[c][c]
-    T x[kCB];
-#pragma unroll
-    for (int r = 0; r < kCB; ++r) {
-        T acc = T(0);
-#pragma unroll
-        for (int t = 0; t < r; ++t) {
-            const T lrt = __shfl_sync(0xffffffffu, row[t], r);          // L[r][t]
-            if (t >= lane) acc = fma(lrt, x[t], acc);
+    if (lane < nb) {
+        // column `lane` of the inverse: L x = e_lane by forward substitution
+        const int c = lane;
+        Di[c * kCD + c] = T(1) / D[c * kCD + c];
+        for (int r = c + 1; r < nb; ++r) {
+            T acc = T(0);
+            for (int t = c; t < r; ++t) acc = fma(D[r * kCD + t], Di[t * kCD + c], acc);
+            Di[r * kCD + c] = -acc / D[r * kCD + r];
         }
-        const T lrr = __shfl_sync(0xffffffffu, row[r], r);
-        T v = T(0);
-        if (r < nb && lane < nb) {
-            if (r == lane) v = T(1) / lrr;
-            else if (r > lane) v = -acc / lrr;
-        }
-        x[r] = v;
     }
-#pragma unroll
-    for (int c = 0; c < kCB; ++c)
-        if (lane < nb && c < nb) A[(size_t)(j0 + lane) * lda + j0 + c] = c <= lane ? row[c] : T(0);
-    // X block: element (r, c = lane) = x[r]; store row-wise (strided by lane: 32 x 32 block, once per step)
-#pragma unroll
-    for (int r = 0; r < kCB; ++r)
-        if (lane < nb && r < nb) X[(size_t)(j0 + r) * ldx + j0 + lane] = lane <= r ? x[r] : T(0);
+    __syncwarp();
+    for (int e = lane; e < nb * nb; e += 32) {
+        const int r = e / nb, c = e - r * nb;
+        A[(size_t)(j0 + r) * lda + j0 + c] = c <= r ? D[r * kCD + c] : T(0);
+        X[(size_t)(j0 + r) * ldx + j0 + c] = c <= r ? Di[r * kCD + c] : T(0);
+    }
 }
 
 template <typename T>
