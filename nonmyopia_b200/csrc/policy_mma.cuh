@@ -144,11 +144,11 @@ struct MmaSmem {
     double *IN, *OUT, *B0, *B1, *HA, *HB, *stage, *cost_acc, *tab, *par;
     unsigned full0, empty0;     // shared addresses of the mbarrier arrays
     int rows, KS;
-    __device__ void carve(double* base, int d, int H, int rows_) {
+    __device__ void carve(double* base, int d, int H, int rows_, int nst = kStages) {
         rows = rows_;
         KS = H + 4;
         double* p = base;
-        stage = p; p += kStages * kStageElems;                 // 16-byte aligned bulk-copy destinations first
+        stage = p; p += nst * kStageElems;                 // 16-byte aligned bulk-copy destinations first
         tab = p; p += NMB_FAST_TAB_LEN;
         par = nullptr;
         B0 = p; p += rows * KS;
@@ -159,16 +159,17 @@ struct MmaSmem {
         OUT = p; p += d * rows;
         cost_acc = p; p += rows;
         full0 = smem_u32(p);
-        empty0 = full0 + 8 * kStages;
+        empty0 = full0 + 8 * nst;
     }
     // Row group [row_off, row_off + rows_g) of a CTA of rows_total rows: the groups' buffers lie one after the other
     // behind the shared weight ring, the mbarriers behind the last group (same footprint as carve(rows_total)).
-    __device__ void carve_group(double* base, int d, int H, int rows_total, int row_off, int rows_g, int n_par) {
+    __device__ void carve_group(double* base, int d, int H, int rows_total, int row_off, int rows_g, int n_par,
+                                int nst = kStages) {
         rows = rows_g;
         KS = H + 4;
         const int per_row = 4 * KS + 2 * d + 2;
         stage = base;
-        tab = base + kStages * kStageElems;
+        tab = base + nst * kStageElems;
         par = tab + NMB_FAST_TAB_LEN;
         double* p = par + n_par + (size_t)row_off * per_row;
         B0 = p; p += rows * KS;
@@ -179,13 +180,13 @@ struct MmaSmem {
         OUT = p; p += d * rows;
         cost_acc = p;
         full0 = smem_u32(par + n_par + (size_t)rows_total * per_row);
-        empty0 = full0 + 8 * kStages;
+        empty0 = full0 + 8 * nst;
     }
-    static size_t bytes(int d, int H, int rows) {
+    static size_t bytes(int d, int H, int rows, int nst = kStages) {
         PolicyLayout lay;
         lay.init(d, H, 1);
-        return ((size_t)kStages * kStageElems + NMB_FAST_TAB_LEN + SmallPar::elems(lay) + (size_t)4 * rows * (H + 4) +
-                (size_t)(2 * d + 2) * rows + 2 * kStages) * 8;
+        return ((size_t)nst * kStageElems + NMB_FAST_TAB_LEN + SmallPar::elems(lay) + (size_t)4 * rows * (H + 4) +
+                (size_t)(2 * d + 2) * rows + 2 * nst) * 8;
     }
     __device__ MmaRing ring() const { return MmaRing{stage, full0, empty0, KS}; }
 };
@@ -332,6 +333,7 @@ template <int NT> __device__ __forceinline__ void zero_acc4(double (&acc)[NT][2]
 //   in : sm.IN [k][rows] = [x; y];  hprev (sm.HA or sm.HB) = previous hidden state, row-major
 //   out: sm.OUT [k][rows] = sigmoid output;  hnew (the other H buffer) = new hidden state
 // B0 holds the embedding then u1, B1 holds p, u2 overwrites hprev (dead after the GRU).
+template <int NST = kStages>
 __device__ __forceinline__ void mma_policy_forward(const PolicyLayout& lay, const double* __restrict__ theta_t, bool head_a,
                                                    const MmaSmem& sm, MmaWarp& w, double* hprev, double* hnew,
                                                    const SaveAreas<double>* save, long long node0, int nvalid,
@@ -373,7 +375,7 @@ __device__ __forceinline__ void mma_policy_forward(const PolicyLayout& lay, cons
     // ---- prepro: B1 = p = elu(Wp ea + bp)
     pc.mark(2);
     zero_acc4(acc);
-    mma_gemm<kStages>(ring, w, sm.B0, H, acc);
+    mma_gemm<NST>(ring, w, sm.B0, H, acc);
     pc.mark(1);
 #pragma unroll
     for (int t = 0; t < 4; ++t) {
@@ -395,8 +397,8 @@ __device__ __forceinline__ void mma_policy_forward(const PolicyLayout& lay, cons
         const double* bhh = sp.at(S_BHH);
         pc.mark(2);
         zero_acc4(acc);
-        mma_gemm<kStages>(ring, w, sm.B1, H, acc);
-        mma_gemm<kStages>(ring, w, hprev, H, acc);
+        mma_gemm<NST>(ring, w, sm.B1, H, acc);
+        mma_gemm<NST>(ring, w, hprev, H, acc);
         pc.mark(1);
 #pragma unroll
         for (int t = 0; t < 4; ++t) {
@@ -406,8 +408,8 @@ __device__ __forceinline__ void mma_policy_forward(const PolicyLayout& lay, cons
         }
         pc.mark(2);
         zero_acc4(acc);
-        mma_gemm<kStages>(ring, w, sm.B1, H, acc);
-        mma_gemm<kStages>(ring, w, hprev, H, acc);
+        mma_gemm<NST>(ring, w, sm.B1, H, acc);
+        mma_gemm<NST>(ring, w, hprev, H, acc);
         pc.mark(1);
 #pragma unroll
         for (int t = 0; t < 4; ++t) {
@@ -418,8 +420,8 @@ __device__ __forceinline__ void mma_policy_forward(const PolicyLayout& lay, cons
         pc.mark(2);
         zero_acc4(acc);
         zero_acc4(gh);
-        mma_gemm<kStages>(ring, w, sm.B1, H, acc);
-        mma_gemm<kStages>(ring, w, hprev, H, gh);
+        mma_gemm<NST>(ring, w, sm.B1, H, acc);
+        mma_gemm<NST>(ring, w, hprev, H, gh);
         pc.mark(1);
 #pragma unroll
         for (int t = 0; t < 4; ++t) {
@@ -454,8 +456,8 @@ __device__ __forceinline__ void mma_policy_forward(const PolicyLayout& lay, cons
     const int sW6 = head_a ? S_AW6 : S_XW6, sB6 = head_a ? S_AB6 : S_XB6;
     pc.mark(2);
     zero_acc4(acc);
-    mma_gemm<kStages>(ring, w, sm.B1, H, acc);
-    mma_gemm<kStages>(ring, w, hnew, H, acc);
+    mma_gemm<NST>(ring, w, sm.B1, H, acc);
+    mma_gemm<NST>(ring, w, hnew, H, acc);
     pc.mark(1);
 #pragma unroll
     for (int t = 0; t < 4; ++t) {
@@ -473,7 +475,7 @@ __device__ __forceinline__ void mma_policy_forward(const PolicyLayout& lay, cons
     // ---- layer 3: u2 = elu(W3 u1 + b3) -> hprev buffer (dead)
     pc.mark(2);
     zero_acc4(acc);
-    mma_gemm<kStages>(ring, w, sm.B0, H, acc);
+    mma_gemm<NST>(ring, w, sm.B0, H, acc);
     pc.mark(1);
 #pragma unroll
     for (int t = 0; t < 4; ++t) {

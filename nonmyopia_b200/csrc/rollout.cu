@@ -225,7 +225,10 @@ __global__ void __launch_bounds__(kNT, 1) ts_rollout_fwd_kernel(ProblemDev<T> pb
 
 // ================================================================== forward, FP64 tensor pipe + TMA weight stream
 // rows (multiple of 8, <= 56) chains per CTA; rows/4 consumer warps + 1 producer warp (policy_mma.cuh).
-template <int DMAX>
+// NST: depth of the weight ring.  kStages for full CTAs; with <= 16 rows per CTA (few chains: 64 restarts on the whole
+// GPU) the activation buffers are small and the kernel is bound by the LATENCY of the weight stream (phase clocks at 64
+// chains: 2.7 k cycles per GEMM against ~0.6 k of tensor work), so the ring takes the freed shared memory.
+template <int DMAX, int NST = kStages>
 __global__ void __launch_bounds__(kMaxRowsMma * 8 + 32, 1)
     ts_rollout_fwd_mma_kernel(ProblemDev<double> pb, RolloutDev<double> ro0, RolloutDev<double> ro1, int rows_cta) {
     using T = double;
@@ -248,10 +251,10 @@ __global__ void __launch_bounds__(kMaxRowsMma * 8 + 32, 1)
 
     MmaSmem sm;
     SmallPar sp;
-    sm.carve_group(reinterpret_cast<T*>(nmb_smem_raw), d, H, rows_cta, grp ? rowsA : 0, rows, SmallPar::elems(pb.lay));
+    sm.carve_group(reinterpret_cast<T*>(nmb_smem_raw), d, H, rows_cta, grp ? rowsA : 0, rows, SmallPar::elems(pb.lay), NST);
     sp.init(pb.lay, sm.par);
     if (threadIdx.x == 0) {
-        for (int s = 0; s < kStages; ++s) {
+        for (int s = 0; s < NST; ++s) {
             mbar_init(sm.full0 + 8 * s, 1);
             mbar_init(sm.empty0 + 8 * s, ncw_all);
         }
@@ -261,7 +264,7 @@ __global__ void __launch_bounds__(kMaxRowsMma * 8 + 32, 1)
     sp.load(pb.lay, ro.theta_t, sm.par, (int)threadIdx.x, (int)blockDim.x);
     __syncthreads();
     if ((int)threadIdx.x >= nthr_all) {      // producer warp
-        mma_producer<kStages, false>(pb.lay, ro.theta_t, L, sm.ring(), ro.level_begin, ro.level_end);
+        mma_producer<NST, false>(pb.lay, ro.theta_t, L, sm.ring(), ro.level_begin, ro.level_end);
         return;
     }
     MmaWarp w;
@@ -306,7 +309,7 @@ __global__ void __launch_bounds__(kMaxRowsMma * 8 + 32, 1)
         T* hs_out = ro.has_save ? ro.sv.HS + ((size_t)(l + 1) * N + chain0) * H : nullptr;
         T* hprev = (l & 1) ? sm.HB : sm.HA;
         T* hnew = (l & 1) ? sm.HA : sm.HB;
-        mma_policy_forward(pb.lay, ro.theta_t, head_a, sm, w, hprev, hnew, sv, node0, nvalid, hs_out, pc, sp);
+        mma_policy_forward<NST>(pb.lay, ro.theta_t, head_a, sm, w, hprev, hnew, sv, node0, nvalid, hs_out, pc, sp);
 
         // ---- output point, Thompson path, cost: 8 threads per chain (nthr = 8 rows)
         const int r = tid >> 3, lane = tid & 7;
@@ -726,11 +729,20 @@ static int launch_fwd_mma(const nmb_ts_problem_t* p, const nmb_ts_rollout_t* r, 
     RolloutDev<double> r0 = make_rollout<double>(*p, r[0]);
     RolloutDev<double> r1 = n > 1 ? make_rollout<double>(*p, r[1]) : r0;
     const int rows = mma_rows_per_cta(p->n_chains, n, sm_count());
-    const size_t smem = MmaSmem::bytes(p->d, p->H, rows);
-    auto kern = ts_rollout_fwd_mma_kernel<DMAX>;
-    NMB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     dim3 grid((unsigned)((p->n_chains + rows - 1) / rows), (unsigned)n);
-    kern<<<grid, rows * 8 + 32, smem, st>>>(pb, r0, r1, rows);
+    constexpr int kStagesSmall = 10;
+    static const bool no_deep = getenv("NMB_FWD_NO_DEEP_RING") != nullptr;         // A/B switch
+    if (rows <= 16 && !no_deep && MmaSmem::bytes(p->d, p->H, rows, kStagesSmall) <= (size_t)227 * 1024) {
+        const size_t smem = MmaSmem::bytes(p->d, p->H, rows, kStagesSmall);
+        auto kern = ts_rollout_fwd_mma_kernel<DMAX, kStagesSmall>;
+        NMB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        kern<<<grid, rows * 8 + 32, smem, st>>>(pb, r0, r1, rows);
+    } else {
+        const size_t smem = MmaSmem::bytes(p->d, p->H, rows);
+        auto kern = ts_rollout_fwd_mma_kernel<DMAX>;
+        NMB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        kern<<<grid, rows * 8 + 32, smem, st>>>(pb, r0, r1, rows);
+    }
     NMB_LAUNCH_CHECK();
     return 0;
 }

@@ -7,7 +7,7 @@ import bench
 from nonmyopia_b200 import _lib, ts_engine as te
 from nonmyopia_b200.gp import SurrogateGP, draw_thompson_path
 from nonmyopia_b200.ts_loop import TSAMLoop
-n_r, S, Lk = 64, 64, 3
+n_r, S, Lk = 64, (int(sys.argv[1]) if len(sys.argv) > 1 else 64), (int(sys.argv[2]) if len(sys.argv) > 2 else 3)
 N = n_r * S
 prob, prev_x, prev_y, prev_h = bench.host_workload(n_r, S, 0)
 gp = SurrogateGP(prob.train_X, prob.train_Y, kernel=prob.kernel, lengthscale=torch.full((2,), prob.lengthscale),
