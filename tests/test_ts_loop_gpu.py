@@ -102,3 +102,45 @@ def test_step_host_launch_ahead_equals_plain_replays():
     other = hx.clone().pin_memory()
     with pytest.raises(_lib.NmbError):
         loop.step_host(other, hy, hh, out)
+
+
+def test_fused_exchange_kernel_with_one_rank_equals_the_unsharded_iteration():
+    """``nmb_peer_exchange_adamw_step`` (split-K reduce, LL push / receive, rank-ordered sum + AdamW, decision + advance
+    in one kernel) run with a world of ONE rank over a plain device buffer must reproduce the unsharded iteration
+    (objective-side decision, ``nmb_policy_adamw_step``) bit for bit: weights, Adam moments, snapshots, loop state.
+    (The 2-rank tests of tests/test_multigpu_gpu.py need two GPUs; this one runs wherever the suite runs.)"""
+    import ctypes as C
+    from nonmyopia_b200 import _lib
+    from nonmyopia_b200.peer import PeerStruct
+    fx = H.load("query_ts_am_ackley_L1")
+
+    class _SoloExchange:
+        def __init__(self, n, dtype):
+            lib = _lib.lib()
+            lib.nmb_peer_exchange_bytes.restype = C.c_int64
+            nbytes = int(lib.nmb_peer_exchange_bytes(_lib.dtype_code(dtype), C.c_int64(n)))
+            self.buf = torch.zeros(nbytes, dtype=torch.uint8, device="cuda")
+            self.struct = PeerStruct(rank=0, world=1, n=n)
+            self.struct.base[0] = self.buf.data_ptr()
+
+        def byref(self):
+            return C.byref(self.struct)
+
+    ref = _make_loop(fx, max_iter=40)
+    fused = _make_loop(fx, max_iter=40)
+    fused.group = "one rank"                     # objective leaves the decision to the exchange
+    fused.px = _SoloExchange(fused.theta.numel(), fused.theta.dtype)
+    fused.fused_exchange = True
+    n = 14
+    for _ in range(n):
+        ref._iteration()
+        fused._iteration()
+    torch.cuda.synchronize()
+    sa, sb = ref.read_state(), fused.read_state()
+    assert sa.step == sb.step == n and sa.n_snapshots == sb.n_snapshots and sa.stall == sb.stall
+    assert torch.equal(ref.theta, fused.theta) and torch.equal(ref.theta_t, fused.theta_t)
+    assert torch.equal(ref.m, fused.m) and torch.equal(ref.v, fused.v)
+    assert torch.equal(ref.best_loss, fused.best_loss) and torch.equal(ref.best_X, fused.best_X)
+    # the exchange epoch advanced with the loop
+    epoch = fused.px.buf[16 * 8:16 * 8 + 8].view(torch.int64)
+    assert int(epoch) == n
