@@ -771,12 +771,22 @@ static int launch_bwd_mma(const nmb_ts_problem_t* p, const nmb_ts_rollout_t* r, 
     ProblemDev<double> pb = make_problem<double>(*p);
     RolloutDev<double> r0 = make_rollout<double>(*p, *r);
     const int rows = mma_rows_per_cta(p->n_chains, 1, sm_count(), kMaxRowsMmaBwd);
-    const size_t smem = MmaBwdSmem::bytes(p->d, DMAX, p->H, rows);
-    auto kern = ts_rollout_bwd_mma_kernel<DMAX>;
-    NMB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     dim3 grid((unsigned)((p->n_chains + rows - 1) / rows));
-    kern<<<grid, rows * (32 / kNTB) + 32, smem, st>>>(pb, r0, (const double*)gl, (const double*)gc, (const double*)gX,
-                                                       (const double*)gA, (double*)gprev, rows);
+    constexpr int kStagesSmall = 10;         // few chains: small adjoint buffers, the weight stream's latency binds
+    static const bool no_deep = getenv("NMB_FWD_NO_DEEP_RING") != nullptr;
+    if (rows <= 16 && !no_deep && MmaBwdSmem::bytes(p->d, DMAX, p->H, rows, kStagesSmall) <= (size_t)227 * 1024) {
+        const size_t smem = MmaBwdSmem::bytes(p->d, DMAX, p->H, rows, kStagesSmall);
+        auto kern = ts_rollout_bwd_mma_kernel<DMAX, kStagesSmall>;
+        NMB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        kern<<<grid, rows * (32 / kNTB) + 32, smem, st>>>(pb, r0, (const double*)gl, (const double*)gc, (const double*)gX,
+                                                           (const double*)gA, (double*)gprev, rows);
+    } else {
+        const size_t smem = MmaBwdSmem::bytes(p->d, DMAX, p->H, rows);
+        auto kern = ts_rollout_bwd_mma_kernel<DMAX>;
+        NMB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        kern<<<grid, rows * (32 / kNTB) + 32, smem, st>>>(pb, r0, (const double*)gl, (const double*)gc, (const double*)gX,
+                                                           (const double*)gA, (double*)gprev, rows);
+    }
     NMB_LAUNCH_CHECK();
     return 0;
 }
