@@ -28,11 +28,12 @@ template <int DMAX> __host__ __device__ constexpr int wh_tp_elems() { return 32 
 template <int DMAX>
 inline size_t wh_mma_bytes(int ldl, int R, int nst, bool bwd) {
     const size_t tp = bwd ? (size_t)(R / 8) * 2 * wh_tp_elems<DMAX>() : 0;
-    return ((size_t)nst * kStageElems + (size_t)R * wh_ks(ldl) + (size_t)R * DMAX + (size_t)2 * R * DMAX + tp + 2 * nst) * 8;
+    // + 64: the 2^(j/64) table of the table-driven exp (fastmath.cuh) behind the kernel profile
+    return ((size_t)nst * kStageElems + (size_t)R * wh_ks(ldl) + (size_t)R * DMAX + (size_t)2 * R * DMAX + tp + 2 * nst + 64) * 8;
 }
 
 struct WhSmem {
-    double *stage, *A, *xs, *red, *tp;
+    double *stage, *A, *xs, *red, *tp, *tab;
     unsigned full0, empty0;
     int KS;
     template <int DMAX>
@@ -46,6 +47,11 @@ struct WhSmem {
         tp = p; p += bwd ? (R / 8) * 2 * wh_tp_elems<DMAX>() : 0;
         full0 = smem_u32(p);
         empty0 = full0 + 8 * nst;
+        tab = p + 2 * nst;
+    }
+    // the exponential of the kernel profile only indexes the first 64 entries of the fast-math table
+    __device__ void load_tab(int tid, int nthr) const {
+        for (int e = tid; e < 64; e += nthr) tab[e] = g_fast_tab[e];
     }
 };
 
@@ -103,6 +109,7 @@ __global__ void __launch_bounds__(288, 1) whiten_fwd_mma_kernel(GpDev<double> g,
     const int KS = sm.KS;
     const long long p0 = (long long)blockIdx.x * R;
     const int nvalid = (int)min((long long)R, n_pts - p0);
+    sm.load_tab(tid, nthr);
     for (int e = tid; e < R * DMAX; e += nthr) {
         const int r = e / DMAX, k = e - r * DMAX;
         sm.xs[e] = (r < nvalid && k < d) ? pts[(p0 + r) * d + k] * __ldg(g.inv_ls + k) : 0.0;
@@ -130,7 +137,7 @@ __global__ void __launch_bounds__(288, 1) whiten_fwd_mma_kernel(GpDev<double> g,
                     r2 = fma(df, df, r2);
                 }
                 double kap, gc;
-                kernel_profile<double>(g.kernel_id, r2, kap, gc);
+                kernel_profile_tab(g.kernel_id, r2, sm.tab, kap, gc);
                 const double kv = (live && r < nvalid) ? g.amp * kap : 0.0;
                 macc[rr] = fma(kv, al, macc[rr]);
                 sm.A[(size_t)r * KS + j] = kv;
@@ -197,6 +204,7 @@ __global__ void __launch_bounds__(288, 1) whiten_bwd_mma_kernel(GpDev<double> g,
     const int KS = sm.KS;
     const long long p0 = (long long)blockIdx.x * R;
     const int nvalid = (int)min((long long)R, n_pts - p0);
+    sm.load_tab(tid, nthr);
     for (int e = tid; e < R * DMAX; e += nthr) {
         const int r = e / DMAX, k = e - r * DMAX;
         sm.xs[e] = (r < nvalid && k < d) ? pts[(p0 + r) * d + k] * __ldg(g.inv_ls + k) : 0.0;
@@ -250,7 +258,7 @@ __global__ void __launch_bounds__(288, 1) whiten_bwd_mma_kernel(GpDev<double> g,
                         r2 = fma(sd[k], sd[k], r2);
                     }
                     double kap, gc;
-                    kernel_profile<double>(g.kernel_id, r2, kap, gc);
+                    kernel_profile_tab(g.kernel_id, r2, sm.tab, kap, gc);
                     const double coef = (acc[t][e] + gm * al) * g.amp * gc;
 #pragma unroll
                     for (int k = 0; k < DMAX; ++k) gx[k] = fma(coef, sd[k], gx[k]);
