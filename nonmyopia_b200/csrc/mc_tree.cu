@@ -686,7 +686,7 @@ static int launch_whiten_mma_d(const nmb_gp_t* gp, bool bwd, const double* pts, 
 #define NMB_WHM(NST)                                                                                                  \
     if (!bwd) {                                                                                                       \
         NMB_CUDA(cudaFuncSetAttribute(whiten_fwd_mma_kernel<DM, NST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
-        whiten_fwd_mma_kernel<DM, NST><<<grid, nthr, smem, st>>>(g, gp->ldl, R, pts, n_pts, U, m0, q);                 \
+        whiten_fwd_mma_kernel<DM, NST><<<grid, (unsigned)((R / 8) * (8 / kWhNT) + 1) * 32, smem, st>>>(g, gp->ldl, R, pts, n_pts, U, m0, q); \
     } else {                                                                                                          \
         NMB_CUDA(cudaFuncSetAttribute(whiten_bwd_mma_kernel<DM, NST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
         whiten_bwd_mma_kernel<DM, NST><<<grid, nthr, smem, st>>>(g, gp->ldl, R, pts, n_pts, gU, g_m0, g_pts);          \

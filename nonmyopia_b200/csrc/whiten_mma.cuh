@@ -90,14 +90,17 @@ __device__ __forceinline__ void wh_init_barriers(const WhSmem& sm, int nst, int 
 }
 
 // ------------------------------------------------------------------ forward
-template <int DMAX, int NST>
-__global__ void __launch_bounds__(288, 1) whiten_fwd_mma_kernel(GpDev<double> g, int ldl, int R,
+// NT = 8-column tiles per warp: 2 -> four warps per 8-row block (16 consumer warps at 32 rows: the 8-warp form ran at
+// 2.2 warps per scheduler with `wait` as its first stall reason), 4 -> two warps per block.
+constexpr int kWhNT = 2;
+template <int DMAX, int NST, int NT = kWhNT>
+__global__ void __launch_bounds__(32 * (32 / 8) * (8 / NT) + 32, 1) whiten_fwd_mma_kernel(GpDev<double> g, int ldl, int R,
                                                                 const double* __restrict__ pts, long long n_pts,
                                                                 double* __restrict__ U, double* __restrict__ m0,
                                                                 double* __restrict__ q) {
     extern __shared__ __align__(16) unsigned char wh_smem_raw[];
     const int n = g.n, d = g.d, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int ncw = (R >> 3) * 2, nthr = ncw * 32;
+    const int ncw = (R >> 3) * (8 / NT), nthr = ncw * 32;      // every warp generates NT of the R kernel rows
     WhSmem sm;
     sm.carve<DMAX>(reinterpret_cast<double*>(wh_smem_raw), ldl, R, NST);
     wh_init_barriers(sm, NST, ncw);
@@ -118,7 +121,9 @@ __global__ void __launch_bounds__(288, 1) whiten_fwd_mma_kernel(GpDev<double> g,
     // ---- kernel rows: lane = training point (its scaled coordinates loaded once, reused for the warp's 4 query
     //      rows = 4 independent sqrt/exp chains), conflict-free row-major stores
     {
-        double ils[DMAX], macc[4] = {0.0, 0.0, 0.0, 0.0};
+        double ils[DMAX], macc[NT];
+#pragma unroll
+        for (int rr = 0; rr < NT; ++rr) macc[rr] = 0.0;
 #pragma unroll
         for (int k = 0; k < DMAX; ++k) ils[k] = k < d ? __ldg(g.inv_ls + k) : 0.0;
         for (int j = lane; j < KS; j += 32) {
@@ -128,7 +133,7 @@ __global__ void __launch_bounds__(288, 1) whiten_fwd_mma_kernel(GpDev<double> g,
             for (int k = 0; k < DMAX; ++k) tj[k] = (live && k < d) ? __ldg(g.train_x + (size_t)j * d + k) * ils[k] : 0.0;
             if (live) al = __ldg(g.alpha + j);
 #pragma unroll
-            for (int rr = 0; rr < 4; ++rr) {
+            for (int rr = 0; rr < NT; ++rr) {
                 const int r = warp + rr * ncw;
                 double r2 = 0.0;
 #pragma unroll
@@ -144,7 +149,7 @@ __global__ void __launch_bounds__(288, 1) whiten_fwd_mma_kernel(GpDev<double> g,
             }
         }
 #pragma unroll
-        for (int rr = 0; rr < 4; ++rr) {
+        for (int rr = 0; rr < NT; ++rr) {
             const int r = warp + rr * ncw;
             const double s = warp_sum(macc[rr]);
             if (lane == 0 && r < nvalid) m0[p0 + r] = s;
@@ -153,16 +158,16 @@ __global__ void __launch_bounds__(288, 1) whiten_fwd_mma_kernel(GpDev<double> g,
     consumer_sync(nthr);
     // ---- U tile = K L^-T, 64 output columns at a time; only k < cb + 64 contributes
     MmaWarp w;
-    w.init(warp, nthr, n);
+    w.init(warp, nthr, n, NT);
     const int row = w.row0 + w.fr;
     double qacc = 0.0;
     for (int cb = 0; cb < n; cb += kOB) {
-        double acc[4][2];
+        double acc[NT][2];
         zero_acc4(acc);
         w.active = cb + w.col0 < n;
-        mma_gemm<NST>(ring, w, sm.A, min(cb + kOB, ldl), acc);
+        mma_gemm<NST, NT>(ring, w, sm.A, min(cb + kOB, ldl), acc);
 #pragma unroll
-        for (int t = 0; t < 4; ++t) {
+        for (int t = 0; t < NT; ++t) {
             const int c = cb + w.col0 + 8 * t + 2 * w.fk;
             if (c < n) {
                 const bool two = c + 1 < n;
@@ -178,9 +183,15 @@ __global__ void __launch_bounds__(288, 1) whiten_fwd_mma_kernel(GpDev<double> g,
     }
     qacc += shfl_xor_(qacc, 1);
     qacc += shfl_xor_(qacc, 2);
-    if (w.fk == 0) sm.red[(warp & 1) * R + row] = qacc;
+    constexpr int wpr = 8 / NT;                                   // column warps that share a row block
+    if (w.fk == 0) sm.red[(warp % wpr) * R + row] = qacc;
     consumer_sync(nthr);
-    if (tid < nvalid) q[p0 + tid] = sm.red[tid] + sm.red[R + tid];
+    if (tid < nvalid) {
+        double qs = 0.0;
+#pragma unroll
+        for (int c = 0; c < wpr; ++c) qs += sm.red[c * R + tid];
+        q[p0 + tid] = qs;
+    }
 }
 
 // ------------------------------------------------------------------ backward
