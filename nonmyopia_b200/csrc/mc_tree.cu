@@ -689,7 +689,7 @@ static int launch_whiten_mma_d(const nmb_gp_t* gp, bool bwd, const double* pts, 
         whiten_fwd_mma_kernel<DM, NST><<<grid, (unsigned)((R / 8) * (8 / kWhNT) + 1) * 32, smem, st>>>(g, gp->ldl, R, pts, n_pts, U, m0, q); \
     } else {                                                                                                          \
         NMB_CUDA(cudaFuncSetAttribute(whiten_bwd_mma_kernel<DM, NST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
-        whiten_bwd_mma_kernel<DM, NST><<<grid, nthr, smem, st>>>(g, gp->ldl, R, pts, n_pts, gU, g_m0, g_pts);          \
+        whiten_bwd_mma_kernel<DM, NST><<<grid, (unsigned)((R / 8) * (8 / kWhNT) + 1) * 32, smem, st>>>(g, gp->ldl, R, pts, n_pts, gU, g_m0, g_pts); \
     }
     if (nst == 4) { NMB_WHM(4) } else { NMB_WHM(3) }
 #undef NMB_WHM

@@ -195,15 +195,15 @@ __global__ void __launch_bounds__(32 * (32 / 8) * (8 / NT) + 32, 1) whiten_fwd_m
 }
 
 // ------------------------------------------------------------------ backward
-template <int DMAX, int NST>
-__global__ void __launch_bounds__(288, 1) whiten_bwd_mma_kernel(GpDev<double> g, int ldl, int R,
+template <int DMAX, int NST, int NT = kWhNT>
+__global__ void __launch_bounds__(32 * (32 / 8) * (8 / NT) + 32, 1) whiten_bwd_mma_kernel(GpDev<double> g, int ldl, int R,
                                                                 const double* __restrict__ pts, long long n_pts,
                                                                 const double* __restrict__ gU,
                                                                 const double* __restrict__ g_m0,
                                                                 double* __restrict__ g_pts) {
     extern __shared__ __align__(16) unsigned char wh_smem_raw[];
     const int n = g.n, d = g.d, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int ncw = (R >> 3) * 2, nthr = ncw * 32;
+    const int ncw = (R >> 3) * (8 / NT), nthr = ncw * 32;
     WhSmem sm;
     sm.carve<DMAX>(reinterpret_cast<double*>(wh_smem_raw), ldl, R, NST, true);
     wh_init_barriers(sm, NST, ncw);
@@ -227,7 +227,7 @@ __global__ void __launch_bounds__(288, 1) whiten_bwd_mma_kernel(GpDev<double> g,
     }
     consumer_sync(nthr);
     MmaWarp w;
-    w.init(warp, nthr, n);
+    w.init(warp, nthr, n, NT);
     const int row = w.row0 + w.fr;
     const double gm = row < nvalid ? g_m0[p0 + row] : 0.0;
     double xr[DMAX], gx[DMAX];
@@ -236,32 +236,37 @@ __global__ void __launch_bounds__(288, 1) whiten_bwd_mma_kernel(GpDev<double> g,
     double ils[DMAX];
 #pragma unroll
     for (int k = 0; k < DMAX; ++k) ils[k] = k < d ? __ldg(g.inv_ls + k) : 0.0;
-    double* tp = sm.tp + (size_t)warp * wh_tp_elems<DMAX>();
+    // this warp's 8 NT training points of the column block and their alpha: [8 NT][DMAX + 1] then [8 NT]
+    constexpr int WC = 8 * NT;
+    double* tp = sm.tp + (size_t)warp * (WC * (DMAX + 2));
     for (int cb = 0; cb < n; cb += kOB) {
-        double acc[4][2];
+        double acc[NT][2];
         zero_acc4(acc);
         w.active = cb + w.col0 < n;
         // this warp's 32 training points of the block (one per lane), fetched under the GEMM and parked in shared
         // memory for the epilogue (per-column global loads inside the epilogue were 19 % of the stall samples)
         const int cpt = cb + w.col0 + lane;
+        const bool mine = lane < WC && cpt < n;
         double tjr[DMAX], alr = 0.0;
 #pragma unroll
-        for (int k = 0; k < DMAX; ++k) tjr[k] = (cpt < n && k < d) ? __ldg(g.train_x + (size_t)cpt * d + k) * ils[k] : 0.0;
-        if (cpt < n) alr = __ldg(g.alpha + cpt);
+        for (int k = 0; k < DMAX; ++k) tjr[k] = (mine && k < d) ? __ldg(g.train_x + (size_t)cpt * d + k) * ils[k] : 0.0;
+        if (mine) alr = __ldg(g.alpha + cpt);
         // g_K[r][j] = sum_{i >= j} gU[r][i] Linv[i][j]: rows i >= cb of Linv, columns cb..cb+63
-        mma_gemm<NST>(ring, w, sm.A + cb, ldl - cb, acc);
+        mma_gemm<NST, NT>(ring, w, sm.A + cb, ldl - cb, acc);
+        __syncwarp();
+        if (lane < WC) {
+#pragma unroll
+            for (int k = 0; k < DMAX; ++k) tp[lane * (DMAX + 1) + k] = tjr[k];
+            tp[WC * (DMAX + 1) + lane] = alr;
+        }
         __syncwarp();
 #pragma unroll
-        for (int k = 0; k < DMAX; ++k) tp[lane * (DMAX + 1) + k] = tjr[k];
-        tp[32 * (DMAX + 1) + lane] = alr;
-        __syncwarp();
-#pragma unroll
-        for (int t = 0; t < 4; ++t) {
+        for (int t = 0; t < NT; ++t) {
 #pragma unroll
             for (int e = 0; e < 2; ++e) {
                 const int cl = 8 * t + 2 * w.fk + e;
                 if (cb + w.col0 + cl < n) {
-                    const double al = tp[32 * (DMAX + 1) + cl];
+                    const double al = tp[WC * (DMAX + 1) + cl];
                     double sd[DMAX], r2 = 0.0;
 #pragma unroll
                     for (int k = 0; k < DMAX; ++k) {
@@ -280,14 +285,23 @@ __global__ void __launch_bounds__(288, 1) whiten_bwd_mma_kernel(GpDev<double> g,
     // reduce over the 4 lanes of a fragment row and the 2 column warps that share the rows
 #pragma unroll
     for (int k = 0; k < DMAX; ++k) { gx[k] += shfl_xor_(gx[k], 1); gx[k] += shfl_xor_(gx[k], 2); }
+    // (the gU tile is dead once every warp has left its last GEMM: it holds the 8 / NT partial sums per row)
+    constexpr int wpr = 8 / NT;
+    consumer_sync(nthr);
+    double* red = sm.A;
     if (w.fk == 0) {
 #pragma unroll
-        for (int k = 0; k < DMAX; ++k) sm.red[((warp & 1) * R + row) * DMAX + k] = gx[k];
+        for (int k = 0; k < DMAX; ++k) red[((warp % wpr) * R + row) * DMAX + k] = gx[k];
     }
     consumer_sync(nthr);
     for (int e = tid; e < R * DMAX; e += nthr) {
         const int r = e / DMAX, k = e - r * DMAX;
-        if (r < nvalid && k < d) g_pts[(p0 + r) * d + k] += (sm.red[e] + sm.red[R * DMAX + e]) * __ldg(g.inv_ls + k);
+        if (r < nvalid && k < d) {
+            double v = 0.0;
+#pragma unroll
+            for (int c = 0; c < wpr; ++c) v += red[c * R * DMAX + e];
+            g_pts[(p0 + r) * d + k] += v * __ldg(g.inv_ls + k);
+        }
     }
 }
 
