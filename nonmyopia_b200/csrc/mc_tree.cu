@@ -320,6 +320,8 @@ __global__ void __launch_bounds__(256) level_fwd_kernel(GpDev<T> g, const __grid
             const T* uz[4];
 #pragma unroll
             for (int b = 0; b < 4; ++b) uz[b] = st.U + (size_t)(tr.off[min(t0 + b, s - 1)] + i % tr.cnt[min(t0 + b, s - 1)]) * g.ldu;
+            // (independent load streams: unrolled so that ~20 loads per lane are in flight - the kernel ran at 1.9 TB/s)
+#pragma unroll 4
             for (int k = lane; k < g.n; k += 32) {
                 const T x = ux[k];
 #pragma unroll
